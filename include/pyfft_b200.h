@@ -1,0 +1,241 @@
+/*
+ * pyfft_b200 -- C ABI of the B200-native accelerator for PYFFT's segmented
+ * spectral-estimation hot path (Welch / STFT / correlation / Hilbert).
+ *
+ * The reference (gmweir/PYFFT) has NO FFI, plugin or operator interface: the hot
+ * path sits behind plain Python callables and bottoms out in numpy.fft call
+ * sites inside per-segment Python loops.  Each entry point below therefore
+ * replaces one of those loops *together with* the numpy.fft calls it feeds; the
+ * "replaces" note on each function cites the reference lines (paths relative to
+ * the reference tree).  INTEGRATION.md shows the ctypes binding a maintainer of
+ * the reference would add.
+ *
+ * Conventions
+ *  - every function returns 0 on success or a negative pyfft_status code;
+ *    pyfft_last_error() returns a thread-local human readable message.
+ *  - all data pointers are DEVICE pointers owned by the caller; the library
+ *    allocates nothing persistent except cached twiddle tables (freed by
+ *    pyfft_shutdown()).  Inputs are const and never written.
+ *  - every call is asynchronous on `stream` (a cudaStream_t passed as void*);
+ *    the library never synchronises the device.
+ *  - no CPU fallback exists: unsupported shapes return PYFFT_EUNSUPPORTED.
+ */
+#ifndef PYFFT_B200_H
+#define PYFFT_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum pyfft_status {
+    PYFFT_OK = 0,
+    PYFFT_EINVAL = -1,       /* bad argument (maps to ValueError)              */
+    PYFFT_EUNSUPPORTED = -2, /* valid but not implemented (NotImplementedError) */
+    PYFFT_ECUDA = -3         /* CUDA runtime error (RuntimeError)               */
+} pyfft_status;
+
+typedef enum pyfft_dtype { PYFFT_F32 = 0, PYFFT_F64 = 1 } pyfft_dtype;
+
+/* detrend modes of fftanal._detrend_func (fft_analysis.py:2538-2549) */
+typedef enum pyfft_detrend { PYFFT_DETREND_NONE = 0, PYFFT_DETREND_MEAN = 1,
+                             PYFFT_DETREND_LINEAR = 2 } pyfft_detrend;
+
+/*
+ * How the "analysed record" x_in[j], j = 0 .. nsig-1 (fft_analysis.py:353-354)
+ * maps onto the caller's sample arrays.  The reference materialises
+ * reflect-padded copies (fft_analysis.py:196-205); here the map is evaluated in
+ * the gather, no copy is made:
+ *     g(j) = (j < reflect) ? (reflect - j) : (j - reflect + i0)      global sample index
+ *     element read = ptr[g(j) - src_base]
+ * src_base lets one rank hold only its slice of a long record (multi-GPU).
+ */
+typedef struct pyfft_record_map {
+    int64_t nsig;      /* length of the analysed record                          */
+    int64_t i0;        /* first analysed sample (fft_analysis.py:143)            */
+    int64_t reflect;   /* nwins-1 when the reference reflect-pads, else 0        */
+    int64_t src_base;  /* global sample index of element 0 of the given pointers */
+    int64_t src_len;   /* elements per channel reachable behind the pointers     */
+} pyfft_record_map;
+
+/* Segmentation (fft_analysis.py:189-221, 359-364): segment k covers analysed
+ * indices [k*hop, k*hop + nfft). */
+typedef struct pyfft_segmentation {
+    int32_t nfft;       /* = nwins; power of two, 16 .. 8192                     */
+    int32_t hop;        /* nwins - noverlap                                      */
+    int64_t seg_first;  /* first segment handled by this call (shard offset)     */
+    int64_t seg_count;  /* number of segments handled by this call               */
+} pyfft_segmentation;
+
+const char* pyfft_version(void);
+const char* pyfft_last_error(void);
+/* frees cached twiddle tables on every device */
+int pyfft_shutdown(void);
+/* number of SMs of the current device (grid sizing / reporting) */
+int pyfft_sm_count(void);
+
+/* ------------------------------------------------------------------------- *
+ * K0  detrend statistics
+ * replaces: pybaseutils detrend_mean / detrend_linear applied to the whole
+ *           analysed record (fft_analysis.py:356-357, 2147-2149).
+ * For each of the nch channels (channel c at ptr + c*ch_stride) ADDS
+ *     stats[2*c+0] += sum_j x(j)      stats[2*c+1] += sum_j j*x(j)
+ * over analysed indices j in [j_begin, j_end).  stats is double[2*nch] and must
+ * be zeroed by the caller (it is a running sum so shards can be all-reduced).
+ * ------------------------------------------------------------------------- */
+int pyfft_detrend_stats(int dtype, const void* ptr, int64_t ch_stride, int32_t nch,
+                        const pyfft_record_map* map, int64_t j_begin, int64_t j_end,
+                        double* stats, void* stream);
+
+/* Turns the (all-reduced) stats into per-channel trend coefficients
+ *     coef[2*c+0] = a, coef[2*c+1] = b   with   detrended(j) = x(j) - (a + b*j)
+ * for mode MEAN (b = 0) or LINEAR (least-squares line over j = 0..nsig-1). */
+int pyfft_detrend_coef(int mode, const double* stats, int32_t nch, int64_t nsig,
+                       double* coef, void* stream);
+
+/* ------------------------------------------------------------------------- *
+ * K1  fused Welch auto/cross accumulation
+ * replaces: the hot loop of fft_pwelch (fft_analysis.py:359-393) -- segment
+ *           gather, window multiply, np.fft.fft per segment, X conj(X),
+ *           Y conj(Y), Y conj(X) -- and the segment sum of :444-446, without
+ *           materialising any per-segment spectrum.
+ * For each pair p = 0..nch-1 the REAL signals u = x, v = y[p] (y channel p at
+ * y + p*y_stride) are packed as u + i v into ONE complex FFT per segment and
+ * split by Hermitian symmetry in registers.  Running sums are ADDED to
+ *     acc[p][0][f] += sum_k |U_k[f]|^2          acc[p][1][f] += sum_k |V_k[f]|^2
+ *     acc[p][2][f] += Re sum_k V_k[f] conj(U_k[f])   acc[p][3][f] += Im ...
+ * for f = 0 .. nfft/2 (nfft/2+1 bins, unscaled), acc = double[nch][4][nfft/2+1].
+ * coef_x (double[2]) / coef_y (double[2*nch]) are the trend coefficients from
+ * pyfft_detrend_coef or NULL.  window = nfft values of `dtype`.
+ * workspace: pyfft_welch_workspace_bytes() bytes of scratch.
+ * ------------------------------------------------------------------------- */
+int64_t pyfft_welch_workspace_bytes(int dtype, const pyfft_segmentation* seg, int32_t nch);
+
+int pyfft_welch_accumulate(int dtype, const void* x, const void* y, int64_t y_stride,
+                           int32_t nch, const pyfft_record_map* map,
+                           const pyfft_segmentation* seg, const void* window,
+                           const double* coef_x, const double* coef_y,
+                           double* acc, void* workspace, int64_t workspace_bytes,
+                           void* stream);
+
+/* ------------------------------------------------------------------------- *
+ * Welch finalize
+ * replaces: one-/two-sided selection and doubling (fft_analysis.py:402-428),
+ *           scaling by 1/S1^2/ENBW (:432-440), the mean over segments
+ *           (:444-446), Cxy_Cxy2 (:1662-1680) and phi_xy (:520).
+ * acc as written by pyfft_welch_accumulate (after any all-reduce), K = total
+ * number of segments summed, scale = 1/(S1^2 * ENBW) (the reference's constants).
+ * onesided != 0: F = nnyq bins [0, nnyq) with x2 on bins 1..F-2 (and F-1 when
+ *                nfft is odd -- never for the power-of-two sizes here);
+ * onesided == 0: F = nfft bins in fftshift order, negative frequencies filled
+ *                from Hermitian symmetry of the real inputs.
+ * Outputs (device, complex128 = double[2]): Pxx[F], Pyy[F][nch], Pxy[F][nch],
+ * Cxy[F][nch], Cxy2[F][nch]; phi[F][nch] double.  Any output may be NULL.
+ * ------------------------------------------------------------------------- */
+int pyfft_welch_finalize(const double* acc, int32_t nfft, int32_t nch, int64_t K,
+                         double scale, int32_t onesided,
+                         double* Pxx, double* Pyy, double* Pxy,
+                         double* Cxy, double* Cxy2, double* phi, void* stream);
+
+/* ------------------------------------------------------------------------- *
+ * K3a  correlation epilogue
+ * replaces: fft_analysis.py:544-597 (and fftanal.crosscorr :1840-1878): the
+ *           irfft / ifft of the averaged spectra, sqrt(nfft) scaling and
+ *           fftshift.  spec = complex128 [F][ncol] (row-major, as produced by
+ *           pyfft_welch_finalize), out = [nfft][ncol]: double when onesided
+ *           (irfft), complex128 when two-sided (ifft(ifftshift)).
+ * halve_interior != 0 applies the x0.5 on bins 1..F-2 the reference uses for
+ * Rxx/Ryy/Rxy (not for iCxy).  Output is sqrt(nfft)*inverse, fftshift-ed.
+ * ------------------------------------------------------------------------- */
+int pyfft_welch_correlation(const double* spec, int32_t nfft, int32_t ncol,
+                            int32_t onesided, int32_t halve_interior,
+                            double* out, void* stream);
+
+/* ------------------------------------------------------------------------- *
+ * K2  short-time Fourier transform (per-segment spectra written out)
+ * replaces: fftanal.fft_win (fft_analysis.py:2126-2203) -- the loop behind
+ *           Xstft/Ystft and spectrogram.stft -- and spectrogram.specgram's loop
+ *           (spectrogram.py:91-112).
+ * Channel c (at x + c*ch_stride, real or interleaved complex samples) and
+ * segment k produce nbins values
+ *     out[c][k][b] = bin_scale[b] * FFT(window * detrended segment)[bin_first + b (mod nfft)]
+ * bin_scale (double[nbins]) carries the reference's sqrt(2)/S1/sqrt(ENBW)
+ * factors (or NULL = 1).  power_out != 0 writes |.|^2 * bin_scale[b] as a real
+ * array instead (specgram).  out_transposed != 0 stores [c][b][k] (specgram's
+ * (wl, nWindows) layout).  Output type follows `dtype` (complex64/128, or
+ * float/double for power_out).
+ * pseg (optional, double[nch][seg_count]) receives
+ *     sum_n g_n - (g_0 + g_{L-1})/2,  g = |window*x|^2     (trapezoid rule core of :2174)
+ * detrend_per_segment != 0 removes the segment's own mean (detrendwin=True,
+ * :2169-2172) instead of using coef.
+ * ------------------------------------------------------------------------- */
+int pyfft_stft(int dtype, int32_t complex_in, const void* x, int64_t ch_stride, int32_t nch,
+               const pyfft_record_map* map, const pyfft_segmentation* seg,
+               const void* window, const double* coef, int32_t detrend_per_segment,
+               int32_t bin_first, int32_t nbins, const double* bin_scale,
+               int32_t power_out, int32_t out_transposed,
+               void* out, double* pseg, void* stream);
+
+/* ------------------------------------------------------------------------- *
+ * Spectral products of materialised STFTs (the non-fused path; used for
+ * complex inputs and for the fftanal class path that keeps *_seg arrays)
+ * replaces: fftanal.Pstft + averagewins means (fft_analysis.py:1944-1990) and
+ *           fft_pwelch :391-393/:444-446 for complex input.
+ * X[K][nb], Y[nch][K][nb] complex of `dtype`; conj_x != 0 gives Y conj(X)
+ * (fft_pwelch convention), else X conj(Y) (fftanal.Pstft convention).
+ * Writes double sums (not means): sxx[nb], syy[nch][nb], sxy[nch][nb][2].
+ * ------------------------------------------------------------------------- */
+int pyfft_stft_products(int dtype, const void* X, const void* Y, int32_t nch, int64_t K,
+                        int32_t nb, int32_t conj_x, double* sxx, double* syy, double* sxy,
+                        void* stream);
+
+/* ------------------------------------------------------------------------- *
+ * K3b  long transforms: analytic signal and FFT cross-correlation
+ * replaces: hilbert.hilbert / hilbert_1d (hilbert.py:22-112) and ccf.ccf /
+ *           fftcorr / cross_correlation_fft (ccf.py:66-77, 239-303).
+ * n must be a power of two for hilbert (2^4 .. 2^27); xcorr zero-pads to the
+ * next power of two >= 2n-1 internally.
+ * pyfft_hilbert: in = batch real records [batch][n]; analytic (complex, may be
+ *   NULL) and/or envelope (|z|, real, may be NULL) of `dtype`.
+ * pyfft_xcorr: for each pair p: out[p][0 .. 2n-2] = correlate(x_p - mean,
+ *   y_p - mean, 'full') * norm_p, norm_p = 1/(n*std_x*std_y) when normalise != 0
+ *   (ccf.py:74-76) else 1; x_p = x + p*x_stride (x_stride may be 0 to reuse one
+ *   reference channel).
+ * workspace sizes from pyfft_bigfft_workspace_bytes(dtype, nfft_padded, batch).
+ * ------------------------------------------------------------------------- */
+int64_t pyfft_bigfft_workspace_bytes(int dtype, int64_t nfft, int32_t batch);
+
+int pyfft_hilbert(int dtype, const void* in, int64_t n, int32_t batch,
+                  void* analytic, void* envelope, void* workspace,
+                  int64_t workspace_bytes, void* stream);
+
+int pyfft_xcorr(int dtype, const void* x, int64_t x_stride, const void* y, int64_t y_stride,
+                int64_t n, int32_t pairs, int32_t normalise, void* out,
+                void* workspace, int64_t workspace_bytes, void* stream);
+
+/* Batched complex FFT of power-of-two length 2^4 .. 2^27 (forward: e^{-2 pi i nk/N}
+ * unnormalised; inverse: 1/N), the numpy.fft.fft/ifft contract used at every
+ * reference call site (fft_analysis.py:2096-2116).  in/out complex of `dtype`,
+ * [batch][n]; in may equal out. */
+int pyfft_fft_c2c(int dtype, const void* in, void* out, int64_t n, int32_t batch,
+                  int32_t inverse, void* workspace, int64_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------- *
+ * K4  multi-channel cross-spectral matrix
+ * replaces: the per-reference-channel loop over fft_pwelch in
+ *           HeatPulse_Funcs.py:576-583 (G[f][i][j] = sum_k X_j conj(X_i)).
+ * x = [nch][..] real channels; ADDS unscaled sums into
+ * G = double[nfft/2+1][nch][nch][2].
+ * ------------------------------------------------------------------------- */
+int64_t pyfft_csm_workspace_bytes(int dtype, const pyfft_segmentation* seg, int32_t nch);
+
+int pyfft_csm_accumulate(int dtype, const void* x, int64_t ch_stride, int32_t nch,
+                         const pyfft_record_map* map, const pyfft_segmentation* seg,
+                         const void* window, const double* coef, double* G,
+                         void* workspace, int64_t workspace_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PYFFT_B200_H */

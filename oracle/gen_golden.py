@@ -1,0 +1,161 @@
+"""TEST INFRASTRUCTURE ONLY -- writes tests/golden/*.npz from the UNMODIFIED reference.
+
+Run in the build container (needs /root/reference):
+
+    python -m oracle.gen_golden
+
+Each fixture stores the inputs (so nothing depends on RNG stream stability), the
+call's keyword arguments and every averaged output of the reference call.  The
+fixtures pin (a) oracle/restatement.py (tests/test_oracle_golden.py, CPU) and
+(b) the CUDA path (tests/test_gpu_golden.py, GPU, through the C ABI).
+"""
+import json
+import os
+import sys
+
+import numpy as np
+
+from . import ref_shim, signals
+
+OUT = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
+                   "tests", "golden")
+
+WELCH_FIELDS = ["Cxy2", "Lxx", "Lyy", "Lxy", "Rxx", "Ryy", "Rxy", "iCxy", "corrcoef",
+                "lags", "Ex", "Ey", "varCxy", "varCxy2", "varPxx", "varPyy", "varPxy",
+                "varPhxy", "varLxx", "varLyy", "varLxy", "S1", "S2", "ENBW", "NENBW",
+                "win", "minFreq", "nwins", "noverlap", "Navr", "nch", "Fs"]
+
+
+def _pack_t(t):
+    """tvec is stored as (n, fs) when it is exactly arange(n)/fs, else verbatim."""
+    n = len(t)
+    if np.array_equal(t, np.arange(n) / signals.FS):
+        return dict(in_t_n=np.asarray(n), in_t_fs=np.asarray(signals.FS))
+    return dict(in_t=t)
+
+
+def _welch(fa, name, t, x, y, tbounds=None, **kw):
+    import warnings
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        r = fa.fft_pwelch(t, x, y, tbounds, useMLAB=False, plotit=False, verbose=False, **kw)
+    info = r[6]
+    d = dict(in_x=x, in_y=y, freq=r[0], Pxy=r[1], Pxx=r[2], Pyy=r[3], Cxy=r[4],
+             phi_xy=r[5])
+    for f in WELCH_FIELDS:
+        d[f] = np.asarray(getattr(info, f))
+    d["ibnds"] = np.asarray(info.ibnds)
+    d.update(_pack_t(t))
+    meta = dict(kw)
+    meta["tbounds"] = None if tbounds is None else [float(v) for v in tbounds]
+    d["kwargs_json"] = np.asarray(json.dumps(meta))
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), **d)
+    print("wrote", name, "K=%d L=%d" % (info.Navr, info.nwins))
+
+
+def main():
+    os.makedirs(OUT, exist_ok=True)
+    m = ref_shim.load_reference()
+    fa, W, SP, H = m["fft_analysis"], m["windows"], m["spectrogram"], m["hilbert"]
+    rng = np.random.default_rng(2026)
+
+    # ---- windows(): every family at two lengths + ROV ---------------------- #
+    names = ["Hanning", "Hamming", "Blackman", "Nuttall3", "nut3a", "nut3b", "nut4",
+             "nut4a", "nut4b", "nut4c", "SFT3F", "SFT4F", "SFT5F", "SFT3M", "SFT4M",
+             "SFT5M", "welch", "bartlett", "box"]
+    d = {}
+    for nm in names:
+        for n in (64, 129):
+            d["%s_%d" % (nm, n)] = W.windows(nm, nwins=n, verbose=False)
+            d["%s_%d_aper" % (nm, n)] = W.windows(nm, nwins=n, periodic=False, verbose=False)
+        d["%s_rov" % nm] = np.asarray(W.windows(nm, verbose=False))
+    d["kaiser8_64"] = W.windows("kaiser", nwins=64, beta=8.0, verbose=False)
+    d["names_json"] = np.asarray(json.dumps(names))
+    np.savez_compressed(os.path.join(OUT, "windows.npz"), **d)
+
+    # ---- fft_pwelch -------------------------------------------------------- #
+    t, x = signals.c1_auto(n=2 ** 15)
+    _welch(fa, "welch_c1_auto", t, x, x, Navr=63, windowoverlap=0.5,
+           windowfunction="Hanning", detrend_style=1)
+    t, x = signals.c1_auto(n=2 ** 14, bin_centred=True)
+    _welch(fa, "welch_c1_bincentred", t, x, x, Navr=31, windowoverlap=0.5,
+           windowfunction="Hanning", detrend_style=1)
+    t, x, y = signals.c2_cross(n=2 ** 15)
+    _welch(fa, "welch_c2_cross", t, x, y, Navr=15, windowoverlap=0.5,
+           windowfunction="Hanning", detrend_style=1)
+    t, x, y = signals.c2_cross(n=2 ** 15, dc=(7.0, 2.5))
+    _welch(fa, "welch_c2_dc", t, x, y, Navr=15, windowoverlap=0.5,
+           windowfunction="Hanning", detrend_style=1)
+    # multi-channel sigy, flat-top window at its ROV, linear detrend
+    t = signals.tvec(20000)
+    x = np.sin(2 * np.pi * 31e3 * t) + 0.2 * rng.standard_normal(len(t)) + 1e-4 * np.arange(len(t))
+    y = np.stack([np.sin(2 * np.pi * 31e3 * t - 0.4 * c) + 0.2 * rng.standard_normal(len(t)) + c
+                  for c in range(3)], 1)
+    _welch(fa, "welch_multi_sft3f_linear", t, x, y, Navr=12, windowfunction="SFT3F",
+           detrend_style=-1)
+    # defaults everywhere (Navr=8, Hanning ROV, mean detrend)
+    _welch(fa, "welch_defaults", t[:4096 * 4], x[:4096 * 4], y[:4096 * 4, 0])
+    # two-sided, complex x
+    xc = x[:8192] + 1j * rng.standard_normal(8192)
+    _welch(fa, "welch_twosided_complex", t[:8192], xc, y[:8192, :2], Navr=15,
+           windowoverlap=0.5, windowfunction="Hamming", detrend_style=1)
+    # partial record (no reflect padding), explicit tper, no detrend
+    _welch(fa, "welch_tbounds_tper", t, x, y[:, :2], [0.002, 0.0121], windowoverlap=0.5,
+           windowfunction="Hanning", detrend_style=0, tper=1024 / signals.FS * (1 + 1e-9))
+    # odd window length (non power of two)
+    _welch(fa, "welch_odd_nfft", t[:12345], x[:12345], y[:12345, 0], Navr=7,
+           windowoverlap=0.3, windowfunction="bartlett", detrend_style=1)
+    # the reference's own self-test recipe (fft_analysis.py:2899-2944)
+    t, x, y = signals.ref_test_fftpwelch()
+    _welch(fa, "welch_ref_selftest", t, x, y, [t[1], t[-1]], Navr=8, windowoverlap=0.5,
+           windowfunction="hamming", detrend_style=1)
+
+    # ---- fftanal class STFT path (what spectrogram.stft returns) ----------- #
+    t, ch = signals.c3_chirps(n=2 ** 15, nch=2)
+    tper = 2048 / signals.FS * (1 + 1e-9)
+    d = dict(in_y=ch, tper=tper)
+    d.update(_pack_t(t))
+    for c in range(2):
+        o = SP.stft(t, ch[c], tper=tper, windowoverlap=0.75, windowfunction="Hanning",
+                    verbose=False)
+        d.update({"Xseg_%d" % c: o.Xseg, "Xpow_%d" % c: o.Xpow, "Xfft_%d" % c: o.Xfft,
+                  "Pxx_%d" % c: o.Pxx})
+    d.update(tseg=o.tseg, freq=o.freq, nwins=o.nwins, noverlap=o.noverlap, Navr=o.Navr,
+             S1=o.S1, S2=o.S2, ENBW=o.ENBW, ibounds=np.asarray(o.ibounds))
+    np.savez_compressed(os.path.join(OUT, "stft_c3.npz"), **d)
+    # two-signal class path up to Pstft (averagewins breaks for 1-D sigy)
+    t, ch = t[:2 ** 14], ch[:, :2 ** 14]
+    o = fa.fftanal(t, ch[0], ch[1], tper=tper, windowoverlap=0.5, verbose=False)
+    o.Xstft(); o.Ystft(); o.Pstft()
+    np.savez_compressed(os.path.join(OUT, "stft_xy.npz"), **_pack_t(t), in_x=ch[0], in_y=ch[1],
+                        tper=tper, Xseg=o.Xseg, Yseg=o.Yseg, Pxy_seg=o.Pxy_seg,
+                        Pxx_seg=o.Pxx_seg, Pyy_seg=o.Pyy_seg, Cxy_seg=o.Cxy_seg,
+                        phixy_seg=o.phixy_seg, tseg=o.tseg, freq=o.freq, Navr=o.Navr,
+                        nwins=o.nwins, noverlap=o.noverlap)
+
+    # ---- specgram ---------------------------------------------------------- #
+    stdout, sys.stdout = sys.stdout, open(os.devnull, "w")
+    try:
+        tm, f, S = SP.specgram(t, ch[0], wl=512)
+        tm2, f2, S2 = SP.specgram(t[:10000], ch[1][:10000], wl=256, hanning=False)
+    finally:
+        sys.stdout = stdout
+    np.savez_compressed(os.path.join(OUT, "specgram.npz"), **_pack_t(t), in_s=ch[0], time=tm,
+                        freq=f, S=S, in_s2=ch[1][:10000], time2=tm2, freq2=f2, S2=S2)
+
+    # ---- hilbert ----------------------------------------------------------- #
+    d = {}
+    for n in (32, 33, 1024, 1000, 4096):
+        u = np.sin(2 * np.pi * 3 * np.arange(n) / n) + 0.3 * rng.standard_normal(n)
+        d["u_%d" % n] = u
+        d["z_%d" % n] = H.hilbert(u)
+        d["z1d_%d" % n] = H.hilbert_1d(u)
+    u2 = rng.standard_normal((4, 512))
+    d["u_batch"] = u2
+    d["z_batch"] = H.hilbert(u2)
+    np.savez_compressed(os.path.join(OUT, "hilbert.npz"), **d)
+    print("golden fixtures in", OUT)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,14 @@
+"""pyfft_b200 -- B200-native (sm_100a) accelerator for PYFFT's segmented spectral
+estimation hot path.
+
+Public names follow the reference package (FFT/__init__.py:20-31): ``fft_pwelch``,
+``fftanal``, ``detrend_none/mean/linear``, ``stft``, ``specgram``, plus ``windows``,
+``hilbert`` and ``ccf``.  Importing this package loads libpyfft_b200.so; it raises if
+the CUDA extension has not been built (there is no CPU fallback).
+"""
+from . import _lib                      # noqa: F401  (fails loudly when the .so is missing)
+from .windows import windows            # noqa: F401
+from .fft_analysis import (fft_pwelch, fftanal, fftinfosc, Cxy_Cxy2, detrend_none,  # noqa: F401
+                           detrend_mean, detrend_linear)
+
+__version__ = "0.1.0"

@@ -1,0 +1,492 @@
+// K0 (detrend statistics), K1 (fused Welch auto/cross accumulation), the
+// partial-sum reduction, the finalize kernel and the correlation epilogue.
+//
+// Reference lines replaced: fft_analysis.py:353-393 (detrend, segment loop,
+// window, FFT, products), :402-446 (side selection, scaling, mean),
+// :1662-1680 (coherence), :520 (phase), :544-597 (correlations).
+#include "common.cuh"
+
+namespace pyfft {
+
+// ------------------------------------------------------------------------- //
+// K0: per-channel sum x(j) and sum j*x(j) over analysed indices
+// ------------------------------------------------------------------------- //
+template <typename T>
+__global__ void __launch_bounds__(256) detrend_stats_kernel(const T* __restrict__ ptr, int64_t ch_stride,
+                                                            RecMap map, int64_t j_begin, int64_t j_end,
+                                                            double* __restrict__ stats) {
+    const int c = blockIdx.y;
+    const T* p = ptr + (int64_t)c * ch_stride;
+    double s0 = 0.0, s1 = 0.0;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t j = j_begin + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < j_end; j += stride) {
+        const double v = (double)p[src_index(map, j)];
+        s0 += v;
+        s1 += v * (double)j;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        s0 += __shfl_xor_sync(0xffffffffu, s0, o);
+        s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+    }
+    __shared__ double sh[2][8];
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    if (l == 0) { sh[0][w] = s0; sh[1][w] = s1; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double a = 0.0, b = 0.0;
+        for (int i = 0; i < 8; ++i) { a += sh[0][i]; b += sh[1][i]; }
+        atomicAdd(&stats[2 * c + 0], a);
+        atomicAdd(&stats[2 * c + 1], b);
+    }
+}
+
+__global__ void detrend_coef_kernel(int mode, const double* __restrict__ stats, int nch, int64_t nsig,
+                                    double* __restrict__ coef) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= nch) return;
+    const double n = (double)nsig;
+    const double mean = stats[2 * c] / n;
+    double a = 0.0, b = 0.0;
+    if (mode == PYFFT_DETREND_MEAN) {
+        a = mean;
+    } else if (mode == PYFFT_DETREND_LINEAR) {
+        // t_j = j - (n-1)/2 ; slope = sum t_j (x_j - mean) / sum t_j^2 ; sum t_j = 0
+        const double tc = 0.5 * (n - 1.0);
+        const double num = stats[2 * c + 1] - tc * stats[2 * c];
+        const double den = n * (n * n - 1.0) / 12.0;
+        b = den > 0.0 ? num / den : 0.0;
+        a = mean - b * tc;
+    }
+    coef[2 * c] = a;
+    coef[2 * c + 1] = b;
+}
+
+// ------------------------------------------------------------------------- //
+// K1: fused gather -> detrend -> window -> FFT(u + i v) -> split -> accumulate
+// ------------------------------------------------------------------------- //
+template <typename T> struct WelchParams {
+    const T* x;
+    const T* y;
+    int64_t y_stride;
+    RecMap map;
+    int64_t hop, seg_first, seg_count, chunk;
+    const T* window;
+    const double* coef_x;
+    const double* coef_y;
+    const cpx<T>* tw;
+    T* partial;     // [nch][nparts][4][L/2+1]
+    int nparts;
+};
+
+template <int LOG2L> struct WelchGeom {
+    static constexpr int L = 1 << LOG2L;
+    static constexpr int TPS = L / 16;
+    static constexpr int THREADS = TPS > 256 ? TPS : 256;
+    static constexpr int SLOTS = THREADS / TPS;
+    static constexpr int NBIN = L / 2 + 1;
+    static constexpr int E = smem_elems(L);
+};
+
+template <typename T, int LOG2L, bool SINGLE>
+constexpr size_t welch_smem_bytes() {
+    return (size_t)(SINGLE ? 1 : 2) * WelchGeom<LOG2L>::SLOTS * WelchGeom<LOG2L>::E * sizeof(cpx<T>) +
+           (size_t)WelchGeom<LOG2L>::L * sizeof(T);
+}
+
+template <typename T, int LOG2L, bool SINGLE>
+__global__ void __launch_bounds__(WelchGeom<LOG2L>::THREADS,
+                                  (sizeof(T) == 4 && WelchGeom<LOG2L>::THREADS == 256) ? 2 : 1)
+welch_pair_kernel(const WelchParams<T> p) {
+    using G = WelchGeom<LOG2L>;
+    constexpr int L = G::L, TPS = G::TPS, SLOTS = G::SLOTS, NBIN = G::NBIN, E = G::E;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    cpx<T>* sm = reinterpret_cast<cpx<T>*>(smem_raw);
+    T* swin = reinterpret_cast<T*>(sm + (size_t)(SINGLE ? 1 : 2) * SLOTS * E);
+    for (int i = threadIdx.x; i < L; i += G::THREADS) swin[i] = p.window[i];
+    __syncthreads();
+
+    const int slot = threadIdx.x / TPS;
+    const int t = threadIdx.x - slot * TPS;
+    const int pair = blockIdx.y;
+    const int part = blockIdx.x * SLOTS + slot;
+    const int64_t k0 = (int64_t)part * p.chunk;
+    const int64_t k1 = (k0 + p.chunk < p.seg_count) ? k0 + p.chunk : p.seg_count;
+    const T* __restrict__ u = p.x;
+    const T* __restrict__ w = p.y + (int64_t)pair * p.y_stride;
+    const double ax = p.coef_x ? p.coef_x[0] : 0.0, bx = p.coef_x ? p.coef_x[1] : 0.0;
+    const double ay = p.coef_y ? p.coef_y[2 * pair] : 0.0, by = p.coef_y ? p.coef_y[2 * pair + 1] : 0.0;
+    const T bxf = (T)bx, byf = (T)by;
+
+    Exchange<T, SINGLE> ex;
+    ex.b[0] = sm + (size_t)slot * E;
+    ex.b[1] = SINGLE ? ex.b[0] : sm + (size_t)(SLOTS + slot) * E;
+    ex.cur = 0;
+
+    T acc[8][4];
+    T nyq[4] = {T(0), T(0), T(0), T(0)};
+#pragma unroll
+    for (int s = 0; s < 8; ++s)
+#pragma unroll
+        for (int q = 0; q < 4; ++q) acc[s][q] = T(0);
+
+    for (int64_t it = 0; it < p.chunk; ++it) {       // same trip count for every slot (barriers inside)
+        const int64_t k = k0 + it;
+        const bool active = k < k1;
+        cpx<T> v[16];
+        if (active) {
+            const int64_t j0 = (p.seg_first + k) * p.hop;
+            const T cx0 = (T)(ax + bx * (double)j0), cy0 = (T)(ay + by * (double)j0);
+#pragma unroll
+            for (int s = 0; s < 16; ++s) {
+                const int n = t + TPS * s;
+                const int64_t e = src_index(p.map, j0 + n);
+                const T wv = swin[n];
+                const T xv = u[e] - (cx0 + bxf * (T)n);
+                const T yv = w[e] - (cy0 + byf * (T)n);
+                v[s] = mk<T>(xv * wv, yv * wv);
+            }
+        } else {
+#pragma unroll
+            for (int s = 0; s < 16; ++s) v[s] = mk<T>(T(0), T(0));
+        }
+        fft_block<T, LOG2L, false, SINGLE>(v, ex, p.tw, t);
+
+        // exchange the spectrum so that every thread can fetch Z[L-f] for its bins
+        ex.before_write();
+        cpx<T>* e = ex.buf();
+#pragma unroll
+        for (int s = 0; s < 16; ++s) e[phys(t + TPS * s)] = v[s];
+        __syncthreads();
+        ex.flip();
+        if (active) {
+#pragma unroll
+            for (int s = 0; s < 8; ++s) {
+                const int f = t + TPS * s;
+                const cpx<T> A = v[s];
+                const cpx<T> B = e[phys((L - f) & (L - 1))];
+                // U = (A + conj B)/2, V = (A - conj B)/(2i); the factors 1/2 are applied at the end
+                const T ur = A.x + B.x, ui = A.y - B.y, vr = A.y + B.y, vi = B.x - A.x;
+                acc[s][0] += ur * ur + ui * ui;
+                acc[s][1] += vr * vr + vi * vi;
+                acc[s][2] += vr * ur + vi * ui;      // Re V conj(U)   (fft_analysis.py:393: Y conj(X))
+                acc[s][3] += vi * ur - vr * ui;      // Im V conj(U)
+            }
+            if (t == 0) {                             // Nyquist bin f = L/2 = slot 8 of thread 0; self-paired
+                const T ur = v[8].x + v[8].x, vr = v[8].y + v[8].y;
+                nyq[0] += ur * ur;
+                nyq[1] += vr * vr;
+                nyq[2] += vr * ur;
+            }
+        }
+    }
+
+    T* out = p.partial + ((size_t)pair * p.nparts + part) * 4 * NBIN;
+#pragma unroll
+    for (int s = 0; s < 8; ++s)
+#pragma unroll
+        for (int q = 0; q < 4; ++q) out[q * NBIN + t + TPS * s] = T(0.25) * acc[s][q];
+    if (t == 0) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) out[q * NBIN + L / 2] = T(0.25) * nyq[q];
+    }
+}
+
+// acc[pair][q][f] += sum_part partial[pair][part][q][f]
+template <typename T>
+__global__ void __launch_bounds__(256) welch_reduce_kernel(const T* __restrict__ partial, int nparts,
+                                                           int per_pair, double* __restrict__ acc) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int pair = blockIdx.y;
+    if (i >= per_pair) return;
+    const T* p = partial + (size_t)pair * nparts * per_pair + i;
+    double s = 0.0;
+    for (int k = 0; k < nparts; ++k) s += (double)p[(size_t)k * per_pair];
+    acc[(size_t)pair * per_pair + i] += s;
+}
+
+// ------------------------------------------------------------------------- //
+// finalize
+// ------------------------------------------------------------------------- //
+__global__ void __launch_bounds__(256) welch_finalize_kernel(const double* __restrict__ acc, int nfft, int nch,
+                                                             double scale_over_k, int onesided, int F,
+                                                             double* __restrict__ Pxx, double* __restrict__ Pyy,
+                                                             double* __restrict__ Pxy, double* __restrict__ Cxy,
+                                                             double* __restrict__ Cxy2, double* __restrict__ phi) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= F * nch) return;
+    const int o = idx / nch, c = idx - o * nch;     // output bin, channel
+    const int nbin = nfft / 2 + 1;
+    int f;                 // source bin in [0, nfft/2]
+    bool conj = false;
+    double wgt = 1.0;
+    if (onesided) {
+        f = o;
+        // x2 on bins 1..F-2 only (fft_analysis.py:414-416); nfft is even here so the last bin stays x1
+        if (o >= 1 && o <= F - 2) wgt = 2.0;
+    } else {
+        // fftshift order: output o <-> frequency index (o + nfft/2) mod nfft  (fft_analysis.py:423-427)
+        const int k = (o + nfft - nfft / 2) % nfft;     // numpy fftshift: shift by nfft//2
+        if (k <= nfft / 2) f = k; else { f = nfft - k; conj = true; }
+    }
+    const double* a = acc + (size_t)c * 4 * nbin;
+    const double s = scale_over_k * wgt;
+    const double pxx = a[0 * nbin + f] * s, pyy = a[1 * nbin + f] * s;
+    const double pr = a[2 * nbin + f] * s, pi = (conj ? -a[3 * nbin + f] : a[3 * nbin + f]) * s;
+    if (Pxx && c == 0) { Pxx[2 * o] = pxx; Pxx[2 * o + 1] = 0.0; }
+    if (Pyy) { Pyy[2 * idx] = pyy; Pyy[2 * idx + 1] = 0.0; }
+    if (Pxy) { Pxy[2 * idx] = pr; Pxy[2 * idx + 1] = pi; }
+    const double den = fabs(pxx) * fabs(pyy);                 // fft_analysis.py:1672, 1677
+    if (Cxy) { const double r = 1.0 / sqrt(den); Cxy[2 * idx] = pr * r; Cxy[2 * idx + 1] = pi * r; }
+    if (Cxy2) { Cxy2[2 * idx] = (pr * pr + pi * pi) / den; Cxy2[2 * idx + 1] = 0.0 / den; }
+    if (phi) phi[idx] = atan2(pi, pr);                        // fft_analysis.py:520
+}
+
+// ------------------------------------------------------------------------- //
+// K3a: correlation epilogue -- one CTA per column, double precision
+// ------------------------------------------------------------------------- //
+template <int LOG2L>
+__global__ void __launch_bounds__(WelchGeom<LOG2L>::TPS)
+welch_correlation_kernel(const double* __restrict__ spec, int ncol, int onesided, int halve,
+                         const cpx<double>* __restrict__ tw, double* __restrict__ out) {
+    // launched with exactly TPS = L/16 threads: every thread carries 16 points
+    constexpr int L = 1 << LOG2L, TPS = L / 16;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    cpx<double>* sm = reinterpret_cast<cpx<double>*>(smem_raw);
+    const int col = blockIdx.x;
+    const int t = threadIdx.x;
+    const int F = onesided ? L / 2 : L;
+    Exchange<double, true> ex;
+    ex.b[0] = ex.b[1] = sm;
+    ex.cur = 0;
+    cpx<double> v[16];
+#pragma unroll
+    for (int s = 0; s < 16; ++s) {
+        const int k = t + TPS * s;                 // frequency index 0..L-1
+        cpx<double> z = mk<double>(0.0, 0.0);
+        if (onesided) {
+            // numpy irfft(q, n=L): q has L/2 bins, the Nyquist bin is absent (= 0) and the
+            // imaginary part of q[0] is ignored; negative frequencies by Hermitian symmetry
+            const int f = k <= L / 2 ? k : L - k;
+            if (f < F) {
+                z.x = spec[2 * ((size_t)f * ncol + col)];
+                z.y = spec[2 * ((size_t)f * ncol + col) + 1];
+                if (k > L / 2) z.y = -z.y;
+                if (f == 0) z.y = 0.0;
+                if (halve && f >= 1 && f <= F - 2) { z.x *= 0.5; z.y *= 0.5; }
+            }
+        } else {
+            // ifft(ifftshift(P)): frequency index k sits at input position (k + L/2) mod L
+            const int o = (k + L / 2) % L;
+            z.x = spec[2 * ((size_t)o * ncol + col)];
+            z.y = spec[2 * ((size_t)o * ncol + col) + 1];
+        }
+        v[s] = z;
+    }
+    fft_block<double, LOG2L, true, true>(v, ex, tw, t);
+    const double sc = sqrt((double)L) / (double)L;     // sqrt(nfft) * (1/nfft of the inverse)
+#pragma unroll
+    for (int s = 0; s < 16; ++s) {
+        const int n = t + TPS * s;                     // lag index before fftshift
+        const int o = (n + L / 2) % L;                 // fftshift (fft_analysis.py:592-595)
+        if (onesided) {
+            out[(size_t)o * ncol + col] = v[s].x * sc;
+        } else {
+            out[2 * ((size_t)o * ncol + col)] = v[s].x * sc;
+            out[2 * ((size_t)o * ncol + col) + 1] = v[s].y * sc;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------- //
+// host side
+// ------------------------------------------------------------------------- //
+static int welch_grid_x(int64_t seg_count, int slots, int nch) {
+    int sms = device_sm_count();
+    if (sms <= 0) sms = 148;
+    int64_t want = ((int64_t)2 * sms + nch - 1) / nch;            // ~2 CTAs per SM over all pairs
+    int64_t maxb = (seg_count + slots - 1) / slots;
+    if (want > maxb) want = maxb;
+    if (want < 1) want = 1;
+    return (int)want;
+}
+
+template <typename T, int LOG2L>
+static int launch_welch(const void* x, const void* y, int64_t y_stride, int nch, const RecMap& map,
+                        const pyfft_segmentation* seg, const void* window, const double* coef_x,
+                        const double* coef_y, double* acc, void* workspace, int64_t workspace_bytes,
+                        cudaStream_t st) {
+    using G = WelchGeom<LOG2L>;
+    constexpr bool SINGLE = welch_smem_bytes<T, LOG2L, false>() > 200 * 1024;
+    constexpr size_t smem = welch_smem_bytes<T, LOG2L, SINGLE>();
+    int status;
+    const cpx<T>* tw = reinterpret_cast<const cpx<T>*>(
+        twiddle_table(sizeof(T) == 8 ? PYFFT_F64 : PYFFT_F32, G::L, &status));
+    if (!tw) return status;
+    const int gx = welch_grid_x(seg->seg_count, G::SLOTS, nch);
+    const int nparts = gx * G::SLOTS;
+    const int64_t need = (int64_t)nch * nparts * 4 * G::NBIN * (int64_t)sizeof(T);
+    if (workspace_bytes < need || !workspace)
+        return fail(PYFFT_EINVAL, "workspace too small: %lld < %lld bytes", (long long)workspace_bytes,
+                    (long long)need);
+    WelchParams<T> p;
+    p.x = static_cast<const T*>(x);
+    p.y = static_cast<const T*>(y);
+    p.y_stride = y_stride;
+    p.map = map;
+    p.hop = seg->hop;
+    p.seg_first = seg->seg_first;
+    p.seg_count = seg->seg_count;
+    p.chunk = (seg->seg_count + nparts - 1) / nparts;
+    p.window = static_cast<const T*>(window);
+    p.coef_x = coef_x;
+    p.coef_y = coef_y;
+    p.tw = tw;
+    p.partial = static_cast<T*>(workspace);
+    p.nparts = nparts;
+    auto kern = welch_pair_kernel<T, LOG2L, SINGLE>;
+    PYFFT_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<dim3(gx, nch), G::THREADS, smem, st>>>(p);
+    PYFFT_LAUNCH_OK("welch_pair_kernel");
+    const int per_pair = 4 * G::NBIN;
+    welch_reduce_kernel<T><<<dim3((per_pair + 255) / 256, nch), 256, 0, st>>>(p.partial, nparts, per_pair, acc);
+    PYFFT_LAUNCH_OK("welch_reduce_kernel");
+    return PYFFT_OK;
+}
+
+template <typename T>
+static int dispatch_welch(int log2l, const void* x, const void* y, int64_t y_stride, int nch,
+                          const RecMap& map, const pyfft_segmentation* seg, const void* window,
+                          const double* coef_x, const double* coef_y, double* acc, void* ws,
+                          int64_t wsb, cudaStream_t st) {
+#define PYFFT_CASE(N) \
+    case N: return launch_welch<T, N>(x, y, y_stride, nch, map, seg, window, coef_x, coef_y, acc, ws, wsb, st);
+    switch (log2l) {
+        PYFFT_CASE(4) PYFFT_CASE(5) PYFFT_CASE(6) PYFFT_CASE(7) PYFFT_CASE(8)
+        PYFFT_CASE(9) PYFFT_CASE(10) PYFFT_CASE(11) PYFFT_CASE(12) PYFFT_CASE(13)
+    }
+#undef PYFFT_CASE
+    return fail(PYFFT_EUNSUPPORTED, "nfft = 2^%d not supported", log2l);
+}
+
+}  // namespace pyfft
+
+using namespace pyfft;
+
+extern "C" {
+
+int pyfft_detrend_stats(int dtype, const void* ptr, int64_t ch_stride, int32_t nch,
+                        const pyfft_record_map* map, int64_t j_begin, int64_t j_end,
+                        double* stats, void* stream) {
+    RecMap m;
+    int rc = check_map(map, &m);
+    if (rc) return rc;
+    if (!ptr || !stats || nch <= 0) return fail(PYFFT_EINVAL, "detrend_stats: NULL pointer or nch <= 0");
+    if ((rc = check_range(m, j_begin, j_end))) return rc;
+    if (j_begin == j_end) return PYFFT_OK;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    int sms = device_sm_count();
+    if (sms <= 0) sms = 148;
+    int64_t blocks = (j_end - j_begin + 256 * 8 - 1) / (256 * 8);
+    int64_t cap = ((int64_t)sms * 8 + nch - 1) / nch;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    dim3 grid((unsigned)blocks, (unsigned)nch);
+    if (dtype == PYFFT_F32)
+        detrend_stats_kernel<float><<<grid, 256, 0, st>>>(static_cast<const float*>(ptr), ch_stride, m, j_begin, j_end, stats);
+    else if (dtype == PYFFT_F64)
+        detrend_stats_kernel<double><<<grid, 256, 0, st>>>(static_cast<const double*>(ptr), ch_stride, m, j_begin, j_end, stats);
+    else
+        return fail(PYFFT_EINVAL, "unknown dtype %d", dtype);
+    PYFFT_LAUNCH_OK("detrend_stats_kernel");
+    return PYFFT_OK;
+}
+
+int pyfft_detrend_coef(int mode, const double* stats, int32_t nch, int64_t nsig, double* coef, void* stream) {
+    if (!stats || !coef || nch <= 0 || nsig <= 0) return fail(PYFFT_EINVAL, "detrend_coef: bad arguments");
+    if (mode < PYFFT_DETREND_NONE || mode > PYFFT_DETREND_LINEAR)
+        return fail(PYFFT_EINVAL, "unknown detrend mode %d", mode);
+    detrend_coef_kernel<<<(nch + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(mode, stats, nch, nsig, coef);
+    PYFFT_LAUNCH_OK("detrend_coef_kernel");
+    return PYFFT_OK;
+}
+
+int64_t pyfft_welch_workspace_bytes(int dtype, const pyfft_segmentation* seg, int32_t nch) {
+    int log2l;
+    int rc = check_seg(seg, 4, 13, &log2l);
+    if (rc) return rc;
+    if (nch <= 0) return fail(PYFFT_EINVAL, "nch must be positive");
+    const int L = 1 << log2l;
+    const int tps = L / 16;
+    const int threads = tps > 256 ? tps : 256;
+    const int slots = threads / tps;
+    const int gx = welch_grid_x(seg->seg_count, slots, nch);
+    const int64_t esz = dtype == PYFFT_F64 ? 8 : 4;
+    int64_t b = (int64_t)nch * gx * slots * 4 * (L / 2 + 1) * esz;
+    return b > 0 ? b : 16;
+}
+
+int pyfft_welch_accumulate(int dtype, const void* x, const void* y, int64_t y_stride, int32_t nch,
+                           const pyfft_record_map* map, const pyfft_segmentation* seg,
+                           const void* window, const double* coef_x, const double* coef_y,
+                           double* acc, void* workspace, int64_t workspace_bytes, void* stream) {
+    RecMap m;
+    int rc = check_map(map, &m);
+    if (rc) return rc;
+    int log2l;
+    if ((rc = check_seg(seg, 4, 13, &log2l))) return rc;
+    if (!x || !y || !window || !acc || nch <= 0) return fail(PYFFT_EINVAL, "welch_accumulate: NULL pointer or nch <= 0");
+    if (seg->seg_count == 0) return PYFFT_OK;
+    const int64_t j_lo = seg->seg_first * (int64_t)seg->hop;
+    const int64_t j_hi = (seg->seg_first + seg->seg_count - 1) * (int64_t)seg->hop + seg->nfft;
+    if ((rc = check_range(m, j_lo, j_hi))) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (dtype == PYFFT_F32)
+        return dispatch_welch<float>(log2l, x, y, y_stride, nch, m, seg, window, coef_x, coef_y, acc, workspace, workspace_bytes, st);
+    if (dtype == PYFFT_F64)
+        return dispatch_welch<double>(log2l, x, y, y_stride, nch, m, seg, window, coef_x, coef_y, acc, workspace, workspace_bytes, st);
+    return fail(PYFFT_EINVAL, "unknown dtype %d", dtype);
+}
+
+int pyfft_welch_finalize(const double* acc, int32_t nfft, int32_t nch, int64_t K, double scale,
+                         int32_t onesided, double* Pxx, double* Pyy, double* Pxy, double* Cxy,
+                         double* Cxy2, double* phi, void* stream) {
+    if (!acc || nfft < 2 || (nfft & 1) || nch <= 0 || K <= 0)
+        return fail(PYFFT_EINVAL, "welch_finalize: bad arguments (even nfft, nch > 0, K > 0 required)");
+    const int F = onesided ? nfft / 2 : nfft;
+    const int total = F * nch;
+    welch_finalize_kernel<<<(total + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        acc, nfft, nch, scale / (double)K, onesided, F, Pxx, Pyy, Pxy, Cxy, Cxy2, phi);
+    PYFFT_LAUNCH_OK("welch_finalize_kernel");
+    return PYFFT_OK;
+}
+
+int pyfft_welch_correlation(const double* spec, int32_t nfft, int32_t ncol, int32_t onesided,
+                            int32_t halve_interior, double* out, void* stream) {
+    if (!spec || !out || ncol <= 0) return fail(PYFFT_EINVAL, "welch_correlation: bad arguments");
+    pyfft_segmentation seg = {nfft, 1, 0, 1};
+    int log2l;
+    int rc = check_seg(&seg, 4, 13, &log2l);
+    if (rc) return rc;
+    int status;
+    const cpx<double>* tw = reinterpret_cast<const cpx<double>*>(twiddle_table(PYFFT_F64, nfft, &status));
+    if (!tw) return status;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const size_t smem = (size_t)smem_elems(nfft) * sizeof(cpx<double>);
+#define PYFFT_CASE(N)                                                                                   \
+    case N: {                                                                                           \
+        auto kern = welch_correlation_kernel<N>;                                                        \
+        PYFFT_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+        kern<<<ncol, (1 << N) / 16, smem, st>>>(spec, ncol, onesided, halve_interior, tw, out);         \
+        break;                                                                                          \
+    }
+    switch (log2l) {
+        PYFFT_CASE(4) PYFFT_CASE(5) PYFFT_CASE(6) PYFFT_CASE(7) PYFFT_CASE(8)
+        PYFFT_CASE(9) PYFFT_CASE(10) PYFFT_CASE(11) PYFFT_CASE(12) PYFFT_CASE(13)
+    }
+#undef PYFFT_CASE
+    PYFFT_LAUNCH_OK("welch_correlation_kernel");
+    return PYFFT_OK;
+}
+
+}  // extern "C"

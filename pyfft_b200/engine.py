@@ -1,0 +1,177 @@
+"""Device-side plumbing between the drop-in Python API and the C ABI.
+
+torch is used for device memory, streams and torch.distributed only; every O(N)
+computation goes through libpyfft_b200.so.  All methods are asynchronous on the
+current torch CUDA stream; nothing here synchronises except explicit ``.cpu()``
+conversions done by the callers.
+"""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import RecordMap, Segmentation, check, lib
+
+_TORCH_REAL = {"fp32": torch.float32, "fp64": torch.float64}
+_TORCH_CPLX = {"fp32": torch.complex64, "fp64": torch.complex128}
+_CODE = {"fp32": _lib.F32, "fp64": _lib.F64}
+
+
+def require_cuda(device=None):
+    if not torch.cuda.is_available():
+        raise RuntimeError("pyfft_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+    if device is None:
+        return torch.device("cuda", torch.cuda.current_device())
+    return torch.device(device)
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+
+def resolve_precision(precision, *arrays):
+    """'fp32' | 'fp64' | None.  None: float32 inputs -> fp32, anything else -> fp64 (the
+    reference computes in float64 throughout)."""
+    if precision is not None:
+        p = str(precision).lower()
+        p = {"float32": "fp32", "single": "fp32", "f32": "fp32", "float64": "fp64",
+             "double": "fp64", "f64": "fp64"}.get(p, p)
+        if p not in ("fp32", "fp64"):
+            raise ValueError("precision must be 'fp32' or 'fp64', got %r" % (precision,))
+        return p
+    for a in arrays:
+        dt = a.dtype
+        if dt in (np.float32, torch.float32, np.complex64, torch.complex64):
+            continue
+        return "fp64"
+    return "fp32"
+
+
+def to_device(a, precision, device, complex_ok=False):
+    """numpy array / torch tensor -> contiguous-on-demand device tensor of the compute dtype."""
+    if isinstance(a, torch.Tensor):
+        t = a
+    else:
+        a = np.asarray(a)
+        t = torch.from_numpy(a if a.flags.writeable else a.copy())
+    if t.is_complex():
+        if not complex_ok:
+            raise ValueError("complex input not supported on this path")
+        want = _TORCH_CPLX[precision]
+    else:
+        want = _TORCH_REAL[precision]
+    return t.to(device=device, dtype=want, non_blocking=True)
+
+
+def channels_first(y, n):
+    """(n,), (n, C) or (C, n) device tensor -> contiguous (C, n).  Mirrors the reference's
+    orientation rule: a 2-D sigy whose second axis has the record length is transposed
+    (fft_analysis.py:163-167)."""
+    if y.dim() == 1:
+        y = y[None, :]
+    elif y.shape[1] != n:
+        y = y.t()            # (n, C) time-major, the reference's native layout
+    return y.contiguous()
+
+
+class WelchPlan(object):
+    """Streaming Welch accumulator for one x channel against nch y channels.
+
+    Mirrors the structure SURVEY.md section 5 asks for: partial sums plus a segment
+    count, so long records can be fed shard by shard (or rank by rank) and
+    finalised once.
+    """
+
+    def __init__(self, nfft, hop, nch, precision, window, device=None):
+        self.device = require_cuda(device)
+        self.nfft, self.hop, self.nch = int(nfft), int(hop), int(nch)
+        self.precision = precision
+        self.code = _CODE[precision]
+        self.nbin = self.nfft // 2 + 1
+        win = np.ascontiguousarray(np.asarray(window, dtype=np.float64))
+        if win.shape != (self.nfft,):
+            raise ValueError("window must have nfft = %d points" % self.nfft)
+        self.window = torch.from_numpy(win).to(self.device, _TORCH_REAL[precision])
+        self.acc = torch.zeros((self.nch, 4, self.nbin), dtype=torch.float64, device=self.device)
+        self.stats = torch.zeros(2 * (self.nch + 1), dtype=torch.float64, device=self.device)
+        self.coef = None
+        self.K = 0
+        self._ws = None
+
+    # -- detrend ------------------------------------------------------------ #
+    def detrend_stats(self, x, y, rmap, j_begin, j_end):
+        """Adds sum x(j), sum j x(j) for j in [j_begin, j_end) (x first, then the y channels)."""
+        check(lib.pyfft_detrend_stats(self.code, _ptr(x), 0, 1, C.byref(rmap), j_begin, j_end,
+                                      _ptr(self.stats), _stream()))
+        check(lib.pyfft_detrend_stats(self.code, _ptr(y), y.stride(0), self.nch, C.byref(rmap),
+                                      j_begin, j_end, C.c_void_p(self.stats.data_ptr() + 16),
+                                      _stream()))
+
+    def solve_detrend(self, mode, nsig, group=None):
+        if mode == _lib.DETREND_NONE:
+            self.coef = None
+            return
+        if group is not None:
+            torch.distributed.all_reduce(self.stats, group=group)
+        self.coef = torch.empty_like(self.stats)
+        check(lib.pyfft_detrend_coef(mode, _ptr(self.stats), self.nch + 1, nsig, _ptr(self.coef),
+                                     _stream()))
+
+    # -- accumulate --------------------------------------------------------- #
+    def accumulate(self, x, y, rmap, seg_first, seg_count):
+        seg = Segmentation(self.nfft, self.hop, seg_first, seg_count)
+        need = check(lib.pyfft_welch_workspace_bytes(self.code, C.byref(seg), self.nch))
+        if self._ws is None or self._ws.numel() < need:
+            self._ws = torch.empty(need, dtype=torch.uint8, device=self.device)
+        cx = C.c_void_p(self.coef.data_ptr()) if self.coef is not None else C.c_void_p(0)
+        cy = C.c_void_p(self.coef.data_ptr() + 16) if self.coef is not None else C.c_void_p(0)
+        check(lib.pyfft_welch_accumulate(self.code, _ptr(x), _ptr(y), y.stride(0), self.nch,
+                                         C.byref(rmap), C.byref(seg), _ptr(self.window), cx, cy,
+                                         _ptr(self.acc), _ptr(self._ws), self._ws.numel(), _stream()))
+        self.K += int(seg_count)
+
+    def all_reduce(self, group=None):
+        """One collective over the packed partial sums."""
+        torch.distributed.all_reduce(self.acc, group=group)
+        k = torch.tensor([self.K], dtype=torch.int64, device=self.device)
+        torch.distributed.all_reduce(k, group=group)
+        self.K = int(k.item())
+
+    # -- finalize ----------------------------------------------------------- #
+    def finalize(self, scale, onesided=True, K=None):
+        """-> dict of device tensors Pxx (F,), Pyy/Pxy/Cxy/Cxy2 (F, nch) complex128, phi (F, nch)."""
+        K = self.K if K is None else int(K)
+        F = self.nfft // 2 if onesided else self.nfft
+        dev = self.device
+        out = dict(Pxx=torch.empty(F, dtype=torch.complex128, device=dev),
+                   Pyy=torch.empty((F, self.nch), dtype=torch.complex128, device=dev),
+                   Pxy=torch.empty((F, self.nch), dtype=torch.complex128, device=dev),
+                   Cxy=torch.empty((F, self.nch), dtype=torch.complex128, device=dev),
+                   Cxy2=torch.empty((F, self.nch), dtype=torch.complex128, device=dev),
+                   phi_xy=torch.empty((F, self.nch), dtype=torch.float64, device=dev))
+        check(lib.pyfft_welch_finalize(_ptr(self.acc), self.nfft, self.nch, K, float(scale),
+                                       1 if onesided else 0, _ptr(out["Pxx"]), _ptr(out["Pyy"]),
+                                       _ptr(out["Pxy"]), _ptr(out["Cxy"]), _ptr(out["Cxy2"]),
+                                       _ptr(out["phi_xy"]), _stream()))
+        return out
+
+    def correlation(self, spec, onesided=True, halve_interior=True):
+        """sqrt(nfft) * irfft / ifft(ifftshift) of a (F,) or (F, ncol) complex128 device tensor,
+        fftshift-ed along axis 0 (fft_analysis.py:544-595)."""
+        ncol = 1 if spec.dim() == 1 else spec.shape[1]
+        shape = (self.nfft,) if spec.dim() == 1 else (self.nfft, ncol)
+        out = torch.empty(shape, dtype=torch.float64 if onesided else torch.complex128,
+                          device=self.device)
+        spec = spec.contiguous()
+        check(lib.pyfft_welch_correlation(_ptr(spec), self.nfft, ncol, 1 if onesided else 0,
+                                          1 if halve_interior else 0, _ptr(out), _stream()))
+        return out
+
+
+def record_map(nsig, i0, reflect, src_base, src_len):
+    return RecordMap(int(nsig), int(i0), int(reflect), int(src_base), int(src_len))

@@ -1,0 +1,528 @@
+"""Drop-in ``fft_pwelch`` / ``fftanal`` on top of the sm_100a kernels.
+
+Same names, positional order, keyword arguments, return tuple and ``fftinfo``
+attributes as the reference's fft_analysis.py (``fft_pwelch`` :36-648,
+``class fftanal`` :1695-2203, ``Cxy_Cxy2`` :1662-1688, ``fftinfosc`` :794-826).
+The host does the O(1)/O(nfft) bookkeeping in float64 exactly like the reference
+(segmentation integers, window, S1/S2/ENBW, variances, amplitude spectra); every
+O(N) step -- detrend statistics, segment gather, window, FFT, products, segment
+means, coherence, correlations -- runs on the GPU through the C ABI
+(include/pyfft_b200.h).  There is no CPU fallback.
+
+Extra, opt-in keyword arguments (defaults keep the reference's behaviour):
+    precision='fp32'|'fp64'   arithmetic on the GPU (default: float32 inputs -> fp32,
+                              anything else -> fp64 like the reference)
+    device=...                CUDA device
+    group=...                 torch.distributed process group: this rank analyses its
+                              share of the segments and the partial sums are combined
+                              with one all-reduce (inputs are the full record on
+                              every rank unless ``shard`` says otherwise)
+    return_device=True        keep the tuple outputs as device tensors
+
+Deliberate differences from the reference (documented in DESIGN.md):
+  * ``useMLAB=True`` (matplotlib.mlab backend) and ``plotit=True`` raise
+    NotImplementedError -- out of scope for the hot path.
+  * the per-segment fields of fftinfo (Pxx_seg, Xfft_seg, ...) are computed lazily
+    on first access instead of being materialised on every call.
+"""
+import numpy as np
+import torch
+
+from . import _lib
+from . import engine as _eng
+from .windows import windows
+
+__all__ = ["fft_pwelch", "fftanal", "fftinfosc", "Cxy_Cxy2", "detrend_none", "detrend_mean",
+           "detrend_linear", "Struct"]
+
+
+class Struct(object):
+    """Attribute bag with the two methods of pybaseutils.Struct the reference uses
+    (fft_analysis.py:22, 1785-1790)."""
+
+    def __init__(self, d=None):
+        if d is not None:
+            if not isinstance(d, dict):
+                d = d.dict_from_class()
+            self.__dict__.update(d)
+
+    def dict_from_class(self):
+        return dict((k, v) for k, v in self.__dict__.items())
+
+
+class fftinfosc(Struct):
+    """Result container of fft_pwelch (fft_analysis.py:794-826): same attribute names."""
+
+    _LAZY = ("Pxx_seg", "Pyy_seg", "Pxy_seg", "Xfft_seg", "Yfft_seg", "phixy_seg", "varphi_seg")
+
+    def __init__(self):
+        f8, c16 = np.float64, np.complex128
+        for name, dt in (("S1", f8), ("S2", f8), ("NENBW", f8), ("ENBW", f8), ("freq", f8),
+                         ("Pxx", c16), ("Pyy", c16), ("Pxy", c16), ("Cxy", c16),
+                         ("varcoh", c16), ("phi_xy", f8), ("varphi", f8), ("Lxx", c16),
+                         ("Lyy", c16), ("Lxy", c16), ("varLxx", c16), ("varLyy", c16),
+                         ("varLxy", c16)):
+            setattr(self, name, np.array([], dtype=dt))
+        self._segment_loader = None
+
+    def __getattr__(self, name):
+        # only reached when normal lookup fails: materialise per-segment spectra on demand
+        if name in fftinfosc._LAZY and self.__dict__.get("_segment_loader") is not None:
+            self.__dict__.update(self.__dict__["_segment_loader"]())
+            self.__dict__["_segment_loader"] = None
+            return self.__dict__[name]
+        raise AttributeError(name)
+
+    def dict_from_class(self):
+        if self.__dict__.get("_segment_loader") is not None:
+            getattr(self, "Pxx_seg")
+        return dict((k, v) for k, v in self.__dict__.items() if not k.startswith("_"))
+
+
+# detrend helpers exported under the reference's names (FFT/__init__.py:21); they are
+# host utilities for callers -- the hot path uses the device statistics kernel.
+def detrend_none(x, axis=None):
+    return x
+
+
+def detrend_mean(x, axis=None):
+    x = np.asarray(x)
+    if axis is None:
+        axis = 0
+    return x - x.mean(axis, keepdims=True)
+
+
+def detrend_linear(x, axis=None):
+    x = np.asarray(x)
+    if axis is None:
+        axis = 0
+    n = x.shape[axis]
+    tt = np.arange(n, dtype=np.float64) - 0.5 * (n - 1)
+    shp = [1] * x.ndim
+    shp[axis] = n
+    tt = tt.reshape(shp)
+    xm = x.mean(axis, keepdims=True)
+    b = (tt * (x - xm)).sum(axis, keepdims=True) / (tt * tt).sum()
+    return x - xm - b * tt
+
+
+def Cxy_Cxy2(Pxx, Pyy, Pxy, ibg=None):
+    """Complex and mean-squared coherence of averaged spectra (fft_analysis.py:1662-1688).
+    O(nfreq) host helper kept for callers; fft_pwelch itself gets both from the finalize
+    kernel."""
+    Pxx = np.atleast_2d(np.array(Pxx))
+    Pyy = np.array(Pyy)
+    Pxy = np.array(Pxy)
+    if np.size(Pxx, axis=1) != np.size(Pyy, axis=1):
+        Pxx = Pxx.T * np.ones((1, np.size(Pyy, axis=1)), dtype=Pxx.dtype)
+    norm = np.abs(Pxx) * np.abs(Pyy)
+    Cxy2 = Pxy * np.conj(Pxy) / norm
+    Cxy = Pxy / np.sqrt(norm)
+    if ibg is None:
+        return Cxy, Cxy2
+    iCxy = np.imag(Cxy) / (1.0 - np.real(Cxy))
+    shifted = np.real(Cxy - np.mean(Cxy[:, ibg], axis=-1))
+    return iCxy, shifted / (1.0 - shifted)
+
+
+# --------------------------------------------------------------------------- #
+# segmentation bookkeeping (host, float64 / Python ints -- verbatim formulas)
+# --------------------------------------------------------------------------- #
+
+def _sample_rate(tvec):
+    return (len(tvec) - 1) / (tvec[-1] - tvec[0])                  # fft_analysis.py:136
+
+
+def _index_bounds(tvec, tbounds, Fs):
+    i0 = int(np.floor(Fs * (tbounds[0] - tvec[0])))                # :143
+    i1 = int(np.floor(1 + Fs * (tbounds[1] - tvec[0])))            # :144
+    return i0, i1
+
+
+class _Plan(object):
+    """Everything fft_pwelch decides before touching the data (fft_analysis.py:102-246)."""
+
+    def __init__(self, tvec, nx, ny, tbounds, Navr, windowoverlap, windowfunction, kwargs):
+        if windowfunction is None:
+            windowfunction = "Hanning"
+        if windowoverlap is None:
+            windowoverlap = windows(windowfunction, verbose=False)
+        if tbounds is None:
+            tbounds = [tvec[0], tvec[-1]]
+        self.windowfunction, self.windowoverlap, self.tbounds = windowfunction, windowoverlap, tbounds
+        ntv = len(tvec)
+        self.Fs = _sample_rate(tvec)
+        self.i0, self.i1 = _index_bounds(tvec, tbounds, self.Fs)
+        nsig = len(range(ntv)[self.i0:self.i1])                    # numpy slice semantics (:149)
+        calc_navr = Navr is None
+        if nx != ny:
+            raise NotImplementedError("different-length sigx/sigy (the reference's nT-model branch, "
+                                      "fft_analysis.py:170-176) is not supported")
+        if "minFreq" in kwargs:
+            kwargs["tper"] = 2.0 / kwargs["minFreq"]               # :180-181
+        if "tper" in kwargs:
+            nwins = int(self.Fs * kwargs["tper"])                  # :182-183
+            if not calc_navr:
+                # the reference leaves `calcNavr` unbound here and dies with NameError (:102, :208)
+                raise NameError("calcNavr")
+        else:
+            if Navr is None:
+                Navr = 8                                           # :185-186
+            calc_navr = False
+            nwins = fftanal._getNwins(nsig, Navr, windowoverlap)   # :189
+        noverlap = fftanal._getNoverlap(nwins, windowoverlap)      # :194
+        self.reflect = (self.i0 == 0 and self.i1 == ntv)           # :197-198
+        if self.reflect:
+            nsig = nx + 2 * (nwins - 1)                            # :202-204
+        if calc_navr:
+            Navr = fftanal._getNavr(nsig, nwins, noverlap)         # :208-209
+        if nwins >= nsig:
+            Navr, nwins = 1, nsig                                  # :214-216
+        self.nwins, self.noverlap, self.Navr = int(nwins), int(noverlap), int(Navr)
+        self.nfft = self.nwins
+        self.Nnyquist = fftanal._getNnyquist(self.nfft)
+        # the analysed record is (reflect-padded sigx)[i0:i1] (:353-354)
+        nsrc = nx + 2 * (int(nwins) - 1) if self.reflect else nx
+        self.nana = len(range(nsrc)[self.i0:self.i1])
+
+
+def _host(t):
+    return t.cpu().numpy()
+
+
+def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
+               windowfunction=None, useMLAB=None, plotit=None, verbose=None,
+               detrend_style=None, onesided=None, **kwargs):
+    """Welch auto-/cross-power spectra, coherence and cross-phase of sigx vs sigy.
+
+    Returns ``(freq, Pxy, Pxx, Pyy, Cxy, phi_xy, fftinfo)`` exactly like the reference
+    (fft_analysis.py:36-648): power spectral densities in [V^2/Hz] as complex128,
+    ``Pxy = <Y conj(X)>`` (:393), one-sided spectra drop the Nyquist bin (:407-416).
+    """
+    precision = kwargs.pop("precision", None)
+    device = kwargs.pop("device", None)
+    group = kwargs.pop("group", None)
+    return_device = kwargs.pop("return_device", False)
+    if useMLAB:
+        raise NotImplementedError("useMLAB=True (matplotlib.mlab backend) is out of scope")
+    if plotit:
+        raise NotImplementedError("plotit=True: plotting is out of scope for the accelerated path; "
+                                  "pass plotit=False")
+    if verbose is None:
+        verbose = False
+    if detrend_style is None:
+        detrend_style = 1                                          # :117-118
+    is_cplx = (sigx.is_complex() if isinstance(sigx, torch.Tensor) else np.iscomplexobj(sigx)) or \
+              (sigy.is_complex() if isinstance(sigy, torch.Tensor) else np.iscomplexobj(sigy))
+    if onesided is None:
+        onesided = not is_cplx                                     # :123-127
+    nx = sigx.shape[0]
+    ntv = len(tvec)
+    if isinstance(sigy, torch.Tensor):
+        ny = sigy.shape[1] if (sigy.dim() == 2 and sigy.shape[1] == ntv) else sigy.shape[0]
+    else:
+        sy = np.shape(sigy)
+        ny = sy[1] if (len(sy) == 2 and sy[1] == ntv) else sy[0]
+    plan = _Plan(tvec, nx, ny, tbounds, Navr, windowoverlap, windowfunction, kwargs)
+    nwins, nfft, K = plan.nwins, plan.nfft, plan.Navr
+    if verbose:
+        print("using the sm_100a kernels for spectra/coherence calculations")
+    win, winparams = windows(plan.windowfunction, nwins=nwins, verbose=verbose, msgout=True,
+                             **({"beta": kwargs["beta"]} if "beta" in kwargs else {}))
+
+    fftinfo = fftinfosc()
+    fftinfo.win = win
+    fftinfo.winparams = winparams
+    fftinfo.windowoverlap = plan.windowoverlap
+    fftinfo.ibnds = [plan.i0, plan.i1]
+    fftinfo.S1, fftinfo.S2, fftinfo.NENBW, fftinfo.ENBW = fftanal._getNorms(win, plan.Nnyquist, plan.Fs)
+
+    if is_cplx:
+        raise NotImplementedError("complex-valued inputs (two-sided spectra of complex data) "
+                                  "are not supported yet")
+    if nfft & (nfft - 1) or nfft < 16 or nfft > 8192:
+        raise NotImplementedError("nwins = %d: the GPU path needs a power-of-two window of 16..8192 "
+                                  "samples (choose Navr/tper accordingly)" % nfft)
+
+    precision = _eng.resolve_precision(precision, sigx, sigy)
+    dev = _eng.require_cuda(device)
+    with torch.cuda.device(dev):
+        x = _eng.to_device(sigx, precision, dev)
+        y = _eng.channels_first(_eng.to_device(sigy, precision, dev), ntv)
+        nch = y.shape[0]
+        if x.dim() != 1:
+            x = x.reshape(-1)
+        x = x.contiguous()
+        refl = nwins - 1 if plan.reflect else 0
+        rmap = _eng.record_map(plan.nana, plan.i0, refl, 0, x.shape[0])
+        hop = nwins - plan.noverlap
+        if hop <= 0:
+            raise ValueError("windowoverlap leaves no hop between segments")
+        if (K - 1) * hop + nwins > plan.nana:
+            # the reference dies here with a broadcasting ValueError (fft_analysis.py:375)
+            raise ValueError("operands could not be broadcast together: segment %d runs past the "
+                             "analysed record (%d samples, nwins=%d, hop=%d)" % (K - 1, plan.nana, nwins, hop))
+        wp = _eng.WelchPlan(nfft, hop, nch, precision, win, dev)
+        mode = _lib.DETREND_MEAN if detrend_style > 0 else (_lib.DETREND_LINEAR if detrend_style < 0
+                                                            else _lib.DETREND_NONE)
+        rank, world = 0, 1
+        if group is not None:
+            rank, world = torch.distributed.get_rank(group), torch.distributed.get_world_size(group)
+        if mode != _lib.DETREND_NONE:
+            # global detrend over the whole analysed record (:356-357): each rank sums its slice
+            j0 = plan.nana * rank // world
+            j1 = plan.nana * (rank + 1) // world
+            wp.detrend_stats(x, y, rmap, j0, j1)
+            wp.solve_detrend(mode, plan.nana, group)
+        k0 = K * rank // world
+        k1 = K * (rank + 1) // world
+        wp.accumulate(x, y, rmap, k0, k1 - k0)
+        if group is not None:
+            wp.all_reduce(group)
+        scale = 1.0 / (fftinfo.S1 ** 2) / fftinfo.ENBW             # :432-440
+        res = wp.finalize(scale, onesided=bool(onesided), K=K)
+        corr = {}
+        for nm, key, halve in (("Rxx", "Pxx", True), ("Ryy", "Pyy", True), ("Rxy", "Pxy", True),
+                               ("iCxy", "Cxy", False)):
+            corr[nm] = wp.correlation(res[key], onesided=bool(onesided), halve_interior=halve)
+
+    freq = np.fft.fftfreq(nfft, 1.0 / plan.Fs)                     # :396
+    freq = freq[:plan.Nnyquist] if onesided else np.fft.fftshift(freq)
+    Pxx, Pyy, Pxy = _host(res["Pxx"]), _host(res["Pyy"]), _host(res["Pxy"])
+    Cxy, Cxy2, phi_xy = _host(res["Cxy"]), _host(res["Cxy2"]), _host(res["phi_xy"])
+
+    # ---- O(nfreq) bookkeeping on the averaged spectra, as in the reference (:496-540) ---- #
+    with np.errstate(all="ignore"):
+        fftinfo.varCxy = ((1.0 - Cxy * np.conjugate(Cxy)) / np.sqrt(2 * K)) ** 2.0
+        fftinfo.varCxy2 = 4.0 * Cxy2 * fftinfo.varCxy
+        fftinfo.varPxx = (Pxx / np.sqrt(K)) ** 2.0
+        fftinfo.varPyy = (Pyy / np.sqrt(K)) ** 2.0
+        fftinfo.varPxy = (Pxy / np.sqrt(K)) ** 2.0
+        fftinfo.varPhxy = (np.sqrt(1.0 - np.abs(Cxy2))) / np.sqrt(2 * K * np.sqrt(np.abs(Cxy2))) ** 2.0
+        for nm, P in (("Lxx", Pxx), ("Lyy", Pyy), ("Lxy", Pxy)):
+            amp = np.sqrt(np.abs(fftinfo.ENBW * P))
+            if onesided:
+                amp[1:-1] = np.sqrt(2) * amp[1:-1]
+                if nfft % 2:
+                    amp[-1] = np.sqrt(2) * amp[-1]
+            setattr(fftinfo, nm, amp)
+        fftinfo.Rxx, fftinfo.Ryy = _host(corr["Rxx"]), _host(corr["Ryy"])
+        fftinfo.Rxy, fftinfo.iCxy = _host(corr["Rxy"]), _host(corr["iCxy"])
+        # zero-lag values sit at index nfft//2 after the fftshift (:585-596)
+        fftinfo.Ex = fftinfo.Rxx[nfft // 2, ...].copy()
+        fftinfo.Ey = fftinfo.Ryy[nfft // 2, ...].copy()
+        fftinfo.corrcoef = fftinfo.Rxy / np.sqrt(
+            np.ones((nfft, 1), dtype=fftinfo.Rxy.dtype) * (fftinfo.Ex * fftinfo.Ey))
+        fftinfo.lags = (np.asarray(range(1, nfft + 1), dtype=int) - plan.Nnyquist) / plan.Fs
+        fftinfo.varLxx = (fftinfo.Lxx ** 2) * (fftinfo.varPxx / np.abs(Pxx) ** 2)
+        fftinfo.varLyy = (fftinfo.Lyy ** 2) * (fftinfo.varPyy / np.abs(Pyy) ** 2)
+        fftinfo.varLxy = (fftinfo.Lxy ** 2) * (fftinfo.varPxy / np.abs(Pxy) ** 2)
+
+    if nch == 1:                                                   # :605-631
+        Pyy, Pxy, Cxy, Cxy2, phi_xy = (a.flatten() for a in (Pyy, Pxy, Cxy, Cxy2, phi_xy))
+        for nm in ("lags", "Rxx", "Ryy", "Rxy", "corrcoef", "iCxy", "Lxx", "Lyy", "Lxy", "varLxx",
+                   "varLyy", "varLxy", "varCxy", "varCxy2", "varPxx", "varPyy", "varPxy", "varPhxy"):
+            setattr(fftinfo, nm, getattr(fftinfo, nm).flatten())
+
+    fftinfo.nch = nch
+    fftinfo.Fs = plan.Fs
+    fftinfo.Navr = K
+    fftinfo.nwins = nwins
+    fftinfo.noverlap = plan.noverlap
+    fftinfo.overlap = plan.windowoverlap
+    fftinfo.window = plan.windowfunction
+    fftinfo.minFreq = 2.0 * plan.Fs / nwins
+    fftinfo.freq = freq.copy()
+    fftinfo.Pxx, fftinfo.Pyy, fftinfo.Pxy = Pxx.copy(), Pyy.copy(), Pxy.copy()
+    fftinfo.Cxy, fftinfo.Cxy2, fftinfo.phi_xy = Cxy.copy(), Cxy2.copy(), phi_xy.copy()
+    fftinfo.precision = precision
+    if return_device:
+        return (torch.from_numpy(freq).to(dev), res["Pxy"], res["Pxx"], res["Pyy"], res["Cxy"],
+                res["phi_xy"], fftinfo)
+    return freq, Pxy, Pxx, Pyy, Cxy, phi_xy, fftinfo
+
+
+# --------------------------------------------------------------------------- #
+# class fftanal -- segmentation statics now, the object API is completed by
+# pyfft_b200/stft.py (attached below) once K2 is available.
+# --------------------------------------------------------------------------- #
+
+class fftanal(Struct):
+    """Object API of the reference (fft_analysis.py:1695-2640)."""
+
+    def __init__(self, tvec=None, sigx=None, sigy=None, **kwargs):
+        self.verbose = kwargs.get("verbose", True)
+        if tvec is None or sigx is None:
+            if self.verbose:
+                print("Please give at least a time-vector [s] and a signal vector [a.u.]")
+            return
+        self.init(tvec, sigx, sigy, **kwargs)
+
+    def init(self, tvec=None, sigx=None, sigy=None, **kwargs):
+        """fft_analysis.py:1713-1783."""
+        self.nosigy = sigy is None or sigx is sigy
+        self.tvec, self.sigx, self.sigy = tvec, sigx, sigy
+        self.tbounds = kwargs.get("tbounds", [tvec.min(), tvec.max()])
+        self.useMLAB = kwargs.get("useMLAB", False)
+        self.plotit = kwargs.get("plotit", False)
+        self.verbose = kwargs.get("verbose", True)
+        self.Navr = kwargs.get("Navr", None)
+        self.window = kwargs.get("windowfunction", "Hanning")
+        if self.window is None:
+            self.window = "Hanning"
+        self.overlap = kwargs.get("windowoverlap", windows(self.window, verbose=False))
+        self.tvecy = kwargs.get("tvecy", None)
+        self.onesided = kwargs.get("onesided", None)
+        self.detrendstyle = kwargs.get("detrend", 1)
+        self.frange = kwargs.get("frange", None)
+        self.axes = kwargs.get("axes", -1)
+        self.precision = kwargs.get("precision", None)
+        self.device = kwargs.get("device", None)
+        if self.onesided is None:
+            self.onesided = not (np.iscomplexobj(sigx) or np.iscomplexobj(sigy))
+        if self.tvecy is not None:
+            raise NotImplementedError("tvecy resampling (filters.upsample) is out of scope")
+        self.Fs = self.__Fs__(self.tvec)
+        self.ibounds = self.__ibounds__(self.tvec, self.tbounds)
+        self.nsig = np.size(self.__trimsig__(tvec, self.ibounds))
+        calc_navr = False
+        if self.Navr is None:
+            calc_navr = True
+            self.Navr = 8
+        if "minFreq" in kwargs:
+            kwargs["tper"] = 2.0 / kwargs["minFreq"]
+        if "tper" in kwargs:
+            self.tper = kwargs["tper"]
+            self.nwins = int(self.Fs * self.tper)
+        else:
+            calc_navr = False
+            self.nwins = self.getNwins()
+        self.noverlap = self.getNoverlap()
+        if calc_navr:
+            self.Navr = self.getNavr()
+        self.win, self.winparams = self.makewindowfn(self.window, self.nwins, self.verbose)
+        self.getNnyquist()
+        self.getNorms()
+
+    def update(self, d=None):
+        if d is not None:
+            if type(d) != dict:
+                d = d.dict_from_class()
+            super(fftanal, self).__init__(d)
+
+    def fftpwelch(self):
+        """fft_analysis.py:1794-1803."""
+        self.freq, self.Pxy, self.Pxx, self.Pyy, self.Cxy, self.phi_xy, self.fftinfo = \
+            fft_pwelch(self.tvec, self.sigx, self.sigy, self.tbounds, Navr=self.Navr,
+                       windowoverlap=self.overlap, windowfunction=self.window,
+                       useMLAB=self.useMLAB, plotit=self.plotit, verbose=self.verbose,
+                       detrend_style=self.detrendstyle, onesided=self.onesided,
+                       precision=self.precision, device=self.device)
+        self.update(self.fftinfo)
+
+    # ---- segmentation / normalisation helpers (verbatim formulas) ---------- #
+    def getNavr(self):
+        self.Navr = fftanal._getNavr(self.nsig, self.nwins, self.noverlap)
+        return self.Navr
+
+    def getNwins(self):
+        self.nwins = fftanal._getNwins(self.nsig, self.Navr, self.overlap)
+        return self.nwins
+
+    def getNoverlap(self):
+        self.noverlap = fftanal._getNoverlap(self.nwins, self.overlap)
+        return self.noverlap
+
+    def getNnyquist(self):
+        self.Nnyquist = self._getNnyquist(self.nwins)
+        return self.Nnyquist
+
+    def getNorms(self):
+        self.S1, self.S2, self.NENBW, self.ENBW = fftanal._getNorms(self.win, self.Nnyquist, self.Fs)
+
+    @staticmethod
+    def __Fs__(tvec):
+        return (len(tvec) - 1) / (tvec[-1] - tvec[0])              # :2375-2377
+
+    @staticmethod
+    def __ibounds__(tvec, tbounds):
+        fs = fftanal.__Fs__(tvec)
+        return [int(np.floor((tbounds[0] - tvec[0]) * fs)),
+                int(np.floor(1 + (tbounds[1] - tvec[0]) * fs))]    # :2379-2383
+
+    @staticmethod
+    def __trimsig__(sigt, ibounds):
+        return sigt[ibounds[0]:ibounds[1]]
+
+    @staticmethod
+    def makewindowfn(windowfunction, nwins, verbose=True):
+        return windows(windowfunction, nwins=nwins, verbose=verbose, msgout=True)
+
+    @staticmethod
+    def _getNwins(nsig, Navr, windowoverlap):
+        nwins = int(np.floor(nsig * 1.0 / (Navr - Navr * windowoverlap + windowoverlap)))  # :2411-2418
+        return nsig if nwins >= nsig else nwins
+
+    @staticmethod
+    def _getNoverlap(nwins, windowoverlap):
+        return int(np.ceil(windowoverlap * nwins))                 # :2420-2422
+
+    @staticmethod
+    def _getNavr(nsig, nwins, noverlap):
+        if nwins >= nsig:
+            return int(1)
+        return (nsig - noverlap) // (nwins - noverlap)            # :2424-2430
+
+    @staticmethod
+    def _getMINoverlap(nsig, nwins, Navr):
+        noverlap = 1
+        while fftanal._checkCOLA(nsig, nwins, noverlap) is False and noverlap < 1e4:
+            noverlap += 1
+        return noverlap
+
+    @staticmethod
+    def _getMAXoverlap(nsig, nwins, Navr):
+        noverlap = int(nwins) - 1
+        while fftanal._checkCOLA(nsig, nwins, noverlap) is False and noverlap > 0:
+            noverlap -= 1
+        return noverlap
+
+    @staticmethod
+    def _checkCOLA(nsig, nwins, noverlap):
+        """Constant-overlap-add test (fft_analysis.py:2466-2468)."""
+        return (nsig - nwins) % (nwins - noverlap) == 0
+
+    @staticmethod
+    def _getNnyquist(nfft):
+        return (nfft + 1) // 2 if nfft % 2 else nfft // 2         # :2470-2484
+
+    @staticmethod
+    def _getS1(win):
+        return np.sum(win)
+
+    @staticmethod
+    def _getS2(win):
+        return np.sum(win ** 2.0)
+
+    @staticmethod
+    def _getNENBW(Nnyquist, S1, S2):
+        return Nnyquist * 1.0 * S2 / (S1 ** 2)
+
+    @staticmethod
+    def _getENBW(Fs, S1, S2):
+        return Fs * S2 / (S1 ** 2)
+
+    @staticmethod
+    def _getNorms(win, Nnyquist, Fs):
+        S1, S2 = fftanal._getS1(win), fftanal._getS2(win)
+        return S1, S2, fftanal._getNENBW(Nnyquist, S1, S2), fftanal._getENBW(Fs, S1, S2)
+
+    @staticmethod
+    def _detrend_func(detrend_style=None):
+        if detrend_style is None:
+            detrend_style = 0
+        if detrend_style > 0:
+            return detrend_mean
+        if detrend_style < 0:
+            return detrend_linear
+        return detrend_none

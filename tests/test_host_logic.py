@@ -1,0 +1,135 @@
+"""CPU: host-side mirror of the reference's bookkeeping (segmentation integers, window
+factory, result containers, error behaviour) against the golden fixtures and the oracle."""
+import json
+
+import numpy as np
+import pytest
+
+from conftest import WELCH_CASES, load_golden
+from oracle import restatement as R
+from pyfft_b200 import fft_analysis as FA
+from pyfft_b200.windows import windows
+
+
+def test_windows_bit_exact_vs_reference_golden():
+    g = load_golden("windows")
+    for nm in json.loads(str(g["names_json"])):
+        for n in (64, 129):
+            assert np.array_equal(windows(nm, nwins=n, verbose=False), g["%s_%d" % (nm, n)]), nm
+            assert np.array_equal(windows(nm, nwins=n, periodic=False, verbose=False),
+                                  g["%s_%d_aper" % (nm, n)]), nm
+        assert windows(nm, verbose=False) == float(g["%s_rov" % nm])
+    assert np.array_equal(windows("kaiser", nwins=64, beta=8.0, verbose=False), g["kaiser8_64"])
+
+
+def test_windows_return_conventions(capsys):
+    w, (title, fom) = windows("Hanning", nwins=16, msgout=True, verbose=False)
+    assert title == "Hanning" and fom.startswith("(SLDR") and w.shape == (16,)
+    rov, (title, _) = windows("SFT3F", msgout=True, verbose=False)
+    assert rov == 0.667 and title == "Fast-decaying Flattop"
+    windows("hamming", nwins=8)
+    assert "Using a periodic Hamming window function" in capsys.readouterr().out
+    assert windows("no such window", verbose=False) == 0.0           # unmatched -> rectangular
+    with pytest.raises(NameError):
+        windows("nuttall", nwins=8, verbose=False)                  # family without suffix
+    with pytest.raises(KeyError):
+        windows("kaiser", nwins=8, verbose=False)
+
+
+@pytest.mark.parametrize("case", WELCH_CASES)
+def test_plan_matches_reference_integers(case):
+    g = load_golden(case)
+    kw = json.loads(str(g["kwargs_json"]))
+    n = len(g["in_t"])
+    extra = {k: kw[k] for k in ("tper", "minFreq") if k in kw}
+    p = FA._Plan(g["in_t"], g["in_x"].shape[0], n, kw.get("tbounds"), kw.get("Navr"),
+                 kw.get("windowoverlap"), kw.get("windowfunction"), extra)
+    assert (p.nwins, p.noverlap, p.Navr) == (int(g["nwins"]), int(g["noverlap"]), int(g["Navr"]))
+    assert [p.i0, p.i1] == [int(v) for v in g["ibnds"]]
+    assert p.Fs == float(g["Fs"])
+    S1, S2, NENBW, ENBW = FA.fftanal._getNorms(windows(p.windowfunction, nwins=p.nwins, verbose=False),
+                                               p.Nnyquist, p.Fs)
+    assert (S1, S2, NENBW, ENBW) == (float(g["S1"]), float(g["S2"]), float(g["NENBW"]), float(g["ENBW"]))
+
+
+def test_plan_random_sweep_against_oracle():
+    rng = np.random.default_rng(0)
+    for _ in range(300):
+        n = int(rng.integers(200, 50000))
+        t = np.arange(n) / 1e6 + float(rng.uniform(0, 1e-3))
+        navr = int(rng.integers(1, 40))
+        ov = float(rng.choice([0.0, 0.25, 0.5, 0.661, 0.75]))
+        part = rng.random() < 0.5
+        tb = [t[int(0.1 * n)], t[int(0.8 * n)]] if part else None
+        use_tper = rng.random() < 0.3
+        kw = {"tper": float(rng.integers(16, n // 4)) / 1e6 * (1 + 1e-9)} if use_tper else {}
+        o = R.welch_plan(t, n, tb, None if use_tper else navr, ov, "Hanning", kw.get("tper"))
+        p = FA._Plan(t, n, n, tb, None if use_tper else navr, ov, "Hanning", dict(kw))
+        assert (p.nwins, p.noverlap, p.Navr, p.i0, p.i1, p.reflect) == \
+               (o["nwins"], o["noverlap"], o["Navr"], o["i0"], o["i1"], o["reflect"])
+
+
+def test_segmentation_statics_and_cola():
+    A = FA.fftanal
+    assert A._getNwins(2 ** 26, 32767, 0.5) == 4096 and A._getNoverlap(4096, 0.5) == 2048
+    assert A._getNavr(2 ** 26, 4096, 2048) == 32767
+    assert A._getNwins(100, 1, 0.5) == 100 and A._getNavr(100, 100, 50) == 1
+    assert A._getNnyquist(4096) == 2048 and A._getNnyquist(4097) == 2049
+    assert A._checkCOLA(2 ** 20, 1024, 512) and not A._checkCOLA(2 ** 20 + 1, 1024, 512)
+    assert A._getMINoverlap(4096 * 3, 4096, 2) == 2048
+    assert A._getMAXoverlap(4096 * 3, 4096, 2) == 4095
+    assert A._detrend_func(1) is FA.detrend_mean and A._detrend_func(-1) is FA.detrend_linear
+    assert A._detrend_func(0) is FA.detrend_none and A._detrend_func(None) is FA.detrend_none
+
+
+def test_detrend_helpers_match_oracle():
+    rng = np.random.default_rng(5)
+    x = rng.standard_normal((500, 3)) + np.arange(500)[:, None] * 0.01 + 3
+    assert np.allclose(FA.detrend_mean(x, axis=0), R.detrend(x, 1), atol=1e-12)
+    assert np.allclose(FA.detrend_linear(x, axis=0), R.detrend(x, -1), atol=1e-12)
+    assert FA.detrend_none(x) is x
+
+
+def test_cxy_cxy2_helper_matches_oracle():
+    rng = np.random.default_rng(6)
+    Pxx = rng.random(32) + 0j
+    Pyy = rng.random((32, 2)) + 0j
+    Pxy = rng.standard_normal((32, 2)) + 1j * rng.standard_normal((32, 2))
+    a = FA.Cxy_Cxy2(Pxx, Pyy, Pxy)
+    b = R.cxy_cxy2(Pxx, Pyy, Pxy)
+    assert np.allclose(a[0], b[0]) and np.allclose(a[1], b[1])
+
+
+def test_fftanal_init_mirrors_reference_fields():
+    g = load_golden("stft_c3")
+    o = FA.fftanal()                                  # prints the reference's hint and returns
+    o.init(g["in_t"], g["in_y"][0], tper=float(g["tper"]), windowoverlap=0.75,
+           windowfunction="Hanning", verbose=False)
+    assert (o.nwins, o.noverlap, o.Navr) == (int(g["nwins"]), int(g["noverlap"]), int(g["Navr"]))
+    assert (o.S1, o.S2, o.ENBW) == (float(g["S1"]), float(g["S2"]), float(g["ENBW"]))
+    assert o.ibounds == [int(v) for v in g["ibounds"]] and o.onesided and o.nosigy
+
+
+def test_reference_error_behaviour_is_mirrored():
+    t = np.arange(4096) / 1e6
+    x = np.zeros(4096)
+    with pytest.raises(NotImplementedError):
+        FA.fft_pwelch(t, x, x, useMLAB=True, plotit=False)
+    with pytest.raises(NotImplementedError):
+        FA.fft_pwelch(t, x, x, plotit=True)
+    with pytest.raises(NameError):                    # Navr together with tper (fft_analysis.py:102, 208)
+        FA._Plan(t, 4096, 4096, None, 4, 0.5, "Hanning", {"tper": 1e-4})
+    with pytest.raises(NotImplementedError):          # nT-model branch
+        FA._Plan(t, 100, 4096, None, 4, 0.5, "Hanning", {})
+
+
+def test_fftinfosc_container():
+    info = FA.fftinfosc()
+    assert info.Pxx.dtype == np.complex128 and info.freq.size == 0
+    with pytest.raises(AttributeError):
+        info.Pxx_seg                                   # nothing to load lazily yet
+    info.Pxx = np.ones(3)
+    d = info.dict_from_class()
+    assert "Pxx" in d and not any(k.startswith("_") for k in d)
+    s = FA.Struct(info)
+    assert np.array_equal(s.Pxx, np.ones(3))
