@@ -1,0 +1,310 @@
+#!/usr/bin/env python
+"""Benchmark of the north-star path: two-channel Welch cross-PSD + coherence, nfft 4096,
+50 % overlap, Hanning, global mean detrend, fp32 (BASELINE.json configs[1]).
+
+    python bench.py --gpus N --steps K --warmup W            (torchrun for N > 1)
+    python bench.py --impl reference ...                     CPU port of the reference path
+
+One "step" = one full pass of the hot path over this rank's resident record slice:
+detrend statistics -> (all-reduce) -> fused gather/window/FFT/accumulate -> (all-reduce of the
+partial sums) -> finalize (scale, mean, coherence, phase).  Weak scaling: every rank holds
+2 x 2^26 fresh samples of one long record of N * 2^26 samples per channel, sharded by
+contiguous segment ranges with a read-only halo.  Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+NFFT, HOP, NCH = 4096, 2048, 2
+N_PER_GPU = 2 ** 26
+FS = 1.0e6
+METRIC = "Welch cross-PSD Msamples/s (nfft 4096)"
+UNIT = "Msamples/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--samples", type=int, default=N_PER_GPU, help="samples per channel per GPU")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    return ap.parse_args()
+
+
+# --------------------------------------------------------------------------- #
+# CPU arm: literal port of the reference hot loop on a bounded sample
+# --------------------------------------------------------------------------- #
+
+def cpu_port_msamples(n=2 ** 22, repeats=1):
+    """Times oracle.restatement.fft_pwelch_port (same per-segment loop, same materialised
+    complex128 temporaries as fft_analysis.py:339-446) on 2 channels x n samples."""
+    from oracle import restatement as R
+    from oracle import signals
+    t, x, y = signals.c2_cross(n=n, dtype=np.float32)
+    x = x.astype(np.float64)
+    y = y.astype(np.float64)
+    navr = n // HOP - 1
+    best = float("inf")
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        R.fft_pwelch_port(t, x, y, navr, 0.5, "Hanning", 1)
+        best = min(best, time.perf_counter() - t0)
+    return NCH * n / best / 1e6, best
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    n = 2 ** 22
+    vals = []
+    for i in range(args.warmup + args.steps):
+        v, sec = cpu_port_msamples(n)
+        if i >= args.warmup:
+            vals.append((v, sec))
+    ms = 1e3 * sum(s for _, s in vals) / len(vals)
+    value = NCH * n / (ms / 1e3) / 1e6
+    sample = "2 ch x 2^22 samples per step (1/16 of the 2^26 workload), float64 like the reference"
+    out = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+           "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+           "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+           "config": workload_config(args.gpus, N_PER_GPU),
+           "cpu_baseline": {"value": value, "unit": UNIT, "cores": 1, "kind": "port", "sample": sample},
+           "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+           "gpu_launches": 0,
+           "note": "numpy port of fft_pwelch's home-brew loop (the reference itself is pure Python and "
+                   "is not present on the GPU box); numpy's pocketfft and the Python loop are "
+                   "single-threaded, so 1 of %d host cores is used" % (os.cpu_count() or 1)}
+    print(json.dumps(out), flush=True)
+
+
+def workload_config(world, n_per_gpu):
+    return {"workload": "two-channel cross-PSD + coherence, %d x 2^%d samples per channel, nfft=4096, "
+                        "50%% overlap, Hanning, mean detrend, fp32" % (world, int(np.log2(n_per_gpu))),
+            "channels": NCH, "samples_per_channel": world * n_per_gpu, "nfft": NFFT, "hop": HOP,
+            "parallelism": "segment ranges x%d + 1 all-reduce" % world if world > 1 else "single GPU",
+            "cache": "inputs (%.0f MB per GPU) exceed the 126 MB L2; no flush needed"
+                     % (NCH * n_per_gpu * 4 / 1e6)}
+
+
+# --------------------------------------------------------------------------- #
+# clocks sampler
+# --------------------------------------------------------------------------- #
+
+class Clocks(object):
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is not None:
+            self.proc.terminate()
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        mx = max([int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()] or [0])
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [nm for i, nm in enumerate(names)
+                   if any(len(r) > 2 + i and r[2 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# --------------------------------------------------------------------------- #
+# GPU arm
+# --------------------------------------------------------------------------- #
+
+def make_slice(torch, dev, g_lo, g_hi, seed, dc, amp, phase):
+    """Samples g_lo..g_hi-1 of one long synthetic record: tone + unit white noise + DC.
+    Noise comes from per-block generators keyed by the GLOBAL block index, so the halo
+    samples two ranks share are identical."""
+    blk = 1 << 20
+    out = torch.empty(g_hi - g_lo, dtype=torch.float32, device=dev)
+    f0 = 400.0 / NFFT                                          # bin-centred tone, cycles/sample
+    for b in range(g_lo // blk, (g_hi - 1) // blk + 1):
+        lo, hi = max(g_lo, b * blk), min(g_hi, (b + 1) * blk)
+        gen = torch.Generator(device=dev).manual_seed(seed * 100003 + b)
+        noise = torch.randn(blk, generator=gen, device=dev, dtype=torch.float32)
+        g = torch.arange(lo, hi, device=dev, dtype=torch.float64)
+        tone = (amp * torch.sin(2 * np.pi * f0 * g + phase)).float()
+        out[lo - g_lo:hi - g_lo] = tone + noise[lo - b * blk:hi - b * blk] + dc
+    return out
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from pyfft_b200 import _lib, engine, fft_pwelch
+    from pyfft_b200 import dist as pdist
+    from pyfft_b200.fft_analysis import fftanal
+    from pyfft_b200.windows import windows
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    group = None
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+        group = dist.group.WORLD
+
+    n, ntot = args.samples, world * args.samples
+    navr = ntot // HOP - 1                                     # -> nwins = 4096 (fft_analysis.py:2411-2418)
+    assert fftanal._getNwins(ntot, navr, 0.5) == NFFT
+    K, nana, refl = navr, ntot, NFFT - 1                       # whole record => reflect map (:196-205)
+    lp = pdist.local_plan(K, HOP, NFFT, nana, 0, refl, rank, world)
+    g_lo, g_hi = lp["src"]
+    x = make_slice(torch, dev, g_lo, g_hi, 11, 7.0, 1.0, 0.0)
+    y = make_slice(torch, dev, g_lo, g_hi, 12, 2.5, 0.5, -np.pi / 4)[None, :].contiguous()
+    rmap = engine.record_map(nana, 0, refl, g_lo, g_hi - g_lo)
+    win = windows("Hanning", nwins=NFFT, verbose=False)
+    S1, S2, _, ENBW = fftanal._getNorms(win, NFFT // 2, FS)
+    scale = 1.0 / S1 ** 2 / ENBW
+    wp = engine.WelchPlan(NFFT, HOP, 1, "fp32", win, dev)
+    k0, k1 = lp["k0"], lp["k1"]
+    s_lo, s_hi = lp["stats_span"]
+
+    def step():
+        wp.acc.zero_()
+        wp.stats.zero_()
+        wp.K = 0
+        wp.detrend_stats(x, y, rmap, s_lo, s_hi)
+        wp.solve_detrend(_lib.DETREND_MEAN, nana, group)
+        wp.accumulate(x, y, rmap, k0, k1 - k0)
+        if group is not None:
+            dist.all_reduce(wp.acc, group=group)
+        return wp.finalize(scale, onesided=True, K=K)
+
+    def barrier():
+        if group is not None:
+            dist.barrier(group=group)
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+        if group is not None:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX, group=group)
+        return float(ms.item()) / steps
+
+    clocks = Clocks(local)
+    if rank == 0:
+        clocks.start()
+    ms_step = timed(step, args.steps, max(args.warmup, 3))
+    # dominant kernel alone (welch_pair_kernel + its 3 us partial-sum reduction)
+    ms_k1 = timed(lambda: wp.accumulate(x, y, rmap, k0, k1 - k0), args.steps, 3)
+    ms_k0 = timed(lambda: wp.detrend_stats(x, y, rmap, s_lo, s_hi), args.steps, 3)
+    clk = clocks.stop() if rank == 0 else None
+    res = step()
+    pk = int(torch.argmax(res["Pxx"].real))
+    assert pk == 400 and bool(torch.isfinite(res["Cxy"].real).all()), "bench sanity check failed"
+
+    value = NCH * ntot / (ms_step / 1e3) / 1e6
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except (OSError, ValueError):
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    alg_bytes = NCH * n * 4                                    # every input sample read once
+    achieved = alg_bytes / (ms_k1 / 1e3) / 1e9
+
+    # ---- end to end: pinned host buffers -> public API -> host result ------------ #
+    e2e = None
+    if not args.no_e2e:
+        xh = x.cpu().pin_memory()
+        yh = y[0].cpu().pin_memory()
+        if world == 1:
+            def full(h):                                       # plain n-sample host record
+                o = torch.empty(n, dtype=torch.float32).pin_memory()
+                o[:h.numel()] = h
+                o[h.numel():] = h[:n - h.numel()]
+                return o
+            xh, yh = full(xh), full(yh)
+            tv = np.arange(n) / FS
+
+            def e2e_step():
+                out = fft_pwelch(tv, xh, yh, Navr=navr, windowoverlap=0.5, windowfunction="Hanning",
+                                 plotit=False, detrend_style=1, precision="fp32")
+                return out[1]
+            h2d = 2 * n * 4
+        else:
+            def e2e_step():
+                x.copy_(xh, non_blocking=True)
+                y[0].copy_(yh, non_blocking=True)
+                r = step()
+                return r["Pxy"].cpu(), r["Pxx"].cpu(), r["Pyy"].cpu(), r["Cxy"].cpu(), r["phi_xy"].cpu()
+            h2d = 2 * (g_hi - g_lo) * 4
+        es = max(3, min(args.steps, 10))
+        ms_e2e = timed(e2e_step, es, 2)
+        e2e = {"value": NCH * ntot / (ms_e2e / 1e3) / 1e6, "unit": UNIT, "h2d_bytes_per_step": h2d,
+               "d2h_bytes_per_step": 6 * (NFFT // 2) * 16 + 4 * NFFT * 8, "ms_per_step": ms_e2e,
+               "steps": es, "api": "pyfft_b200.fft_pwelch" if world == 1 else "engine.WelchPlan (sharded)"}
+
+    if rank != 0:
+        if group is not None:
+            dist.destroy_process_group()
+        return
+    cpu = None
+    if world == 1 and not args.no_cpu:
+        v, sec = cpu_port_msamples(2 ** 23, repeats=2)
+        cpu = {"value": v, "unit": UNIT, "cores": 1, "kind": "port",
+               "sample": "2 ch x 2^23 samples (1/8 of the workload), float64, best of 2 (%.2f s)" % sec}
+    out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+           "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
+           "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "config": workload_config(world, n),
+           "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                        "frac": achieved / peak, "traffic": None, "kernel": "welch_pair_kernel<float,12>",
+                        "algorithmic_bytes": alg_bytes, "kernel_ms": ms_k1,
+                        "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s",
+                        "whole_step_frac": alg_bytes / (ms_step / 1e3) / 1e9 / peak,
+                        "detrend_stats_ms": ms_k0},
+           "cpu_baseline": cpu, "e2e": e2e, "clocks": clk, "gpu_launches": 6 * args.steps}
+    print(json.dumps(out), flush=True)
+    if group is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

@@ -29,6 +29,7 @@ import numpy as np
 import torch
 
 from . import _lib
+from . import dist as _dist
 from . import engine as _eng
 from .windows import windows
 
@@ -268,15 +269,12 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
         rank, world = 0, 1
         if group is not None:
             rank, world = torch.distributed.get_rank(group), torch.distributed.get_world_size(group)
+        lp = _dist.local_plan(K, hop, nwins, plan.nana, plan.i0, refl, rank, world)
         if mode != _lib.DETREND_NONE:
             # global detrend over the whole analysed record (:356-357): each rank sums its slice
-            j0 = plan.nana * rank // world
-            j1 = plan.nana * (rank + 1) // world
-            wp.detrend_stats(x, y, rmap, j0, j1)
+            wp.detrend_stats(x, y, rmap, lp["stats_span"][0], lp["stats_span"][1])
             wp.solve_detrend(mode, plan.nana, group)
-        k0 = K * rank // world
-        k1 = K * (rank + 1) // world
-        wp.accumulate(x, y, rmap, k0, k1 - k0)
+        wp.accumulate(x, y, rmap, lp["k0"], lp["k1"] - lp["k0"])
         if group is not None:
             wp.all_reduce(group)
         scale = 1.0 / (fftinfo.S1 ** 2) / fftinfo.ENBW             # :432-440

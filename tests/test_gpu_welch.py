@@ -1,0 +1,133 @@
+"""GPU parity: fft_pwelch on the sm_100a kernels (through the C ABI) vs the golden
+fixtures written by the unmodified reference and vs the oracle on seeded inputs.
+
+Tolerances (BASELINE.json north_star):
+  fp32: max |P - P_ref| <= 1e-5 * max |P_ref| for PSD/CSD, <= 1e-4 absolute for coherence
+  fp64: <= 1e-12 relative to the spectral peak
+"""
+import json
+
+import numpy as np
+import pytest
+
+from conftest import UNIT_SCALE, load_golden, phase_err, relerr
+
+pytestmark = pytest.mark.gpu
+
+POW2_CASES = ["welch_c1_auto", "welch_c1_bincentred", "welch_c2_cross", "welch_c2_dc",
+              "welch_tbounds_tper"]
+TOL = {"fp64": dict(P=1e-12, C=1e-10, R=1e-11), "fp32": dict(P=1e-5, C=1e-4, R=2e-5)}
+
+
+def _run(g, precision):
+    from pyfft_b200 import fft_pwelch
+    kw = json.loads(str(g["kwargs_json"]))
+    tb = kw.pop("tbounds")
+    x, y = g["in_x"], g["in_y"]
+    if precision == "fp32":
+        x, y = x.astype(np.float32), y.astype(np.float32)
+    return fft_pwelch(g["in_t"], x, y, tb, plotit=False, precision=precision, **kw)
+
+
+def _check(out, ref, precision, reference_is_fp32_rounded=False):
+    tol = TOL[precision]
+    freq, Pxy, Pxx, Pyy, Cxy, phi, info = out
+    assert relerr(freq, ref["freq"]) < 1e-14
+    for nm, a in (("Pxy", Pxy), ("Pxx", Pxx), ("Pyy", Pyy)):
+        assert a.dtype == np.complex128
+        assert relerr(a, ref[nm]) <= tol["P"], nm
+    assert relerr(Cxy, ref["Cxy"], 1.0) <= tol["C"]
+    assert relerr(info.Cxy2, ref["Cxy2"], 1.0) <= tol["C"]
+    assert phase_err(phi, ref["phi_xy"], ref["Pxy"]) <= 10 * tol["P"]
+    for nm in ("Rxx", "Ryy", "Rxy", "Lxx", "Lyy", "Lxy", "Ex", "Ey"):
+        assert relerr(getattr(info, nm), ref[nm]) <= tol["R"], nm
+    for nm in ("iCxy", "corrcoef"):
+        assert relerr(getattr(info, nm), ref[nm], 1.0) <= 10 * tol["C"], nm
+    assert relerr(info.lags, ref["lags"]) < 1e-14
+    for nm in ("nwins", "noverlap", "Navr", "nch"):
+        assert int(getattr(info, nm)) == int(ref[nm])
+    for nm in ("S1", "S2", "ENBW", "NENBW", "minFreq"):
+        assert float(getattr(info, nm)) == float(ref[nm])
+
+
+@pytest.mark.parametrize("case", POW2_CASES)
+def test_fp64_matches_reference_golden(case, cuda_device):
+    g = load_golden(case)
+    _check(_run(g, "fp64"), g, "fp64")
+
+
+@pytest.mark.parametrize("case", POW2_CASES)
+def test_fp32_matches_oracle_on_rounded_inputs(case, cuda_device):
+    from oracle import restatement as R
+    g = load_golden(case)
+    kw = json.loads(str(g["kwargs_json"]))
+    tb = kw.pop("tbounds")
+    x32, y32 = g["in_x"].astype(np.float32), g["in_y"].astype(np.float32)
+    with np.errstate(all="ignore"):
+        ref = R.fft_pwelch(g["in_t"], x32.astype(np.float64), y32.astype(np.float64), tb, **kw)
+    _check(_run(g, "fp32"), ref, "fp32")
+
+
+@pytest.mark.parametrize("case", ["welch_multi_sft3f_linear", "welch_defaults", "welch_odd_nfft",
+                                  "welch_ref_selftest", "welch_twosided_complex"])
+def test_unsupported_shapes_fail_loudly(case, cuda_device):
+    """non power-of-two windows / complex inputs: NotImplementedError, never a CPU fallback."""
+    with pytest.raises(NotImplementedError):
+        _run(load_golden(case), "fp64")
+
+
+@pytest.mark.parametrize("log2l", [4, 5, 6, 7, 8, 9, 10, 11, 12, 13])
+@pytest.mark.parametrize("precision", ["fp32", "fp64"])
+def test_every_window_length_vs_oracle(log2l, precision, cuda_device):
+    from oracle import restatement as R
+    from pyfft_b200 import fft_pwelch
+    L = 1 << log2l
+    rng = np.random.default_rng(100 + log2l)
+    K, nch = 9, 2 if log2l % 2 else 3
+    n = L // 2 * (K + 1) + 5                           # a few unused tail samples
+    t = np.arange(n) / 1e6
+    x = np.sin(2 * np.pi * 0.11 * np.arange(n)) + rng.standard_normal(n) + 2.0
+    y = np.stack([np.cos(2 * np.pi * 0.11 * np.arange(n) + c) + rng.standard_normal(n) - c
+                  for c in range(nch)], 1)
+    if precision == "fp32":
+        x, y = x.astype(np.float32), y.astype(np.float32)
+    det = (1, -1, 0)[log2l % 3]
+    tb = [t[3], t[-1]]                                 # no reflect padding here
+    kw = dict(windowoverlap=0.5, windowfunction="Hanning", detrend_style=det,
+              tper=L / 1e6 * (1 + 1e-9))
+    with np.errstate(all="ignore"):
+        ref = R.fft_pwelch(t, x.astype(np.float64), y.astype(np.float64), tb, **kw)
+    assert ref["nwins"] == L
+    out = fft_pwelch(t, x, y, tb, plotit=False, precision=precision, **kw)
+    _check(out, ref, precision)
+
+
+@pytest.mark.parametrize("precision", ["fp32", "fp64"])
+def test_two_sided_real_input_and_reflect(precision, cuda_device):
+    from oracle import restatement as R
+    from pyfft_b200 import fft_pwelch
+    rng = np.random.default_rng(42)
+    n = 2 ** 14
+    t = np.arange(n) / 1e6
+    x = rng.standard_normal(n) + 0.5
+    y = np.roll(x, 3) + 0.3 * rng.standard_normal(n)
+    if precision == "fp32":
+        x, y = x.astype(np.float32), y.astype(np.float32)
+    kw = dict(Navr=31, windowoverlap=0.5, windowfunction="Hamming", detrend_style=1, onesided=False)
+    with np.errstate(all="ignore"):
+        ref = R.fft_pwelch(t, x.astype(np.float64), y.astype(np.float64), **kw)
+    assert ref["reflect"] and ref["Pxx"].shape == (1024,)
+    _check(fft_pwelch(t, x, y, plotit=False, precision=precision, **kw), ref, precision)
+
+
+def test_device_tensor_inputs_and_identical_signals(cuda_device):
+    import torch
+    from pyfft_b200 import fft_pwelch
+    n = 2 ** 16
+    t = np.arange(n) / 1e6
+    g = torch.Generator(device=cuda_device).manual_seed(5)
+    x = torch.randn(n, generator=g, device=cuda_device, dtype=torch.float32)
+    f, Pxy, Pxx, Pyy, Cxy, phi, info = fft_pwelch(t, x, x, Navr=63, windowoverlap=0.5, plotit=False)
+    assert info.precision == "fp32" and info.nwins == 2048
+    assert np.allclose(np.abs(Cxy), 1.0, atol=1e-5) and np.allclose(phi, 0.0, atol=1e-5)
+    assert relerr(Pxx, Pyy) < 1e-6 and relerr(Pxy.real, Pxx.real) < 1e-6
