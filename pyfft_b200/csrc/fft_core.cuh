@@ -115,20 +115,139 @@ template <typename T, bool INV> struct SmallFFT<T, 16, INV> {
     }
 };
 
+// ---- shared-memory exchange through explicit 32-bit shared-window addresses ---- //
+// (keeps every access an LDS/STS; generic pointers selected at run time made the
+// compiler fall back to generic LD/ST)
+template <typename T> struct SharedIO;
+template <> struct SharedIO<float> {
+    static __device__ __forceinline__ cpx<float> ld(uint32_t a) {
+        cpx<float> r;
+        asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(r.x), "=f"(r.y) : "r"(a) : "memory");
+        return r;
+    }
+    static __device__ __forceinline__ void st(uint32_t a, cpx<float> v) {
+        asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(a), "f"(v.x), "f"(v.y) : "memory");
+    }
+};
+template <> struct SharedIO<double> {
+    static __device__ __forceinline__ cpx<double> ld(uint32_t a) {
+        cpx<double> r;
+        asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(r.x), "=d"(r.y) : "r"(a) : "memory");
+        return r;
+    }
+    static __device__ __forceinline__ void st(uint32_t a, cpx<double> v) {
+        asm volatile("st.shared.v2.f64 [%0], {%1, %2};" ::"r"(a), "d"(v.x), "d"(v.y) : "memory");
+    }
+};
+
+// Two exchange buffers used alternately: every exchange is
+//     write cur;  __syncthreads();  read cur;  flip()
+// A thread can only start writing a buffer again after it passed the barrier of the
+// exchange in between, which every thread reaches after finishing its reads of that
+// buffer -- so ONE barrier per exchange is enough, across passes, epilogue exchanges and
+// consecutive segments alike.
+// SINGLE = true (two buffers do not fit in shared memory): cur == other and every write
+// is preceded by an extra barrier after the last reads.
+template <typename T, bool SINGLE_ = false> struct Exchange {
+    static constexpr bool SINGLE = SINGLE_;
+    uint32_t cur, other;         // byte addresses in the shared window
+    __device__ __forceinline__ void flip() { uint32_t x = cur; cur = other; other = x; }
+    __device__ __forceinline__ void before_write() const { if (SINGLE) __syncthreads(); }
+    __device__ __forceinline__ cpx<T> ld(uint32_t buf, int idx) const {
+        return SharedIO<T>::ld(buf + (uint32_t)phys(idx) * (uint32_t)sizeof(cpx<T>));
+    }
+    __device__ __forceinline__ void st(uint32_t buf, int idx, cpx<T> v) const {
+        SharedIO<T>::st(buf + (uint32_t)phys(idx) * (uint32_t)sizeof(cpx<T>), v);
+    }
+};
+
+// Per-thread base twiddles, one per twiddled pass p = 1, 2, 3:
+//     w[p-1] = exp(-+2 pi i (t mod NS_p) / (NS_p R_p))
+// loaded once per kernel from the long-double table; the powers w^r a radix-R butterfly
+// needs are formed in registers by a multiplication tree of depth <= 4 (no per-segment
+// table traffic: the table lookups were what saturated L1 in the first version).
+template <typename T> struct Twiddles { cpx<T> w[3]; };
+
+template <typename T, int LOG2L, bool INV>
+__device__ __forceinline__ Twiddles<T> load_twiddles(const cpx<T>* __restrict__ tw, int t) {
+    constexpr int L = 1 << LOG2L;
+    Twiddles<T> r;
+    int ns = 16;
+#pragma unroll
+    for (int p = 0; p < 3; ++p) {
+        r.w[p] = mk<T>(T(1), T(0));
+        if (ns < L) {
+            const int rem = L / ns;
+            const int R = rem >= 16 ? 16 : rem;
+            cpx<T> w = tw[(t & (ns - 1)) * (L / (ns * R))];
+            if (INV) w.y = -w.y;
+            r.w[p] = w;
+            ns *= R;
+        }
+    }
+    return r;
+}
+
+// exp(-+2 pi i m / 16), m = 0..7, as compile-time constants
+template <typename T, bool INV>
+__device__ __forceinline__ cpx<T> w16_power(int m) {
+    const T h = T(0.70710678118654752440), c1 = T(0.92387953251128675613), s1 = T(0.38268343236508977173);
+    T re = T(1), im = T(0);
+    switch (m) {
+        case 1: re = c1; im = -s1; break;
+        case 2: re = h; im = -h; break;
+        case 3: re = s1; im = -c1; break;
+        case 4: re = T(0); im = T(-1); break;
+        case 5: re = -s1; im = -c1; break;
+        case 6: re = -h; im = -h; break;
+        case 7: re = -c1; im = -s1; break;
+        default: break;
+    }
+    return mk<T>(re, INV ? -im : im);
+}
+
+// u[r] *= w^r, r = 1..R-1
+template <typename T, int R>
+__device__ __forceinline__ void apply_twiddle_powers(cpx<T>* u, cpx<T> w1) {
+    u[1] = cmul(u[1], w1);
+    if (R > 2) {
+        const cpx<T> w2 = cmul(w1, w1);
+        const cpx<T> w3 = cmul(w2, w1);
+        u[2] = cmul(u[2], w2);
+        u[3] = cmul(u[3], w3);
+        if (R > 4) {
+            const cpx<T> w4 = cmul(w2, w2);
+            const cpx<T> w5 = cmul(w4, w1), w6 = cmul(w4, w2), w7 = cmul(w4, w3);
+            u[4] = cmul(u[4], w4); u[5] = cmul(u[5], w5); u[6] = cmul(u[6], w6); u[7] = cmul(u[7], w7);
+            if (R > 8) {
+                const cpx<T> w8 = cmul(w4, w4);
+                u[8] = cmul(u[8], w8);
+                u[9] = cmul(u[9], cmul(w8, w1));
+                u[10] = cmul(u[10], cmul(w8, w2));
+                u[11] = cmul(u[11], cmul(w8, w3));
+                u[12] = cmul(u[12], cmul(w8, w4));
+                u[13] = cmul(u[13], cmul(w8, w5));
+                u[14] = cmul(u[14], cmul(w8, w6));
+                u[15] = cmul(u[15], cmul(w8, w7));
+            }
+        }
+    }
+}
+
 // One Stockham pass of radix R with NS = product of the previous radices.
 //  FIRST: inputs are already in v[] (no exchange read, no twiddles)
 //  LAST : results stay in v[] in natural order (no exchange write)
-// `tw` = exp(-2 pi i k / L), k = 0..L-1.
-//  SINGLE: buf_in == buf_out (one exchange buffer only): barrier between this
-//          pass's reads and its writes
-template <typename T, int L, int NS, int R, bool INV, bool FIRST, bool LAST, bool SINGLE = false>
-__device__ __forceinline__ void stockham_pass(cpx<T> (&v)[16], const cpx<T>* buf_in, cpx<T>* buf_out,
-                                              const cpx<T>* __restrict__ tw, int t) {
+//  w1   : this thread's base twiddle for the pass (butterfly m = 0); a remainder pass
+//         (R < 16, always the last one) runs 16/R butterflies whose base twiddles differ
+//         by the compile-time rotation exp(-+2 pi i m TPS / L)
+template <typename T, int L, int NS, int R, bool INV, bool FIRST, bool LAST, bool SINGLE>
+__device__ __forceinline__ void stockham_pass(cpx<T> (&v)[16], const Exchange<T, SINGLE>& ex, uint32_t buf_in,
+                                              uint32_t buf_out, cpx<T> w1, int t) {
     constexpr int TPS = (L / 16) > 0 ? (L / 16) : 1;
     constexpr int NB = 16 / R;
     if (!FIRST) {
 #pragma unroll
-        for (int s = 0; s < 16; ++s) v[s] = buf_in[phys(t + TPS * s)];
+        for (int s = 0; s < 16; ++s) v[s] = ex.ld(buf_in, t + TPS * s);
         if (SINGLE && !LAST) __syncthreads();
     }
 #pragma unroll
@@ -138,14 +257,9 @@ __device__ __forceinline__ void stockham_pass(cpx<T> (&v)[16], const cpx<T>* buf
 #pragma unroll
         for (int r = 0; r < R; ++r) u[r] = v[m + r * NB];
         if (NS > 1) {
-            const int k = j & (NS - 1);
-            constexpr int STEP = L / (NS * R);
-#pragma unroll
-            for (int r = 1; r < R; ++r) {
-                cpx<T> w = tw[r * k * STEP];
-                if (INV) w.y = -w.y;
-                u[r] = cmul(u[r], w);
-            }
+            cpx<T> wm = w1;
+            if (m > 0) wm = cmul(w1, w16_power<T, INV>(m));   // m TPS / (NS R) = m / 16 here
+            apply_twiddle_powers<T, R>(u, wm);
         }
         SmallFFT<T, R, INV>::run(u);
         if (LAST) {
@@ -154,62 +268,41 @@ __device__ __forceinline__ void stockham_pass(cpx<T> (&v)[16], const cpx<T>* buf
         } else {
             const int base = (j / NS) * (NS * R) + (j & (NS - 1));
 #pragma unroll
-            for (int r = 0; r < R; ++r) buf_out[phys(base + r * NS)] = u[r];
+            for (int r = 0; r < R; ++r) ex.st(buf_out, base + r * NS, u[r]);
         }
     }
 }
 
-// Two exchange buffers used alternately: every exchange is
-//     write bufs[cur];  __syncthreads();  read bufs[cur];  cur ^= 1
-// A thread can only start writing bufs[c] again after it passed the barrier of
-// the exchange in between, which every thread reaches after finishing its reads
-// of bufs[c] -- so ONE barrier per exchange is enough, across passes, epilogue
-// exchanges and consecutive segments alike.
-//
-// SINGLE = true (used when two buffers do not fit in shared memory): b[0] == b[1]
-// and every write is preceded by an extra barrier after the last reads.
-template <typename T, bool SINGLE_ = false> struct Exchange {
-    static constexpr bool SINGLE = SINGLE_;
-    cpx<T>* b[2];
-    int cur;
-    __device__ __forceinline__ cpx<T>* buf() const { return b[cur]; }
-    __device__ __forceinline__ void flip() { cur ^= 1; }
-    // call before writing buf() when the previous reads of it were NOT already
-    // separated from this write by a barrier (first pass of a segment, epilogue)
-    __device__ __forceinline__ void before_write() const { if (SINGLE) __syncthreads(); }
-};
-
-template <typename T, int L, int NS, int REMAIN, bool INV, bool SINGLE> struct PassChain {
-    // REMAIN = L / NS still to be transformed; this is never the first pass.
+template <typename T, int L, int NS, int REMAIN, int P, bool INV, bool SINGLE> struct PassChain {
+    // REMAIN = L / NS still to be transformed; P = index of this pass (>= 1)
     static constexpr int R = REMAIN >= 16 ? 16 : REMAIN;
     static constexpr bool LAST = (REMAIN == R);
     static __device__ __forceinline__ void run(cpx<T> (&v)[16], Exchange<T, SINGLE>& ex,
-                                               const cpx<T>* __restrict__ tw, int t) {
-        // the previous pass wrote ex.buf(); barrier, then read it
-        __syncthreads();
-        const cpx<T>* in = ex.buf();
+                                               const Twiddles<T>& tw, int t) {
+        __syncthreads();                 // the previous pass wrote ex.cur
+        const uint32_t in = ex.cur;
         ex.flip();
-        stockham_pass<T, L, NS, R, INV, false, LAST, SINGLE>(v, in, ex.buf(), tw, t);
-        if (!LAST) PassChain<T, L, NS * R, REMAIN / R, INV, SINGLE>::run(v, ex, tw, t);
+        stockham_pass<T, L, NS, R, INV, false, LAST, SINGLE>(v, ex, in, ex.cur, tw.w[P - 1], t);
+        if (!LAST) PassChain<T, L, NS * R, REMAIN / R, P + 1, INV, SINGLE>::run(v, ex, tw, t);
     }
 };
-template <typename T, int L, int NS, bool INV, bool SINGLE> struct PassChain<T, L, NS, 1, INV, SINGLE> {
-    static __device__ __forceinline__ void run(cpx<T> (&)[16], Exchange<T, SINGLE>&, const cpx<T>*, int) {}
+template <typename T, int L, int NS, int P, bool INV, bool SINGLE> struct PassChain<T, L, NS, 1, P, INV, SINGLE> {
+    static __device__ __forceinline__ void run(cpx<T> (&)[16], Exchange<T, SINGLE>&, const Twiddles<T>&, int) {}
 };
 
 // Full transform of one segment slot.  v[] in: element t + TPS*s; out: bin t + TPS*s.
 // All threads of the CTA must call this together (it contains barriers).
 template <typename T, int LOG2L, bool INV, bool SINGLE>
 __device__ __forceinline__ void fft_block(cpx<T> (&v)[16], Exchange<T, SINGLE>& ex,
-                                          const cpx<T>* __restrict__ tw, int t) {
+                                          const Twiddles<T>& tw, int t) {
     constexpr int L = 1 << LOG2L;
     static_assert(LOG2L >= 4 && LOG2L <= 13, "16 <= L <= 8192");
     if (L == 16) {
-        stockham_pass<T, L, 1, 16, INV, true, true>(v, nullptr, nullptr, tw, t);
+        stockham_pass<T, L, 1, 16, INV, true, true, SINGLE>(v, ex, 0u, 0u, mk<T>(T(1), T(0)), t);
     } else {
         ex.before_write();
-        stockham_pass<T, L, 1, 16, INV, true, false>(v, nullptr, ex.buf(), tw, t);
-        PassChain<T, L, 16, L / 16, INV, SINGLE>::run(v, ex, tw, t);
+        stockham_pass<T, L, 1, 16, INV, true, false, SINGLE>(v, ex, 0u, ex.cur, mk<T>(T(1), T(0)), t);
+        PassChain<T, L, 16, L / 16, 1, INV, SINGLE>::run(v, ex, tw, t);
     }
 }
 

@@ -117,11 +117,13 @@ welch_pair_kernel(const WelchParams<T> p) {
     const double ax = p.coef_x ? p.coef_x[0] : 0.0, bx = p.coef_x ? p.coef_x[1] : 0.0;
     const double ay = p.coef_y ? p.coef_y[2 * pair] : 0.0, by = p.coef_y ? p.coef_y[2 * pair + 1] : 0.0;
     const T bxf = (T)bx, byf = (T)by;
+    const bool linear = (bx != 0.0) || (by != 0.0);
 
+    const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(sm);
     Exchange<T, SINGLE> ex;
-    ex.b[0] = sm + (size_t)slot * E;
-    ex.b[1] = SINGLE ? ex.b[0] : sm + (size_t)(SLOTS + slot) * E;
-    ex.cur = 0;
+    ex.cur = sbase + (uint32_t)(slot * E * sizeof(cpx<T>));
+    ex.other = SINGLE ? ex.cur : sbase + (uint32_t)((SLOTS + slot) * E * sizeof(cpx<T>));
+    const Twiddles<T> tws = load_twiddles<T, LOG2L, false>(p.tw, t);
 
     T acc[8][4];
     T nyq[4] = {T(0), T(0), T(0), T(0)};
@@ -136,27 +138,48 @@ welch_pair_kernel(const WelchParams<T> p) {
         cpx<T> v[16];
         if (active) {
             const int64_t j0 = (p.seg_first + k) * p.hop;
-            const T cx0 = (T)(ax + bx * (double)j0), cy0 = (T)(ay + by * (double)j0);
+            T cx0 = (T)(ax + bx * (double)j0), cy0 = (T)(ay + by * (double)j0);
+            if (j0 >= p.map.reflect) {
+                // plain segment: one base offset, 32-bit element offsets, coalesced 4-byte loads
+                const int64_t e0 = j0 - p.map.reflect + p.map.i0 - p.map.src_base;
+                const T* __restrict__ us = u + e0 + t;
+                const T* __restrict__ ws = w + e0 + t;
+#pragma unroll
+                for (int s = 0; s < 16; ++s) v[s] = mk<T>(us[TPS * s], ws[TPS * s]);
+            } else {
+                // segment touching the mirrored head of the record (fft_analysis.py:196-205)
+#pragma unroll
+                for (int s = 0; s < 16; ++s) {
+                    const int64_t e = src_index(p.map, j0 + t + TPS * s);
+                    v[s] = mk<T>(u[e], w[e]);
+                }
+            }
+            if (linear) {
+#pragma unroll
+                for (int s = 0; s < 16; ++s) {
+                    const T n = (T)(t + TPS * s);
+                    v[s].x -= cx0 + bxf * n;
+                    v[s].y -= cy0 + byf * n;
+                }
+                cx0 = T(0);
+                cy0 = T(0);
+            }
 #pragma unroll
             for (int s = 0; s < 16; ++s) {
-                const int n = t + TPS * s;
-                const int64_t e = src_index(p.map, j0 + n);
-                const T wv = swin[n];
-                const T xv = u[e] - (cx0 + bxf * (T)n);
-                const T yv = w[e] - (cy0 + byf * (T)n);
-                v[s] = mk<T>(xv * wv, yv * wv);
+                const T wv = swin[t + TPS * s];
+                v[s] = mk<T>((v[s].x - cx0) * wv, (v[s].y - cy0) * wv);
             }
         } else {
 #pragma unroll
             for (int s = 0; s < 16; ++s) v[s] = mk<T>(T(0), T(0));
         }
-        fft_block<T, LOG2L, false, SINGLE>(v, ex, p.tw, t);
+        fft_block<T, LOG2L, false, SINGLE>(v, ex, tws, t);
 
         // exchange the spectrum so that every thread can fetch Z[L-f] for its bins
         ex.before_write();
-        cpx<T>* e = ex.buf();
+        const uint32_t e = ex.cur;
 #pragma unroll
-        for (int s = 0; s < 16; ++s) e[phys(t + TPS * s)] = v[s];
+        for (int s = 0; s < 16; ++s) ex.st(e, t + TPS * s, v[s]);
         __syncthreads();
         ex.flip();
         if (active) {
@@ -164,7 +187,7 @@ welch_pair_kernel(const WelchParams<T> p) {
             for (int s = 0; s < 8; ++s) {
                 const int f = t + TPS * s;
                 const cpx<T> A = v[s];
-                const cpx<T> B = e[phys((L - f) & (L - 1))];
+                const cpx<T> B = ex.ld(e, (L - f) & (L - 1));
                 // U = (A + conj B)/2, V = (A - conj B)/(2i); the factors 1/2 are applied at the end
                 const T ur = A.x + B.x, ui = A.y - B.y, vr = A.y + B.y, vi = B.x - A.x;
                 acc[s][0] += ur * ur + ui * ui;
@@ -257,8 +280,8 @@ welch_correlation_kernel(const double* __restrict__ spec, int ncol, int onesided
     const int t = threadIdx.x;
     const int F = onesided ? L / 2 : L;
     Exchange<double, true> ex;
-    ex.b[0] = ex.b[1] = sm;
-    ex.cur = 0;
+    ex.cur = ex.other = (uint32_t)__cvta_generic_to_shared(sm);
+    const Twiddles<double> tws = load_twiddles<double, LOG2L, true>(tw, t);
     cpx<double> v[16];
 #pragma unroll
     for (int s = 0; s < 16; ++s) {
@@ -283,7 +306,7 @@ welch_correlation_kernel(const double* __restrict__ spec, int ncol, int onesided
         }
         v[s] = z;
     }
-    fft_block<double, LOG2L, true, true>(v, ex, tw, t);
+    fft_block<double, LOG2L, true, true>(v, ex, tws, t);
     const double sc = sqrt((double)L) / (double)L;     // sqrt(nfft) * (1/nfft of the inverse)
 #pragma unroll
     for (int s = 0; s < 16; ++s) {

@@ -1,9 +1,7 @@
 #!/bin/bash
-# One gpurun call: microbench + GPU tests + smoke + short bench.  Everything is logged
 # under gpurun_out/ so that a cut-off call can still be read.
 mkdir -p gpurun_out
 nvidia-smi > gpurun_out/nvidia-smi.txt 2>&1
-if [ -x tools/microbench ]; then timeout 120 tools/microbench > gpurun_out/microbench.txt 2>&1; fi
 timeout 1500 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1
 echo "pytest exit $?" >> gpurun_out/pytest_gpu.log
 timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1
