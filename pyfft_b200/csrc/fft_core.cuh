@@ -153,6 +153,15 @@ template <typename T, bool SINGLE_ = false> struct Exchange {
     uint32_t cur, other;         // byte addresses in the shared window
     __device__ __forceinline__ void flip() { uint32_t x = cur; cur = other; other = x; }
     __device__ __forceinline__ void before_write() const { if (SINGLE) __syncthreads(); }
+    // phys(base + r*STRIDE) == phys(base) + r*(STRIDE + STRIDE/16) when STRIDE % 16 == 0, and
+    // == phys(base) + r when STRIDE == 1, base % 16 == 0, r < 16: one address per thread plus
+    // compile-time immediates instead of a shift/add per access.
+    template <int STRIDE> static __device__ __forceinline__ constexpr uint32_t lin(int r) {
+        return (uint32_t)(r * (STRIDE % 16 == 0 ? STRIDE + STRIDE / 16 : STRIDE)) * (uint32_t)sizeof(cpx<T>);
+    }
+    static __device__ __forceinline__ uint32_t addr(uint32_t buf, int idx) {
+        return buf + (uint32_t)phys(idx) * (uint32_t)sizeof(cpx<T>);
+    }
     __device__ __forceinline__ cpx<T> ld(uint32_t buf, int idx) const {
         return SharedIO<T>::ld(buf + (uint32_t)phys(idx) * (uint32_t)sizeof(cpx<T>));
     }
@@ -246,8 +255,14 @@ __device__ __forceinline__ void stockham_pass(cpx<T> (&v)[16], const Exchange<T,
     constexpr int TPS = (L / 16) > 0 ? (L / 16) : 1;
     constexpr int NB = 16 / R;
     if (!FIRST) {
+        if (TPS % 16 == 0) {
+            const uint32_t a = ex.addr(buf_in, t);
 #pragma unroll
-        for (int s = 0; s < 16; ++s) v[s] = ex.ld(buf_in, t + TPS * s);
+            for (int s = 0; s < 16; ++s) v[s] = SharedIO<T>::ld(a + ex.template lin<TPS>(s));
+        } else {
+#pragma unroll
+            for (int s = 0; s < 16; ++s) v[s] = ex.ld(buf_in, t + TPS * s);
+        }
         if (SINGLE && !LAST) __syncthreads();
     }
 #pragma unroll
@@ -267,8 +282,14 @@ __device__ __forceinline__ void stockham_pass(cpx<T> (&v)[16], const Exchange<T,
             for (int r = 0; r < R; ++r) v[m + r * NB] = u[r];
         } else {
             const int base = (j / NS) * (NS * R) + (j & (NS - 1));
+            if (NS % 16 == 0 || (NS == 1 && R == 16)) {
+                const uint32_t a = ex.addr(buf_out, base);
 #pragma unroll
-            for (int r = 0; r < R; ++r) ex.st(buf_out, base + r * NS, u[r]);
+                for (int r = 0; r < R; ++r) SharedIO<T>::st(a + ex.template lin<NS>(r), u[r]);
+            } else {
+#pragma unroll
+                for (int r = 0; r < R; ++r) ex.st(buf_out, base + r * NS, u[r]);
+            }
         }
     }
 }

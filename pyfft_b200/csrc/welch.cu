@@ -19,8 +19,30 @@ __global__ void __launch_bounds__(256) detrend_stats_kernel(const T* __restrict_
     const T* p = ptr + (int64_t)c * ch_stride;
     double s0 = 0.0, s1 = 0.0;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    for (int64_t j = j_begin + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < j_end; j += stride) {
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    // mirrored head of the record (at most nwins-1 samples): element-wise map
+    const int64_t j_mid = j_begin > map.reflect ? j_begin : (map.reflect < j_end ? map.reflect : j_end);
+    for (int64_t j = j_begin + tid; j < j_mid; j += stride) {
         const double v = (double)p[src_index(map, j)];
+        s0 += v;
+        s1 += v * (double)j;
+    }
+    // plain part: contiguous in memory, 8 independent coalesced loads in flight per thread
+    const T* __restrict__ q = p + (map.i0 - map.reflect - map.src_base);
+    int64_t j = j_mid + tid;
+    for (; j + 7 * stride < j_end; j += 8 * stride) {
+        T r[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) r[i] = q[j + i * stride];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const double v = (double)r[i];
+            s0 += v;
+            s1 += v * (double)(j + i * stride);
+        }
+    }
+    for (; j < j_end; j += stride) {
+        const double v = (double)q[j];
         s0 += v;
         s1 += v * (double)j;
     }
@@ -146,6 +168,17 @@ welch_pair_kernel(const WelchParams<T> p) {
                 const T* __restrict__ ws = w + e0 + t;
 #pragma unroll
                 for (int s = 0; s < 16; ++s) v[s] = mk<T>(us[TPS * s], ws[TPS * s]);
+                // pull the NEW samples of the next segment of this slot into L2 (one 128-byte line
+                // per thread) so that its loads one iteration from now are L2 hits, not DRAM misses
+                if (k + 1 < k1) {
+                    constexpr int LINE = 128 / (int)sizeof(T);
+                    const int64_t hop_lines = (p.hop + LINE - 1) / LINE;
+                    if (t < 2 * hop_lines) {
+                        const T* base = (t < hop_lines ? u : w) + e0 + L;
+                        const int64_t ln = t < hop_lines ? t : t - hop_lines;
+                        asm volatile("prefetch.global.L1 [%0];" ::"l"(base + ln * LINE));
+                    }
+                }
             } else {
                 // segment touching the mirrored head of the record (fft_analysis.py:196-205)
 #pragma unroll
@@ -175,19 +208,38 @@ welch_pair_kernel(const WelchParams<T> p) {
         }
         fft_block<T, LOG2L, false, SINGLE>(v, ex, tws, t);
 
-        // exchange the spectrum so that every thread can fetch Z[L-f] for its bins
+        // exchange the upper half of the spectrum so that every thread can fetch Z[L-f] for its
+        // bins f = t + TPS*s, s < 8: the partner is thread TPS - t, slot 15 - s (thread 0 pairs with
+        // itself: slot 16 - s, taken from its own registers).  Unpadded layout [slot-8][t]: ascending
+        // writes and descending reads of 16 consecutive 8-byte words are both conflict-free.
         ex.before_write();
         const uint32_t e = ex.cur;
+        constexpr uint32_t CB = (uint32_t)sizeof(cpx<T>);
+        if (TPS % 16 == 0) {
+            const uint32_t a = e + (uint32_t)t * CB;
 #pragma unroll
-        for (int s = 0; s < 16; ++s) ex.st(e, t + TPS * s, v[s]);
+            for (int s = 8; s < 16; ++s) SharedIO<T>::st(a + (uint32_t)((s - 8) * TPS) * CB, v[s]);
+        } else {
+#pragma unroll
+            for (int s = 0; s < 16; ++s) ex.st(e, t + TPS * s, v[s]);
+        }
         __syncthreads();
         ex.flip();
         if (active) {
+            const uint32_t pa = e + (uint32_t)(TPS - t) * CB;
 #pragma unroll
             for (int s = 0; s < 8; ++s) {
                 const int f = t + TPS * s;
                 const cpx<T> A = v[s];
-                const cpx<T> B = ex.ld(e, (L - f) & (L - 1));
+                cpx<T> B;
+                if (TPS % 16 == 0) {
+                    B = SharedIO<T>::ld(pa + (uint32_t)((7 - s) * TPS) * CB);
+                    // thread 0 pairs with itself (bin TPS*s with TPS*(16-s)): its slot 16-s sits in row
+                    // 8-s of column 0, exactly where this address points -- only DC (s = 0) is special
+                    if (s == 0 && t == 0) B = A;
+                } else {
+                    B = ex.ld(e, (L - f) & (L - 1));
+                }
                 // U = (A + conj B)/2, V = (A - conj B)/(2i); the factors 1/2 are applied at the end
                 const T ur = A.x + B.x, ui = A.y - B.y, vr = A.y + B.y, vi = B.x - A.x;
                 acc[s][0] += ur * ur + ui * ui;
