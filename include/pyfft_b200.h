@@ -162,9 +162,10 @@ int pyfft_welch_correlation(const double* spec, int32_t nfft, int32_t ncol,
  *     out[c][k][b] = bin_scale[b] * FFT(window * detrended segment)[bin_first + b (mod nfft)]
  * bin_scale (double[nbins]) carries the reference's sqrt(2)/S1/sqrt(ENBW)
  * factors (or NULL = 1).  power_out != 0 writes |.|^2 * bin_scale[b] as a real
- * array instead (specgram).  out_transposed != 0 stores [c][b][k] (specgram's
- * (wl, nWindows) layout).  Output type follows `dtype` (complex64/128, or
- * float/double for power_out).
+ * array instead (specgram).  Output type follows `dtype` (complex64/128, or float/double
+ * for power_out), layout [c][k][b].  Real input packs two consecutive segments into one
+ * complex transform.  complex_in: coef holds the real/imaginary means at coef[4c], coef[4c+2]
+ * (mean detrend only).
  * pseg (optional, double[nch][seg_count]) receives
  *     sum_n g_n - (g_0 + g_{L-1})/2,  g = |window*x|^2     (trapezoid rule core of :2174)
  * detrend_per_segment != 0 removes the segment's own mean (detrendwin=True,
@@ -174,8 +175,7 @@ int pyfft_stft(int dtype, int32_t complex_in, const void* x, int64_t ch_stride, 
                const pyfft_record_map* map, const pyfft_segmentation* seg,
                const void* window, const double* coef, int32_t detrend_per_segment,
                int32_t bin_first, int32_t nbins, const double* bin_scale,
-               int32_t power_out, int32_t out_transposed,
-               void* out, double* pseg, void* stream);
+               int32_t power_out, void* out, double* pseg, void* stream);
 
 /* ------------------------------------------------------------------------- *
  * Spectral products of materialised STFTs (the non-fused path; used for

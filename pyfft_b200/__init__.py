@@ -11,4 +11,6 @@ from .windows import windows            # noqa: F401
 from .fft_analysis import (fft_pwelch, fftanal, fftinfosc, Cxy_Cxy2, detrend_none,  # noqa: F401
                            detrend_mean, detrend_linear)
 
+from .spectrogram import stft, specgram  # noqa: F401,E402
+
 __version__ = "0.1.0"

@@ -26,14 +26,4 @@ int pyfft_csm_accumulate(int, const void*, int64_t, int32_t, const pyfft_record_
                          const void*, const double*, double*, void*, int64_t, void*) {
     return fail(PYFFT_EUNSUPPORTED, "pyfft_csm_accumulate (K4) is not implemented yet");
 }
-int pyfft_stft(int, int32_t, const void*, int64_t, int32_t, const pyfft_record_map*, const pyfft_segmentation*,
-               const void*, const double*, int32_t, int32_t, int32_t, const double*, int32_t, int32_t, void*,
-               double*, void*) {
-    return fail(PYFFT_EUNSUPPORTED, "pyfft_stft (K2) is not implemented yet");
-}
-int pyfft_stft_products(int, const void*, const void*, int32_t, int64_t, int32_t, int32_t, double*, double*,
-                        double*, void*) {
-    return fail(PYFFT_EUNSUPPORTED, "pyfft_stft_products is not implemented yet");
-}
-
 }  // extern "C"

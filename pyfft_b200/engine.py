@@ -175,3 +175,73 @@ class WelchPlan(object):
 
 def record_map(nsig, i0, reflect, src_base, src_len):
     return RecordMap(int(nsig), int(i0), int(reflect), int(src_base), int(src_len))
+
+
+# --------------------------------------------------------------------------- #
+# K2: STFT with materialised per-segment spectra
+# --------------------------------------------------------------------------- #
+
+def detrend_coefficients(x, rmap, mode, precision, nsig, group=None, j_span=None):
+    """Global trend coefficients (a, b) per channel of a (C, n) device tensor -> double[2C]
+    device tensor or None.  x(j) - (a + b j) is what pybaseutils.detrend_mean/linear remove
+    (fft_analysis.py:2147-2149)."""
+    if mode == _lib.DETREND_NONE:
+        return None
+    nch = x.shape[0]
+    stats = torch.zeros(2 * nch, dtype=torch.float64, device=x.device)
+    j0, j1 = (0, nsig) if j_span is None else j_span
+    check(lib.pyfft_detrend_stats(_CODE[precision], _ptr(x), x.stride(0), nch, C.byref(rmap), j0, j1,
+                                  _ptr(stats), _stream()))
+    if group is not None:
+        torch.distributed.all_reduce(stats, group=group)
+    coef = torch.empty_like(stats)
+    check(lib.pyfft_detrend_coef(mode, _ptr(stats), nch, nsig, _ptr(coef), _stream()))
+    return coef
+
+
+def stft(x, rmap, nfft, hop, seg_first, seg_count, window, precision, coef=None,
+         per_segment=False, bin_first=0, nbins=None, bin_scale=None, power_out=False,
+         want_pseg=False):
+    """x: (C, n) real device tensor (or complex, interleaved) -> (out [C][K][nbins], pseg [C][K] | None).
+
+    out is complex64/128 (or float32/64 when power_out) following `precision`."""
+    dev = x.device
+    cplx = x.is_complex()
+    nch = x.shape[0]
+    nbins = nfft if nbins is None else int(nbins)
+    win = torch.from_numpy(np.ascontiguousarray(np.asarray(window, dtype=np.float64))).to(
+        dev, _TORCH_REAL[precision])
+    odt = _TORCH_REAL[precision] if power_out else _TORCH_CPLX[precision]
+    out = torch.empty((nch, int(seg_count), nbins), dtype=odt, device=dev)
+    pseg = torch.zeros((nch, int(seg_count)), dtype=torch.float64, device=dev) if want_pseg else None
+    scale = None
+    if bin_scale is not None:
+        scale = torch.from_numpy(np.ascontiguousarray(np.asarray(bin_scale, dtype=np.float64))).to(dev)
+        if scale.numel() != nbins:
+            raise ValueError("bin_scale needs nbins entries")
+    seg = Segmentation(int(nfft), int(hop), int(seg_first), int(seg_count))
+    xr = torch.view_as_real(x) if cplx else x
+    stride = x.stride(0)                                     # elements (complex elements for complex input)
+    check(lib.pyfft_stft(_CODE[precision], 1 if cplx else 0, _ptr(xr), stride * (2 if cplx else 1), nch,
+                         C.byref(rmap), C.byref(seg), _ptr(win), _ptr(coef), 1 if per_segment else 0,
+                         int(bin_first), nbins, _ptr(scale), 1 if power_out else 0, _ptr(out), _ptr(pseg),
+                         _stream()))
+    return out, pseg
+
+
+def stft_products(X, Y, conj_x, precision):
+    """X [K][nb], Y [nch][K][nb] (or None) complex device tensors -> double sums
+    (sxx [nb], syy [nch][nb], sxy [nch][nb] complex128) over the K segments."""
+    K, nb = X.shape
+    dev = X.device
+    sxx = torch.empty(nb, dtype=torch.float64, device=dev)
+    if Y is None:
+        check(lib.pyfft_stft_products(_CODE[precision], _ptr(X), None, 1, K, nb, 1 if conj_x else 0,
+                                      _ptr(sxx), None, None, _stream()))
+        return sxx, None, None
+    nch = Y.shape[0]
+    syy = torch.empty((nch, nb), dtype=torch.float64, device=dev)
+    sxy = torch.empty((nch, nb), dtype=torch.complex128, device=dev)
+    check(lib.pyfft_stft_products(_CODE[precision], _ptr(X), _ptr(Y), nch, K, nb, 1 if conj_x else 0,
+                                  _ptr(sxx), _ptr(syy), _ptr(sxy), _stream()))
+    return sxx, syy, sxy

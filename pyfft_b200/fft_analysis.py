@@ -191,6 +191,43 @@ def _host(t):
     return t.cpu().numpy()
 
 
+def _make_segment_loader(sigx, sigy, ntv, plan, win, mode, precision, dev, onesided, scale):
+    """Per-segment fields of fftinfo (fft_analysis.py:461-481) are produced on first access by
+    the STFT kernel instead of on every call: Xfft_seg (Navr, nfft), Yfft_seg (nch, Navr, nfft)
+    raw transforms; Pxx_seg (Navr, nf), Pyy_seg / Pxy_seg (nch, Navr, nf) scaled like the
+    averaged spectra; phixy_seg; varphi_seg."""
+    def load():
+        nw, K = plan.nwins, plan.Navr
+        hop = nw - plan.noverlap
+        with torch.cuda.device(dev):
+            x = _eng.to_device(sigx, precision, dev).reshape(1, -1).contiguous()
+            y = _eng.channels_first(_eng.to_device(sigy, precision, dev), ntv)
+            rmap = _eng.record_map(plan.nana, plan.i0, nw - 1 if plan.reflect else 0, 0, x.shape[1])
+            out = {}
+            specs = []
+            for sig in (x, y):
+                coef = _eng.detrend_coefficients(sig, rmap, mode, precision, plan.nana)
+                S, _ = _eng.stft(sig, rmap, nw, hop, 0, K, win, precision, coef=coef)
+                specs.append(S.to(torch.complex128))
+            X, Y = specs[0][0], specs[1]                               # (K, nfft), (nch, K, nfft)
+            F = plan.Nnyquist if onesided else nw
+            wgt = torch.full((F,), float(scale), dtype=torch.float64, device=dev)
+            if onesided:
+                wgt[1:-1] *= 2.0                                       # :414-416
+                pick = lambda a: a[..., :F]
+            else:
+                pick = lambda a: torch.fft.fftshift(a, dim=-1)         # index shuffle only (:425-427)
+            out["Xfft_seg"] = _host(X)
+            out["Yfft_seg"] = _host(Y)
+            out["Pxx_seg"] = _host(pick(X * X.conj()) * wgt)
+            out["Pyy_seg"] = _host(pick(Y * Y.conj()) * wgt)
+            out["Pxy_seg"] = _host(pick(Y * X.conj()[None]) * wgt)     # Y conj(X) (:393)
+        out["phixy_seg"] = np.angle(out["Pxy_seg"])
+        out["varphi_seg"] = np.zeros_like(out["phixy_seg"])
+        return out
+    return load
+
+
 def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
                windowfunction=None, useMLAB=None, plotit=None, verbose=None,
                detrend_style=None, onesided=None, **kwargs):
@@ -334,6 +371,8 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
     fftinfo.Pxx, fftinfo.Pyy, fftinfo.Pxy = Pxx.copy(), Pyy.copy(), Pxy.copy()
     fftinfo.Cxy, fftinfo.Cxy2, fftinfo.phi_xy = Cxy.copy(), Cxy2.copy(), phi_xy.copy()
     fftinfo.precision = precision
+    fftinfo._segment_loader = _make_segment_loader(sigx, sigy, ntv, plan, win, mode, precision, dev,
+                                                   bool(onesided), scale)
     if return_device:
         return (torch.from_numpy(freq).to(dev), res["Pxy"], res["Pxx"], res["Pyy"], res["Cxy"],
                 res["phi_xy"], fftinfo)
@@ -524,3 +563,14 @@ class fftanal(Struct):
         if detrend_style < 0:
             return detrend_linear
         return detrend_none
+
+
+# the STFT half of the object API lives in _fftanal_stft.py
+from . import _fftanal_stft as _stft_api  # noqa: E402
+
+for _name, _fn in _stft_api.METHODS.items():
+    setattr(fftanal, _name, _fn)
+
+
+fftanal.fftshift = lambda self, sig, axes=None: np.fft.fftshift(sig, axes=self.axes if axes is None else axes)
+fftanal.ifftshift = lambda self, sig, axes=None: np.fft.ifftshift(sig, axes=self.axes if axes is None else axes)
