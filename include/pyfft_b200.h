@@ -198,11 +198,15 @@ int pyfft_stft_products(int dtype, const void* X, const void* Y, int32_t nch, in
  * next power of two >= 2n-1 internally.
  * pyfft_hilbert: in = batch real records [batch][n]; analytic (complex, may be
  *   NULL) and/or envelope (|z|, real, may be NULL) of `dtype`.
- * pyfft_xcorr: for each pair p: out[p][0 .. 2n-2] = correlate(x_p - mean,
- *   y_p - mean, 'full') * norm_p, norm_p = 1/(n*std_x*std_y) when normalise != 0
- *   (ccf.py:74-76) else 1; x_p = x + p*x_stride (x_stride may be 0 to reuse one
- *   reference channel).
- * workspace sizes from pyfft_bigfft_workspace_bytes(dtype, nfft_padded, batch).
+ * pyfft_xcorr: for each pair p: out[p][0 .. 2n-2] = correlate(x_p - mean, y_p - mean, 'full')
+ *   * norm_p (numpy.correlate lag order, ccf.py:69-74).  normalise = 1: means removed and
+ *   norm_p = 1/(n*std_x*std_y) (ccf.ccf, ccf.py:74-76); normalise = 2: means removed,
+ *   norm_p = 1; normalise = 0: raw correlation, no mean removal (fftcorr /
+ *   cross_correlation_fft, ccf.py:239-303).  x_p = x + p*x_stride (x_stride may be 0 to
+ *   reuse one reference channel); out is real of `dtype`, [pairs][2n-1].
+ *   workspace: pyfft_bigfft_workspace_bytes(dtype, L, pairs + (x_stride ? pairs : 1)) with
+ *   L = the power of two >= 2n-1 (at least 16).
+ * pyfft_hilbert needs pyfft_bigfft_workspace_bytes(dtype, n, batch) only when analytic is NULL.
  * ------------------------------------------------------------------------- */
 int64_t pyfft_bigfft_workspace_bytes(int dtype, int64_t nfft, int32_t batch);
 

@@ -12,5 +12,7 @@ from .fft_analysis import (fft_pwelch, fftanal, fftinfosc, Cxy_Cxy2, detrend_non
                            detrend_mean, detrend_linear)
 
 from .spectrogram import stft, specgram  # noqa: F401,E402
+from .hilbert import hilbert, hilbert_1d  # noqa: F401,E402
+from .ccf import ccf, ccf_sh, fftcorr, cross_correlation_fft  # noqa: F401,E402
 
 __version__ = "0.1.0"

@@ -72,22 +72,24 @@ int check_seg(const pyfft_segmentation* seg, int min_log2, int max_log2, int* lo
 }
 
 static std::mutex g_tw_mutex;
-static std::map<std::tuple<int, int, int64_t>, void*> g_tw_cache;
+static std::map<std::tuple<int, int, int64_t, int64_t, int64_t>, void*> g_tw_cache;
 
-const void* twiddle_table(int dtype, int64_t L, int* status) {
+// table[k] = exp(-2 pi i k step / M), k = 0 .. count-1
+const void* twiddle_table_ex(int dtype, int64_t M, int64_t step, int64_t count, int* status) {
     *status = PYFFT_OK;
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess) { *status = fail(PYFFT_ECUDA, "cudaGetDevice failed"); return nullptr; }
     std::lock_guard<std::mutex> lock(g_tw_mutex);
-    auto key = std::make_tuple(dev, dtype, L);
+    auto key = std::make_tuple(dev, dtype, M, step, count);
     auto it = g_tw_cache.find(key);
     if (it != g_tw_cache.end()) return it->second;
     size_t esz = dtype == PYFFT_F64 ? 16 : 8;
-    std::vector<unsigned char> host(esz * (size_t)L);
+    std::vector<unsigned char> host(esz * (size_t)count);
     const long double two_pi = 6.283185307179586476925286766559005768L;
-    for (int64_t k = 0; k < L; ++k) {
-        // octant symmetry is not needed at long-double accuracy
-        long double a = -two_pi * (long double)k / (long double)L;
+    for (int64_t k = 0; k < count; ++k) {
+        // the angle is reduced exactly in integers before the long-double evaluation
+        const int64_t j = (int64_t)(((__int128)k * step) % M);
+        long double a = -two_pi * (long double)j / (long double)M;
         long double c = cosl(a), s = sinl(a);
         if (dtype == PYFFT_F64) {
             double* p = reinterpret_cast<double*>(host.data()) + 2 * k;
@@ -108,6 +110,8 @@ const void* twiddle_table(int dtype, int64_t L, int* status) {
     g_tw_cache[key] = d;
     return d;
 }
+
+const void* twiddle_table(int dtype, int64_t L, int* status) { return twiddle_table_ex(dtype, L, 1, L, status); }
 
 void free_twiddles() {
     std::lock_guard<std::mutex> lock(g_tw_mutex);

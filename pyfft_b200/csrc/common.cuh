@@ -58,6 +58,8 @@ inline int ilog2(int64_t v) {
 // per (device, L, dtype).  First use of an L allocates and copies
 // synchronously -- do that (one warm-up call) outside CUDA graph capture.
 const void* twiddle_table(int dtype, int64_t L, int* status);
+// exp(-2 pi i k step / M), k = 0..count-1 (two-level tables of the long transforms)
+const void* twiddle_table_ex(int dtype, int64_t M, int64_t step, int64_t count, int* status);
 void free_twiddles();
 
 int device_sm_count();

@@ -245,3 +245,61 @@ def stft_products(X, Y, conj_x, precision):
     check(lib.pyfft_stft_products(_CODE[precision], _ptr(X), _ptr(Y), nch, K, nb, 1 if conj_x else 0,
                                   _ptr(sxx), _ptr(syy), _ptr(sxy), _stream()))
     return sxx, syy, sxy
+
+
+# --------------------------------------------------------------------------- #
+# K3b: long transforms
+# --------------------------------------------------------------------------- #
+
+def _is_pow2(n):
+    return n >= 1 and (n & (n - 1)) == 0
+
+
+def hilbert(u, precision, want_analytic=True, want_envelope=False):
+    """u: (batch, n) real device tensor, n a power of two -> (analytic complex | None,
+    envelope real | None) device tensors (hilbert.py:22-67)."""
+    batch, n = u.shape
+    dev = u.device
+    u = u.contiguous()
+    z = torch.empty((batch, n), dtype=_TORCH_CPLX[precision], device=dev) if want_analytic else None
+    env = torch.empty((batch, n), dtype=_TORCH_REAL[precision], device=dev) if want_envelope else None
+    ws, wsb = None, 0
+    if z is None:
+        wsb = check(lib.pyfft_bigfft_workspace_bytes(_CODE[precision], n, batch))
+        ws = torch.empty(wsb, dtype=torch.uint8, device=dev)
+    check(lib.pyfft_hilbert(_CODE[precision], _ptr(u), n, batch, _ptr(z), _ptr(env), _ptr(ws), wsb,
+                            _stream()))
+    return z, env
+
+
+def xcorr(x, y, precision, normalise=1):
+    """x: (n,) or (pairs, n); y: (pairs, n) real device tensors -> (pairs, 2n-1) real device
+    tensor in numpy.correlate 'full' order (ccf.py:66-77)."""
+    pairs, n = y.shape
+    dev = y.device
+    y = y.contiguous()
+    x = x.contiguous()
+    shared = x.dim() == 1 or x.shape[0] == 1
+    if not shared and x.shape != y.shape:
+        raise ValueError("x must be one record or one record per pair")
+    L = 16
+    while L < 2 * n - 1:
+        L *= 2
+    wsb = check(lib.pyfft_bigfft_workspace_bytes(_CODE[precision], L, pairs + (1 if shared else pairs)))
+    ws = torch.empty(wsb, dtype=torch.uint8, device=dev)
+    out = torch.empty((pairs, 2 * n - 1), dtype=_TORCH_REAL[precision], device=dev)
+    check(lib.pyfft_xcorr(_CODE[precision], _ptr(x), 0 if shared else n, _ptr(y), n, n, pairs,
+                          int(normalise), _ptr(out), _ptr(ws), wsb, _stream()))
+    return out
+
+
+def fft_c2c(z, precision, inverse=False):
+    """(batch, n) complex device tensor, n a power of two -> numpy.fft.fft / ifft along the last axis."""
+    batch, n = z.shape
+    z = z.contiguous()
+    out = torch.empty_like(z)
+    wsb = check(lib.pyfft_bigfft_workspace_bytes(_CODE[precision], n, batch))
+    ws = torch.empty(wsb, dtype=torch.uint8, device=z.device)
+    check(lib.pyfft_fft_c2c(_CODE[precision], _ptr(z), _ptr(out), n, batch, 1 if inverse else 0, _ptr(ws),
+                            wsb, _stream()))
+    return out

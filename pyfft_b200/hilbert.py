@@ -1,0 +1,68 @@
+"""Drop-in for the reference's hilbert.py: the analytic signal through one long forward FFT,
+the bin mask and one long inverse FFT, all inside pyfft_hilbert (K3b).
+
+Same names, arguments and return values as hilbert.py:22-112; the extra keywords
+(``precision``, ``device``, ``return_device``, ``envelope``) default to the reference's
+behaviour.  Lengths that are not powers of two raise NotImplementedError (no CPU fallback).
+"""
+import numpy as np
+import torch
+
+from . import engine
+
+
+def _prepare(uin, nfft, axes, precision, device):
+    dev = engine.require_cuda(device)
+    if not isinstance(uin, torch.Tensor):
+        uin = np.atleast_1d(np.asarray(uin))
+    prec = engine.resolve_precision(precision, uin)
+    u = engine.to_device(uin, prec, dev)
+    if u.dim() == 0:
+        u = u[None]
+    if u.dim() > 2:
+        raise NotImplementedError("hilbert: at most 2-D input")
+    ax = axes % u.dim()
+    if u.dim() == 2 and ax == 0:
+        u = u.t()
+    u2 = u.reshape(-1, u.shape[-1])
+    n = u2.shape[1]
+    if nfft is None:
+        nfft = n
+    nfft = int(nfft)
+    if nfft < n:                                    # numpy.fft.fft(u, n=nfft) truncates ...
+        u2 = u2[:, :nfft]
+    elif nfft > n:                                  # ... or zero-pads (hilbert.py:54)
+        u2 = torch.nn.functional.pad(u2, (0, nfft - n))
+    if not engine._is_pow2(nfft) or nfft < 16:
+        raise NotImplementedError("hilbert: nfft = %d is not a power of two >= 16 (GPU path only)" % nfft)
+    return u2, prec, (u.dim() == 2 and ax == 0), u.dim()
+
+
+def hilbert(uin, nfft=None, axes=-1, precision=None, device=None, return_device=False, envelope=False):
+    """Analytic signal u + j H[u] (hilbert.py:22-67).  ``envelope=True`` returns |z| instead
+    (fused into the last pass; the complex signal is never written)."""
+    u2, prec, transposed, ndim = _prepare(uin, nfft, axes, precision, device)
+    z, env = engine.hilbert(u2, prec, want_analytic=not envelope, want_envelope=envelope)
+    out = env if envelope else z
+    if transposed:
+        out = out.t()
+    if ndim == 1:
+        out = out[0]
+    if return_device:
+        return out.squeeze()
+    res = out.cpu().numpy()
+    res = res.astype(np.float64 if envelope else np.complex128)
+    return res.squeeze()                             # hilbert.py:67
+
+
+def hilbert_1d(uin, nfft=None, precision=None, device=None, return_device=False):
+    """hilbert.py:70-112 -- same mask written as an array; 1-D input."""
+    if not isinstance(uin, torch.Tensor):
+        uin = np.atleast_1d(np.asarray(uin))
+    if uin.ndim != 1:
+        raise ValueError("hilbert_1d expects a 1-D signal")
+    u2, prec, _, _ = _prepare(uin, nfft, -1, precision, device)
+    z, _ = engine.hilbert(u2, prec)
+    if return_device:
+        return z[0]
+    return z[0].cpu().numpy().astype(np.complex128)

@@ -1,0 +1,128 @@
+"""GPU parity of K3b (long transforms): hilbert / hilbert_1d against the reference's golden
+outputs, ccf against the direct O(N^2) definition (ccf.py:66-77) and the oracle's FFT identity,
+pyfft_fft_c2c against numpy.fft for every pass decomposition (1, 2 and 3 passes)."""
+import numpy as np
+import pytest
+
+from conftest import load_golden, relerr
+
+pytestmark = pytest.mark.gpu
+
+TOLZ = {"fp64": 1e-12, "fp32": 2e-6}
+
+
+@pytest.mark.parametrize("precision", ["fp64", "fp32"])
+def test_hilbert_matches_reference_golden(precision, cuda_device):
+    from pyfft_b200 import hilbert, hilbert_1d
+    g = load_golden("hilbert")
+    for n in (32, 1024, 4096):
+        u = g["u_%d" % n] if precision == "fp64" else g["u_%d" % n].astype(np.float32)
+        z = hilbert(u, precision=precision)
+        assert z.shape == (n,) and z.dtype == np.complex128
+        assert relerr(z, g["z_%d" % n]) <= TOLZ[precision]
+        assert relerr(hilbert_1d(u, precision=precision), g["z1d_%d" % n]) <= TOLZ[precision]
+    ub = g["u_batch"] if precision == "fp64" else g["u_batch"].astype(np.float32)
+    assert relerr(hilbert(ub, precision=precision), g["z_batch"]) <= TOLZ[precision]
+    # axis 0 of a time-major array
+    assert relerr(hilbert(ub.T.copy(), axes=0, precision=precision), g["z_batch"].T) <= TOLZ[precision]
+
+
+def test_hilbert_non_power_of_two_fails_loudly(cuda_device):
+    from pyfft_b200 import hilbert
+    g = load_golden("hilbert")
+    with pytest.raises(NotImplementedError):
+        hilbert(g["u_33"])
+    with pytest.raises(NotImplementedError):
+        hilbert(g["u_1000"])
+
+
+@pytest.mark.parametrize("log2n", [14, 19, 22])
+def test_hilbert_long_records_and_envelope(log2n, cuda_device):
+    """2- and 3-pass decompositions against the oracle; the fused envelope equals |analytic|."""
+    from oracle import restatement as R
+    from pyfft_b200 import hilbert
+    n = 1 << log2n
+    rng = np.random.default_rng(40 + log2n)
+    t = np.arange(n) / 1.0e6
+    u = (1 + 0.5 * np.sin(2 * np.pi * 1e3 * t)) * np.sin(2 * np.pi * 1e5 * t) + 0.05 * rng.standard_normal(n)
+    ref = R.hilbert(u)
+    assert relerr(hilbert(u), ref) <= 1e-12
+    u32 = u.astype(np.float32)
+    ref32 = R.hilbert(u32.astype(np.float64))
+    z32 = hilbert(u32)
+    assert relerr(z32, ref32) <= 1e-5
+    env = hilbert(u32, envelope=True)
+    assert env.dtype == np.float64 and relerr(env, np.abs(ref32)) <= 1e-5
+
+
+@pytest.mark.parametrize("precision", ["fp64", "fp32"])
+def test_ccf_matches_direct_definition(precision, cuda_device):
+    from oracle import restatement as R
+    from pyfft_b200 import ccf
+    rng = np.random.default_rng(7)
+    fs, n = 1e5, 2048                                   # ccf_test recipe (ccf.py:139-148)
+    t = np.arange(n) / fs
+    x1 = np.sin(2 * np.pi * 1e3 * t) + rng.standard_normal(n) + 3.0
+    x2 = np.sin(2 * np.pi * 1e3 * t - 50 * np.pi / 180) + rng.standard_normal(n) - 1.0
+    if precision == "fp32":
+        x1, x2 = x1.astype(np.float32), x2.astype(np.float32)
+    tau_ref, co_ref = R.ccf_direct(x1.astype(np.float64), x2.astype(np.float64), fs)
+    tau, co = ccf(x1, x2, fs, precision=precision)
+    assert co.shape == (2 * n - 1,) and np.array_equal(tau, tau_ref)
+    tol = 1e-12 if precision == "fp64" else 2e-6
+    assert np.max(np.abs(co - co_ref)) <= tol
+    # odd length, and several channels against one reference in a single call
+    x3 = rng.standard_normal((3, 1001)) + np.array([[0.0], [5.0], [-2.0]])
+    x0 = rng.standard_normal(1001)
+    _, cm = ccf(x0, x3, fs)
+    for c in range(3):
+        assert np.max(np.abs(cm[c] - R.ccf_direct(x0, x3[c], fs)[1])) <= 1e-12
+    # zero lag of an auto-ccf is 1
+    assert abs(ccf(x0, x0, fs)[1][1000] - 1.0) < 1e-12
+
+
+def test_ccf_long_record_peak_at_known_delay(cuda_device):
+    """2^21 samples (padded transform 2^22, three passes): FFT identity oracle + known delay."""
+    from oracle import restatement as R
+    from pyfft_b200 import ccf
+    rng = np.random.default_rng(8)
+    n, d = 1 << 21, 37 * 5
+    s = rng.standard_normal(n + d)
+    x1 = s[d:] + 0.1 * rng.standard_normal(n)
+    x2 = s[:n] + 0.1 * rng.standard_normal(n)          # x2 lags x1 by d samples
+    tau_ref, co_ref = R.ccf_fft(x1, x2, 1.0e6)
+    tau, co = ccf(x1, x2, 1.0e6)
+    assert np.max(np.abs(co - co_ref)) <= 1e-12
+    assert np.argmax(co) == np.argmax(co_ref)
+    _, co32 = ccf(x1.astype(np.float32), x2.astype(np.float32), 1.0e6)
+    assert np.max(np.abs(co32 - co_ref)) <= 1e-5
+
+
+def test_fftcorr_and_cross_correlation_fft(cuda_device):
+    from pyfft_b200 import cross_correlation_fft, fftcorr
+    rng = np.random.default_rng(9)
+    x, y = rng.standard_normal(256), rng.standard_normal(256)
+    ref = np.fft.ifft(np.conj(np.fft.fft(x)) * np.fft.fft(y))          # ccf.py:239-248
+    assert relerr(fftcorr(x, y), ref) <= 1e-12
+    for mode in ("full", "same", "valid"):
+        assert relerr(cross_correlation_fft(x, y, mode=mode), np.correlate(x, y, mode)) <= 1e-12
+
+
+@pytest.mark.parametrize("precision", ["fp64", "fp32"])
+@pytest.mark.parametrize("log2n", [4, 7, 9, 10, 13, 18, 19, 21])
+def test_fft_c2c_matches_numpy(precision, log2n, cuda_device):
+    import torch
+    from pyfft_b200 import engine
+    n = 1 << log2n
+    batch = 3 if log2n <= 13 else 1
+    rng = np.random.default_rng(log2n)
+    z = rng.standard_normal((batch, n)) + 1j * rng.standard_normal((batch, n))
+    if precision == "fp32":
+        z = z.astype(np.complex64)
+    zd = torch.from_numpy(z).to(cuda_device)
+    tol = 1e-12 if precision == "fp64" else 3e-6
+    ref = np.fft.fft(z.astype(np.complex128), axis=-1)
+    out = engine.fft_c2c(zd, precision).cpu().numpy()
+    assert relerr(out, ref) <= tol
+    back = engine.fft_c2c(torch.from_numpy(ref.astype(z.dtype)).to(cuda_device), precision, inverse=True)
+    assert relerr(back.cpu().numpy(), z) <= tol
