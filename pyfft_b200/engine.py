@@ -303,3 +303,26 @@ def fft_c2c(z, precision, inverse=False):
     check(lib.pyfft_fft_c2c(_CODE[precision], _ptr(z), _ptr(out), n, batch, 1 if inverse else 0, _ptr(ws),
                             wsb, _stream()))
     return out
+
+
+# --------------------------------------------------------------------------- #
+# K4: multi-channel cross-spectral matrix
+# --------------------------------------------------------------------------- #
+
+def csm_accumulate(x, rmap, nfft, hop, seg_first, seg_count, window, precision, coef=None, G=None):
+    """x: (C, n) real device tensor -> G (nfft/2+1, C, C) complex128 device tensor with the
+    unscaled sums  G[f, i, j] += sum_k X_j conj(X_i)  (fft_analysis.py:393 per channel pair)."""
+    dev = x.device
+    nch = x.shape[0]
+    nb = nfft // 2 + 1
+    if G is None:
+        G = torch.zeros((nb, nch, nch), dtype=torch.complex128, device=dev)
+    win = torch.from_numpy(np.ascontiguousarray(np.asarray(window, dtype=np.float64))).to(
+        dev, _TORCH_REAL[precision])
+    seg = Segmentation(int(nfft), int(hop), int(seg_first), int(seg_count))
+    need = check(lib.pyfft_csm_workspace_bytes(_CODE[precision], C.byref(seg), nch))
+    ws = torch.empty(need, dtype=torch.uint8, device=dev)
+    check(lib.pyfft_csm_accumulate(_CODE[precision], _ptr(x), x.stride(0), nch, C.byref(rmap), C.byref(seg),
+                                   _ptr(win), _ptr(coef), _ptr(torch.view_as_real(G)), _ptr(ws), need,
+                                   _stream()))
+    return G

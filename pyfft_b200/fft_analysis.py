@@ -379,6 +379,66 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
     return freq, Pxy, Pxx, Pyy, Cxy, phi_xy, fftinfo
 
 
+def cross_spectral_matrix(tvec, sig, tbounds=None, Navr=None, windowoverlap=None, windowfunction=None,
+                          detrend_style=None, **kwargs):
+    """All-pairs cross-power spectral density of a multi-channel record in ONE pass.
+
+    The reference builds this matrix by calling fft_pwelch once per reference channel with
+    every channel as sigy (HeatPulse_Funcs.py:576-583); ``G[f, i, j]`` equals the ``Pxy[f, j]``
+    of the call with ``sigx = sig[:, i]`` -- one-sided, Nyquist bin dropped, x2 on interior
+    bins, scaled by 1/(S1^2 ENBW), mean over segments (fft_analysis.py:393-446).  Segmentation,
+    window, reflect padding and global detrend follow fft_pwelch exactly.
+
+    Returns ``(freq, G)`` with G complex128 of shape (Nnyquist, nch, nch).  ``group``: a
+    torch.distributed process group -- segments are sharded across its ranks and the partial
+    matrices summed by one all-reduce.
+    """
+    precision = kwargs.pop("precision", None)
+    device = kwargs.pop("device", None)
+    group = kwargs.pop("group", None)
+    return_device = kwargs.pop("return_device", False)
+    if detrend_style is None:
+        detrend_style = 1
+    ntv = len(tvec)
+    precision = _eng.resolve_precision(precision, sig)
+    dev = _eng.require_cuda(device)
+    with torch.cuda.device(dev):
+        x = _eng.channels_first(_eng.to_device(sig, precision, dev), ntv)
+        nch, nx = x.shape
+        plan = _Plan(tvec, nx, nx, tbounds, Navr, windowoverlap, windowfunction, kwargs)
+        nwins, K = plan.nwins, plan.Navr
+        if nwins & (nwins - 1) or nwins < 16 or nwins > 8192:
+            raise NotImplementedError("nwins = %d: the GPU path needs a power-of-two window of 16..8192 "
+                                      "samples" % nwins)
+        win = windows(plan.windowfunction, nwins=nwins, verbose=False)
+        S1, S2, _, ENBW = fftanal._getNorms(win, plan.Nnyquist, plan.Fs)
+        refl = nwins - 1 if plan.reflect else 0
+        rmap = _eng.record_map(plan.nana, plan.i0, refl, 0, nx)
+        hop = nwins - plan.noverlap
+        if (K - 1) * hop + nwins > plan.nana:
+            raise ValueError("operands could not be broadcast together: segment %d runs past the "
+                             "analysed record" % (K - 1))
+        mode = _lib.DETREND_MEAN if detrend_style > 0 else (_lib.DETREND_LINEAR if detrend_style < 0
+                                                            else _lib.DETREND_NONE)
+        rank, world = 0, 1
+        if group is not None:
+            rank, world = torch.distributed.get_rank(group), torch.distributed.get_world_size(group)
+        lp = _dist.local_plan(K, hop, nwins, plan.nana, plan.i0, refl, rank, world)
+        coef = _eng.detrend_coefficients(x, rmap, mode, precision, plan.nana, group=group,
+                                         j_span=lp["stats_span"])
+        G = _eng.csm_accumulate(x, rmap, nwins, hop, lp["k0"], lp["k1"] - lp["k0"], win, precision, coef=coef)
+        if group is not None:
+            torch.distributed.all_reduce(torch.view_as_real(G), group=group)
+        F = plan.Nnyquist
+        wgt = torch.full((F,), 1.0 / (S1 ** 2) / ENBW / K, dtype=torch.float64, device=dev)
+        wgt[1:-1] *= 2.0                                           # :414-416
+        G = G[:F] * wgt[:, None, None]
+    freq = np.fft.fftfreq(nwins, 1.0 / plan.Fs)[:F]
+    if return_device:
+        return torch.from_numpy(freq).to(dev), G
+    return freq, _host(G)
+
+
 # --------------------------------------------------------------------------- #
 # class fftanal -- segmentation statics now, the object API is completed by
 # pyfft_b200/stft.py (attached below) once K2 is available.
