@@ -120,6 +120,38 @@ int pyfft_welch_accumulate(int dtype, const void* x, const void* y, int64_t y_st
                            void* stream);
 
 /* ------------------------------------------------------------------------- *
+ * K1, mean detrend fused (one pass over HBM instead of K0 + K1)
+ * replaces: the same lines as pyfft_welch_accumulate plus the global mean removal
+ *           of fft_analysis.py:356-357, without a separate statistics pass.
+ * est = double[2*(nch+1)] (a, b) pairs, x first then the y channels, as written by
+ * pyfft_detrend_coef from ANY cheap estimate of the means (b ignored).  The kernel
+ * accumulates the spectra of (sample - est) into acc and, by linearity of the FFT,
+ * everything needed to move them to the exact global mean afterwards:
+ *     lin   = double[nch][4][nfft/16]   += sum_k U_k, V_k (re, im) for bins f < nfft/16
+ *     stats = double[2*(nch+1)]         stats[2c] += raw sum of the samples of analysed
+ *             indices [seg_first*hop, (seg_first+seg_count)*hop)  (same layout as
+ *             pyfft_detrend_stats, so shards and the uncovered tail add into one buffer)
+ * pyfft_welch_mean_correct then applies, with delta_c = stats[2c]/nana - est[2c] and
+ * W = FFT(window)[0 .. nfft/16) (wlow, double[nfft/16][2]):
+ *     sum|U|^2 += -2 dx Re(W* sumU) + K dx^2 |W|^2         (same for V with dy)
+ *     sumVU*   += -dx W* sumV - dy W (sumU)* + K dx dy |W|^2
+ * K = number of segments accumulated in THIS acc (apply per shard, before the
+ * all-reduce of acc; stats must already hold the whole record's sums).  Bins
+ * f >= nfft/16 are left alone: the caller must check that |W[f]|^2 is negligible
+ * there (true for every cosine-sum window; the Python host checks and otherwise
+ * uses the two-pass route).
+ * ------------------------------------------------------------------------- */
+int pyfft_welch_accumulate_mean(int dtype, const void* x, const void* y, int64_t y_stride,
+                                int32_t nch, const pyfft_record_map* map,
+                                const pyfft_segmentation* seg, const void* window,
+                                const double* est, double* acc, double* lin, double* stats,
+                                void* workspace, int64_t workspace_bytes, void* stream);
+
+int pyfft_welch_mean_correct(double* acc, const double* lin, int32_t nfft, int32_t nch,
+                             int64_t K, const double* est, const double* stats, int64_t nana,
+                             const double* wlow, void* stream);
+
+/* ------------------------------------------------------------------------- *
  * Welch finalize
  * replaces: one-/two-sided selection and doubling (fft_analysis.py:402-428),
  *           scaling by 1/S1^2/ENBW (:432-440), the mean over segments

@@ -99,6 +99,11 @@ template <typename T> struct WelchParams {
     const cpx<T>* tw;
     T* partial;     // [nch][nparts][4][L/2+1]
     int nparts;
+    // mean-fused mode (FUSE): coef holds a PROVISIONAL mean; the kernel also returns what the
+    // finalize step needs to move the result to the exact global mean by linearity
+    T* lin_partial;     // [nch][nparts][4][L/16]: sum_k U_k, V_k (re, im) for bins f < L/16
+    double* dev_sums;   // [nch+1]: sum of (sample - provisional mean) over the first `hop`
+                        // samples of every segment of this call (x first, then the y channels)
 };
 
 template <int LOG2L> struct WelchGeom {
@@ -116,7 +121,7 @@ constexpr size_t welch_smem_bytes() {
            (size_t)WelchGeom<LOG2L>::L * sizeof(T);
 }
 
-template <typename T, int LOG2L, bool SINGLE>
+template <typename T, int LOG2L, bool SINGLE, bool FUSE>
 __global__ void __launch_bounds__(WelchGeom<LOG2L>::THREADS,
                                   (sizeof(T) == 4 && WelchGeom<LOG2L>::THREADS == 256) ? 2 : 1)
 welch_pair_kernel(const WelchParams<T> p) {
@@ -149,6 +154,9 @@ welch_pair_kernel(const WelchParams<T> p) {
 
     T acc[8][4];
     T nyq[4] = {T(0), T(0), T(0), T(0)};
+    T lin[4] = {T(0), T(0), T(0), T(0)};
+    T devx = T(0), devy = T(0);
+    const int hs = (int)(p.hop / TPS), hrem = (int)(p.hop - (int64_t)hs * TPS);
 #pragma unroll
     for (int s = 0; s < 8; ++s)
 #pragma unroll
@@ -196,6 +204,20 @@ welch_pair_kernel(const WelchParams<T> p) {
                 }
                 cx0 = T(0);
                 cy0 = T(0);
+            }
+            if (FUSE) {
+                // deviations of the first `hop` samples of the segment: every analysed sample of
+                // [seg_first*hop, (seg_first+seg_count)*hop) is counted exactly once
+                if (hs == 8 && hrem == 0) {             // 50 % overlap: no predicates
+                    const T sx = ((v[0].x + v[1].x) + (v[2].x + v[3].x)) + ((v[4].x + v[5].x) + (v[6].x + v[7].x));
+                    const T sy = ((v[0].y + v[1].y) + (v[2].y + v[3].y)) + ((v[4].y + v[5].y) + (v[6].y + v[7].y));
+                    devx += sx - T(8) * cx0;
+                    devy += sy - T(8) * cy0;
+                } else {
+#pragma unroll
+                    for (int s = 0; s < 16; ++s)
+                        if (s < hs || (s == hs && t < hrem)) { devx += v[s].x - cx0; devy += v[s].y - cy0; }
+                }
             }
 #pragma unroll
             for (int s = 0; s < 16; ++s) {
@@ -246,6 +268,7 @@ welch_pair_kernel(const WelchParams<T> p) {
                 acc[s][1] += vr * vr + vi * vi;
                 acc[s][2] += vr * ur + vi * ui;      // Re V conj(U)   (fft_analysis.py:393: Y conj(X))
                 acc[s][3] += vi * ur - vr * ui;      // Im V conj(U)
+                if (FUSE && s == 0) { lin[0] += ur; lin[1] += ui; lin[2] += vr; lin[3] += vi; }
             }
             if (t == 0) {                             // Nyquist bin f = L/2 = slot 8 of thread 0; self-paired
                 const T ur = v[8].x + v[8].x, vr = v[8].y + v[8].y;
@@ -265,6 +288,51 @@ welch_pair_kernel(const WelchParams<T> p) {
 #pragma unroll
         for (int q = 0; q < 4; ++q) out[q * NBIN + L / 2] = T(0.25) * nyq[q];
     }
+    if (FUSE) {
+        T* lo = p.lin_partial + ((size_t)pair * p.nparts + part) * 4 * TPS;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) lo[q * TPS + t] = T(0.5) * lin[q];
+        double sx = (double)devx, sy = (double)devy;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            sx += __shfl_xor_sync(0xffffffffu, sx, o);
+            sy += __shfl_xor_sync(0xffffffffu, sy, o);
+        }
+        if ((threadIdx.x & 31) == 0) {
+            if (pair == 0) atomicAdd(&p.dev_sums[0], sx);
+            atomicAdd(&p.dev_sums[1 + pair], sy);
+        }
+    }
+}
+
+// stats[2c] += dev_sums[c] + count * est[2c]   (raw sum of the samples the fused kernel covered)
+__global__ void welch_raw_sums_kernel(const double* __restrict__ dev_sums, const double* __restrict__ est,
+                                      int n, double count, double* __restrict__ stats) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c < n) stats[2 * c] += dev_sums[c] + count * est[2 * c];
+}
+
+// Moves sums accumulated about a provisional mean to the exact mean m = est + delta:
+// U = U~ - dx W, V = V~ - dy W with W = FFT(window)  (bins f < nlin; negligible elsewhere,
+// checked by the caller against the window's leakage)
+__global__ void __launch_bounds__(256) welch_mean_correct_kernel(double* __restrict__ acc, const double* __restrict__ lin,
+                                                                 int nlin, int nbin, int nch, double K,
+                                                                 const double* __restrict__ est,
+                                                                 const double* __restrict__ stats, double nana,
+                                                                 const double* __restrict__ W) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= nch * nlin) return;
+    const int c = idx / nlin, f = idx - c * nlin;
+    const double dx = stats[0] / nana - est[0];
+    const double dy = stats[2 * (1 + c)] / nana - est[2 * (1 + c)];
+    const double wr = W[2 * f], wi = W[2 * f + 1], w2 = wr * wr + wi * wi;
+    const double* l = lin + (size_t)c * 4 * nlin;
+    const double sur = l[f], sui = l[nlin + f], svr = l[2 * nlin + f], svi = l[3 * nlin + f];
+    double* a = acc + (size_t)c * 4 * nbin;
+    a[f] += -2.0 * dx * (wr * sur + wi * sui) + K * dx * dx * w2;
+    a[nbin + f] += -2.0 * dy * (wr * svr + wi * svi) + K * dy * dy * w2;
+    a[2 * nbin + f] += -dx * (wr * svr + wi * svi) - dy * (wr * sur + wi * sui) + K * dx * dy * w2;
+    a[3 * nbin + f] += -dx * (wr * svi - wi * svr) - dy * (wi * sur - wr * sui);
 }
 
 // acc[pair][q][f] += sum_part partial[pair][part][q][f]
@@ -389,18 +457,21 @@ static int welch_grid_x(int64_t seg_count, int slots, int nch) {
 template <typename T, int LOG2L>
 static int launch_welch(const void* x, const void* y, int64_t y_stride, int nch, const RecMap& map,
                         const pyfft_segmentation* seg, const void* window, const double* coef_x,
-                        const double* coef_y, double* acc, void* workspace, int64_t workspace_bytes,
-                        cudaStream_t st) {
+                        const double* coef_y, double* acc, double* lin, double* stats, void* workspace,
+                        int64_t workspace_bytes, cudaStream_t st) {
     using G = WelchGeom<LOG2L>;
     constexpr bool SINGLE = welch_smem_bytes<T, LOG2L, false>() > 200 * 1024;
     constexpr size_t smem = welch_smem_bytes<T, LOG2L, SINGLE>();
+    const bool fuse = lin != nullptr;
     int status;
     const cpx<T>* tw = reinterpret_cast<const cpx<T>*>(
         twiddle_table(sizeof(T) == 8 ? PYFFT_F64 : PYFFT_F32, G::L, &status));
     if (!tw) return status;
     const int gx = welch_grid_x(seg->seg_count, G::SLOTS, nch);
     const int nparts = gx * G::SLOTS;
-    const int64_t need = (int64_t)nch * nparts * 4 * G::NBIN * (int64_t)sizeof(T);
+    const int64_t main_bytes = (int64_t)nch * nparts * 4 * G::NBIN * (int64_t)sizeof(T);
+    const int64_t lin_bytes = (int64_t)nch * nparts * 4 * G::TPS * (int64_t)sizeof(T);
+    const int64_t need = main_bytes + lin_bytes + 8 * (int64_t)(nch + 1);
     if (workspace_bytes < need || !workspace)
         return fail(PYFFT_EINVAL, "workspace too small: %lld < %lld bytes", (long long)workspace_bytes,
                     (long long)need);
@@ -419,11 +490,25 @@ static int launch_welch(const void* x, const void* y, int64_t y_stride, int nch,
     p.tw = tw;
     p.partial = static_cast<T*>(workspace);
     p.nparts = nparts;
-    auto kern = welch_pair_kernel<T, LOG2L, SINGLE>;
-    PYFFT_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<dim3(gx, nch), G::THREADS, smem, st>>>(p);
-    PYFFT_LAUNCH_OK("welch_pair_kernel");
+    p.lin_partial = reinterpret_cast<T*>(static_cast<char*>(workspace) + main_bytes);
+    p.dev_sums = reinterpret_cast<double*>(static_cast<char*>(workspace) + main_bytes + lin_bytes);
     const int per_pair = 4 * G::NBIN;
+    if (fuse) {
+        PYFFT_CUDA_OK(cudaMemsetAsync(p.dev_sums, 0, sizeof(double) * (size_t)(nch + 1), st));
+        auto kern = welch_pair_kernel<T, LOG2L, SINGLE, true>;
+        PYFFT_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        kern<<<dim3(gx, nch), G::THREADS, smem, st>>>(p);
+        PYFFT_LAUNCH_OK("welch_pair_kernel");
+        welch_reduce_kernel<T><<<dim3((4 * G::TPS + 255) / 256, nch), 256, 0, st>>>(p.lin_partial, nparts, 4 * G::TPS, lin);
+        // coef_x and coef_y are one contiguous (a, b) array: x first, then the y channels
+        welch_raw_sums_kernel<<<(nch + 1 + 127) / 128, 128, 0, st>>>(p.dev_sums, coef_x, nch + 1,
+                                                                     (double)seg->seg_count * (double)seg->hop, stats);
+    } else {
+        auto kern = welch_pair_kernel<T, LOG2L, SINGLE, false>;
+        PYFFT_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        kern<<<dim3(gx, nch), G::THREADS, smem, st>>>(p);
+        PYFFT_LAUNCH_OK("welch_pair_kernel");
+    }
     welch_reduce_kernel<T><<<dim3((per_pair + 255) / 256, nch), 256, 0, st>>>(p.partial, nparts, per_pair, acc);
     PYFFT_LAUNCH_OK("welch_reduce_kernel");
     return PYFFT_OK;
@@ -432,10 +517,10 @@ static int launch_welch(const void* x, const void* y, int64_t y_stride, int nch,
 template <typename T>
 static int dispatch_welch(int log2l, const void* x, const void* y, int64_t y_stride, int nch,
                           const RecMap& map, const pyfft_segmentation* seg, const void* window,
-                          const double* coef_x, const double* coef_y, double* acc, void* ws,
-                          int64_t wsb, cudaStream_t st) {
+                          const double* coef_x, const double* coef_y, double* acc, double* lin, double* stats,
+                          void* ws, int64_t wsb, cudaStream_t st) {
 #define PYFFT_CASE(N) \
-    case N: return launch_welch<T, N>(x, y, y_stride, nch, map, seg, window, coef_x, coef_y, acc, ws, wsb, st);
+    case N: return launch_welch<T, N>(x, y, y_stride, nch, map, seg, window, coef_x, coef_y, acc, lin, stats, ws, wsb, st);
     switch (log2l) {
         PYFFT_CASE(4) PYFFT_CASE(5) PYFFT_CASE(6) PYFFT_CASE(7) PYFFT_CASE(8)
         PYFFT_CASE(9) PYFFT_CASE(10) PYFFT_CASE(11) PYFFT_CASE(12) PYFFT_CASE(13)
@@ -497,14 +582,15 @@ int64_t pyfft_welch_workspace_bytes(int dtype, const pyfft_segmentation* seg, in
     const int slots = threads / tps;
     const int gx = welch_grid_x(seg->seg_count, slots, nch);
     const int64_t esz = dtype == PYFFT_F64 ? 8 : 4;
-    int64_t b = (int64_t)nch * gx * slots * 4 * (L / 2 + 1) * esz;
+    int64_t b = (int64_t)nch * gx * slots * 4 * (L / 2 + 1 + tps) * esz + 8 * (int64_t)(nch + 1);
     return b > 0 ? b : 16;
 }
 
-int pyfft_welch_accumulate(int dtype, const void* x, const void* y, int64_t y_stride, int32_t nch,
-                           const pyfft_record_map* map, const pyfft_segmentation* seg,
-                           const void* window, const double* coef_x, const double* coef_y,
-                           double* acc, void* workspace, int64_t workspace_bytes, void* stream) {
+static int welch_accumulate_common(int dtype, const void* x, const void* y, int64_t y_stride, int32_t nch,
+                                   const pyfft_record_map* map, const pyfft_segmentation* seg,
+                                   const void* window, const double* coef_x, const double* coef_y,
+                                   double* acc, double* lin, double* stats, void* workspace,
+                                   int64_t workspace_bytes, void* stream) {
     RecMap m;
     int rc = check_map(map, &m);
     if (rc) return rc;
@@ -517,10 +603,40 @@ int pyfft_welch_accumulate(int dtype, const void* x, const void* y, int64_t y_st
     if ((rc = check_range(m, j_lo, j_hi))) return rc;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (dtype == PYFFT_F32)
-        return dispatch_welch<float>(log2l, x, y, y_stride, nch, m, seg, window, coef_x, coef_y, acc, workspace, workspace_bytes, st);
+        return dispatch_welch<float>(log2l, x, y, y_stride, nch, m, seg, window, coef_x, coef_y, acc, lin, stats, workspace, workspace_bytes, st);
     if (dtype == PYFFT_F64)
-        return dispatch_welch<double>(log2l, x, y, y_stride, nch, m, seg, window, coef_x, coef_y, acc, workspace, workspace_bytes, st);
+        return dispatch_welch<double>(log2l, x, y, y_stride, nch, m, seg, window, coef_x, coef_y, acc, lin, stats, workspace, workspace_bytes, st);
     return fail(PYFFT_EINVAL, "unknown dtype %d", dtype);
+}
+
+int pyfft_welch_accumulate(int dtype, const void* x, const void* y, int64_t y_stride, int32_t nch,
+                           const pyfft_record_map* map, const pyfft_segmentation* seg,
+                           const void* window, const double* coef_x, const double* coef_y,
+                           double* acc, void* workspace, int64_t workspace_bytes, void* stream) {
+    return welch_accumulate_common(dtype, x, y, y_stride, nch, map, seg, window, coef_x, coef_y, acc, nullptr,
+                                   nullptr, workspace, workspace_bytes, stream);
+}
+
+int pyfft_welch_accumulate_mean(int dtype, const void* x, const void* y, int64_t y_stride, int32_t nch,
+                                const pyfft_record_map* map, const pyfft_segmentation* seg,
+                                const void* window, const double* est, double* acc, double* lin,
+                                double* stats, void* workspace, int64_t workspace_bytes, void* stream) {
+    if (!est || !lin || !stats) return fail(PYFFT_EINVAL, "welch_accumulate_mean: est, lin and stats are required");
+    if (seg && seg->hop > seg->nfft) return fail(PYFFT_EINVAL, "welch_accumulate_mean: hop > nfft leaves gaps in the mean");
+    return welch_accumulate_common(dtype, x, y, y_stride, nch, map, seg, window, est, est + 2, acc, lin, stats,
+                                   workspace, workspace_bytes, stream);
+}
+
+int pyfft_welch_mean_correct(double* acc, const double* lin, int32_t nfft, int32_t nch, int64_t K,
+                             const double* est, const double* stats, int64_t nana, const double* wlow,
+                             void* stream) {
+    if (!acc || !lin || !est || !stats || !wlow || nfft < 16 || nch <= 0 || K < 0 || nana <= 0)
+        return fail(PYFFT_EINVAL, "welch_mean_correct: bad arguments");
+    const int nlin = nfft / 16, nbin = nfft / 2 + 1;
+    welch_mean_correct_kernel<<<(nch * nlin + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        acc, lin, nlin, nbin, nch, (double)K, est, stats, (double)nana, wlow);
+    PYFFT_LAUNCH_OK("welch_mean_correct_kernel");
+    return PYFFT_OK;
 }
 
 int pyfft_welch_finalize(const double* acc, int32_t nfft, int32_t nch, int64_t K, double scale,

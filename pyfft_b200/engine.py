@@ -102,6 +102,18 @@ class WelchPlan(object):
         self.coef = None
         self.K = 0
         self._ws = None
+        # mean-fused route (pyfft_welch_accumulate_mean): usable when the window's transform
+        # is negligible beyond the nfft/16 bins the kernel keeps linear sums for
+        self.nlin = self.nfft // 16
+        W = np.fft.fft(win)
+        p = np.abs(W) ** 2
+        leak = float(p[self.nlin:self.nfft // 2 + 1].max() / (win ** 2).sum()) if self.nfft >= 1024 else 1.0
+        self.can_fuse_mean = self.nfft >= 1024 and leak < (1e-9 if precision == "fp32" else 1e-18)
+        self.lin = torch.zeros((self.nch, 4, self.nlin), dtype=torch.float64, device=self.device)
+        self.wlow = torch.from_numpy(np.ascontiguousarray(
+            np.stack([W.real[:self.nlin], W.imag[:self.nlin]], 1))).to(self.device)
+        self.est = None
+        self.K_local = 0
 
     # -- detrend ------------------------------------------------------------ #
     def detrend_stats(self, x, y, rmap, j_begin, j_end):
@@ -121,6 +133,42 @@ class WelchPlan(object):
         self.coef = torch.empty_like(self.stats)
         check(lib.pyfft_detrend_coef(mode, _ptr(self.stats), self.nch + 1, nsig, _ptr(self.coef),
                                      _stream()))
+
+    # -- mean detrend fused into the accumulation ---------------------------- #
+    def estimate_mean(self, x, y, rmap, j_begin, j_end, nsample=65536):
+        """Provisional means from the first `nsample` analysed samples of this shard (any
+        estimate works: the exact global mean is restored by mean_correct)."""
+        j1 = min(j_end, j_begin + nsample)
+        tmp = torch.zeros_like(self.stats)
+        check(lib.pyfft_detrend_stats(self.code, _ptr(x), 0, 1, C.byref(rmap), j_begin, j1, _ptr(tmp),
+                                      _stream()))
+        check(lib.pyfft_detrend_stats(self.code, _ptr(y), y.stride(0), self.nch, C.byref(rmap), j_begin, j1,
+                                      C.c_void_p(tmp.data_ptr() + 16), _stream()))
+        self.est = torch.empty_like(tmp)
+        check(lib.pyfft_detrend_coef(_lib.DETREND_MEAN, _ptr(tmp), self.nch + 1, j1 - j_begin,
+                                     _ptr(self.est), _stream()))
+
+    def accumulate_mean(self, x, y, rmap, seg_first, seg_count):
+        """K1 with the mean removal fused: adds to acc, lin and the raw sums in stats."""
+        seg = Segmentation(self.nfft, self.hop, seg_first, seg_count)
+        need = check(lib.pyfft_welch_workspace_bytes(self.code, C.byref(seg), self.nch))
+        if self._ws is None or self._ws.numel() < need:
+            self._ws = torch.empty(need, dtype=torch.uint8, device=self.device)
+        check(lib.pyfft_welch_accumulate_mean(self.code, _ptr(x), _ptr(y), y.stride(0), self.nch,
+                                              C.byref(rmap), C.byref(seg), _ptr(self.window), _ptr(self.est),
+                                              _ptr(self.acc), _ptr(self.lin), _ptr(self.stats),
+                                              _ptr(self._ws), self._ws.numel(), _stream()))
+        self.K += int(seg_count)
+        self.K_local += int(seg_count)
+
+    def mean_correct(self, nana, group=None):
+        """stats must cover the whole analysed record (all-reduced here when sharded)."""
+        if group is not None:
+            torch.distributed.all_reduce(self.stats, group=group)
+        check(lib.pyfft_welch_mean_correct(_ptr(self.acc), _ptr(self.lin), self.nfft, self.nch,
+                                           self.K_local, _ptr(self.est), _ptr(self.stats), int(nana),
+                                           _ptr(self.wlow), _stream()))
+        self.coef = None
 
     # -- accumulate --------------------------------------------------------- #
     def accumulate(self, x, y, rmap, seg_first, seg_count):

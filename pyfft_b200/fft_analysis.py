@@ -241,6 +241,7 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
     device = kwargs.pop("device", None)
     group = kwargs.pop("group", None)
     return_device = kwargs.pop("return_device", False)
+    two_pass = kwargs.pop("two_pass_detrend", False)     # force the K0 + K1 route (testing)
     if useMLAB:
         raise NotImplementedError("useMLAB=True (matplotlib.mlab backend) is out of scope")
     if plotit:
@@ -307,11 +308,26 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
         if group is not None:
             rank, world = torch.distributed.get_rank(group), torch.distributed.get_world_size(group)
         lp = _dist.local_plan(K, hop, nwins, plan.nana, plan.i0, refl, rank, world)
-        if mode != _lib.DETREND_NONE:
-            # global detrend over the whole analysed record (:356-357): each rank sums its slice
-            wp.detrend_stats(x, y, rmap, lp["stats_span"][0], lp["stats_span"][1])
-            wp.solve_detrend(mode, plan.nana, group)
-        wp.accumulate(x, y, rmap, lp["k0"], lp["k1"] - lp["k0"])
+        nseg = lp["k1"] - lp["k0"]
+        if mode == _lib.DETREND_MEAN and wp.can_fuse_mean and nseg > 0 and hop <= nwins \
+                and not two_pass:
+            # global mean (:356-357) fused into the single pass over the data: provisional mean
+            # from the head of the shard, exact correction by linearity afterwards
+            s_lo, s_hi = lp["stats_span"]
+            c_lo, c_hi = lp["k0"] * hop, lp["k1"] * hop          # what the fused kernel sums
+            wp.estimate_mean(x, y, rmap, c_lo, c_hi)
+            wp.accumulate_mean(x, y, rmap, lp["k0"], nseg)
+            if s_lo < c_lo:
+                wp.detrend_stats(x, y, rmap, s_lo, c_lo)
+            if s_hi > c_hi:
+                wp.detrend_stats(x, y, rmap, c_hi, s_hi)
+            wp.mean_correct(plan.nana, group)
+        else:
+            if mode != _lib.DETREND_NONE:
+                # global detrend over the whole analysed record (:356-357): each rank sums its slice
+                wp.detrend_stats(x, y, rmap, lp["stats_span"][0], lp["stats_span"][1])
+                wp.solve_detrend(mode, plan.nana, group)
+            wp.accumulate(x, y, rmap, lp["k0"], nseg)
         if group is not None:
             wp.all_reduce(group)
         scale = 1.0 / (fftinfo.S1 ** 2) / fftinfo.ENBW             # :432-440

@@ -131,3 +131,28 @@ def test_device_tensor_inputs_and_identical_signals(cuda_device):
     assert info.precision == "fp32" and info.nwins == 2048
     assert np.allclose(np.abs(Cxy), 1.0, atol=1e-5) and np.allclose(phi, 0.0, atol=1e-5)
     assert relerr(Pxx, Pyy) < 1e-6 and relerr(Pxy.real, Pxx.real) < 1e-6
+
+
+@pytest.mark.parametrize("precision", ["fp32", "fp64"])
+@pytest.mark.parametrize("window", ["Hanning", "Hamming", "SFT3F", "Bartlett"])
+def test_fused_mean_route_equals_two_pass_and_oracle(precision, window, cuda_device):
+    """Mean detrend fused into K1 (provisional mean + exact linear correction): a drifting
+    record makes the provisional mean wrong by ~sigma; results must still match the oracle and
+    the two-pass (K0 + K1) route.  Windows whose transform leaks beyond nfft/16 bins fall back
+    to two passes by themselves."""
+    from oracle import restatement as R
+    from oracle import signals
+    from pyfft_b200 import fft_pwelch
+    n = 2 ** 17
+    t, x, y = signals.c2_cross(n=n, dc=(50.0, -20.0))
+    x = x + np.linspace(0.0, 2.0, n)
+    y = y - np.linspace(0.0, 1.0, n) ** 2
+    if precision == "fp32":
+        x, y = x.astype(np.float32), y.astype(np.float32)
+    kw = dict(Navr=63, windowoverlap=0.5, windowfunction=window, detrend_style=1)
+    with np.errstate(all="ignore"):
+        ref = R.fft_pwelch(t, x.astype(np.float64), y.astype(np.float64), **kw)
+    a = fft_pwelch(t, x, y, plotit=False, precision=precision, **kw)
+    b = fft_pwelch(t, x, y, plotit=False, precision=precision, two_pass_detrend=True, **kw)
+    _check(a, ref, precision)
+    _check(b, ref, precision)
