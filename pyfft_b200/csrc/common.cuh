@@ -64,4 +64,9 @@ void free_twiddles();
 
 int device_sm_count();
 
+// shared between welch.cu and welch_tc.cu
+int welch_reduce_launch_f32(const float* partial, int nparts, int per_pair, int nch, double* acc, cudaStream_t st);
+int welch_raw_sums_launch(const double* dev_sums, const double* est, int n, double count, double* stats,
+                          cudaStream_t st);
+
 }  // namespace pyfft

@@ -344,7 +344,15 @@ __global__ void __launch_bounds__(256) welch_reduce_kernel(const T* __restrict__
     if (i >= per_pair) return;
     const T* p = partial + (size_t)pair * nparts * per_pair + i;
     double s = 0.0;
-    for (int k = 0; k < nparts; ++k) s += (double)p[(size_t)k * per_pair];
+    int k = 0;
+    for (; k + 8 <= nparts; k += 8) {               // 8 independent loads in flight
+        T r[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) r[u] = p[(size_t)(k + u) * per_pair];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) s += (double)r[u];
+    }
+    for (; k < nparts; ++k) s += (double)p[(size_t)k * per_pair];
     acc[(size_t)pair * per_pair + i] += s;
 }
 
@@ -527,6 +535,19 @@ static int dispatch_welch(int log2l, const void* x, const void* y, int64_t y_str
     }
 #undef PYFFT_CASE
     return fail(PYFFT_EUNSUPPORTED, "nfft = 2^%d not supported", log2l);
+}
+
+int welch_reduce_launch_f32(const float* partial, int nparts, int per_pair, int nch, double* acc, cudaStream_t st) {
+    welch_reduce_kernel<float><<<dim3((per_pair + 255) / 256, nch), 256, 0, st>>>(partial, nparts, per_pair, acc);
+    PYFFT_LAUNCH_OK("welch_reduce_kernel");
+    return PYFFT_OK;
+}
+
+int welch_raw_sums_launch(const double* dev_sums, const double* est, int n, double count, double* stats,
+                          cudaStream_t st) {
+    welch_raw_sums_kernel<<<(n + 127) / 128, 128, 0, st>>>(dev_sums, est, n, count, stats);
+    PYFFT_LAUNCH_OK("welch_raw_sums_kernel");
+    return PYFFT_OK;
 }
 
 }  // namespace pyfft

@@ -114,6 +114,13 @@ class WelchPlan(object):
             np.stack([W.real[:self.nlin], W.imag[:self.nlin]], 1))).to(self.device)
         self.est = None
         self.K_local = 0
+        # tensor-core route (pyfft_welch_accumulate_tc): nfft 4096, fp32, hop % 512 == 0, window
+        # transform negligible beyond the 8 bins it keeps linear sums for
+        leak8 = float(p[8:self.nfft // 2 + 1].max() / (win ** 2).sum()) if self.nfft == 4096 else 1.0
+        self.can_use_tc = (self.nfft == 4096 and precision == "fp32" and self.hop % 512 == 0
+                           and self.hop <= self.nfft and leak8 < 1e-9)
+        self.prescale = None
+        self._tc_status = None
 
     # -- detrend ------------------------------------------------------------ #
     def detrend_stats(self, x, y, rmap, j_begin, j_end):
@@ -160,6 +167,35 @@ class WelchPlan(object):
                                               _ptr(self._ws), self._ws.numel(), _stream()))
         self.K += int(seg_count)
         self.K_local += int(seg_count)
+
+    # -- tensor-core route -------------------------------------------------- #
+    def prepare_tc(self, x, y, rmap, j_begin, j_end, nsample=65536):
+        """Provisional means and power-of-two scales from the head of the shard."""
+        j1 = min(j_end, j_begin + nsample)
+        self.est = torch.zeros(2 * (self.nch + 1), dtype=torch.float64, device=self.device)
+        self.prescale = torch.empty(self.nch + 1, dtype=torch.float64, device=self.device)
+        check(lib.pyfft_welch_tc_prepare(_ptr(x), _ptr(y), y.stride(0), self.nch, C.byref(rmap), j_begin, j1,
+                                         _ptr(self.est), _ptr(self.prescale), _stream()))
+
+    def accumulate_tc(self, x, y, rmap, seg_first, seg_count):
+        """K1 on the tensor cores (tcgen05): adds to acc, lin and the raw sums in stats."""
+        seg = Segmentation(self.nfft, self.hop, seg_first, seg_count)
+        need = check(lib.pyfft_welch_tc_workspace_bytes(C.byref(seg), self.nch))
+        if self._ws is None or self._ws.numel() < need:
+            self._ws = torch.empty(need, dtype=torch.uint8, device=self.device)
+        if self._tc_status is None:
+            self._tc_status = torch.zeros(1, dtype=torch.int32, device=self.device)
+        check(lib.pyfft_welch_accumulate_tc(_ptr(x), _ptr(y), y.stride(0), self.nch, C.byref(rmap),
+                                            C.byref(seg), _ptr(self.window), _ptr(self.est),
+                                            _ptr(self.prescale), _ptr(self.acc), _ptr(self.lin),
+                                            _ptr(self.stats), _ptr(self._ws), self._ws.numel(),
+                                            _ptr(self._tc_status), _stream()))
+        self.K += int(seg_count)
+        self.K_local += int(seg_count)
+
+    def tc_failed(self):
+        """True when a tensor-core barrier wait timed out (synchronises)."""
+        return self._tc_status is not None and int(self._tc_status.item()) != 0
 
     def mean_correct(self, nana, group=None):
         """stats must cover the whole analysed record (all-reduced here when sharded)."""

@@ -63,6 +63,16 @@ __global__ void __launch_bounds__(128) probe_kernel(const __half* A, const __hal
             tmem_ld_wait();
             for (int j = 0; j < 32; ++j) if (c0 + j < N) D[(size_t)tid * N + c0 + j] = r[j];
         }
+        // unaligned column offsets: 32 columns from column 34, 2 columns from column 66
+        if (N >= 72) {
+            float r[32], a, b;
+            tmem_ld32(tbase + ((uint32_t)(warp * 32) << 16) + 34, r);
+            tmem_ld2(tbase + ((uint32_t)(warp * 32) << 16) + 66, a, b);
+            tmem_ld_wait();
+            bool same = (a == D[(size_t)tid * N + 66]) && (b == D[(size_t)tid * N + 67]);
+            for (int j = 0; j < 32; ++j) same = same && (r[j] == D[(size_t)tid * N + 34 + j]);
+            if (!same) atomicAdd(&status[1], 1);
+        }
     } else if (tid == 0) {
         status[0] = 1;
     }
@@ -83,18 +93,18 @@ static int run(int reps) {
     int* dS;
     long long* dC;
     cudaMalloc(&dA, hA.size() * 2); cudaMalloc(&dB, hB.size() * 2); cudaMalloc(&dD, 128 * N * 4);
-    cudaMalloc(&dS, 4); cudaMalloc(&dC, 8);
+    cudaMalloc(&dS, 8); cudaMalloc(&dC, 8);
     cudaMemcpy(dA, hA.data(), hA.size() * 2, cudaMemcpyHostToDevice);
     cudaMemcpy(dB, hB.data(), hB.size() * 2, cudaMemcpyHostToDevice);
-    cudaMemset(dS, 0, 4); cudaMemset(dD, 0, 128 * N * 4);
+    cudaMemset(dS, 0, 8); cudaMemset(dD, 0, 128 * N * 4);
     const int smem = (128 + N) * K * 2 + 1024;
     cudaFuncSetAttribute(probe_kernel<N, K>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     probe_kernel<N, K><<<1, 128, smem>>>(dA, dB, dD, dS, reps, dC);
     cudaError_t e = cudaDeviceSynchronize();
     if (e != cudaSuccess) { printf("N=%d K=%d: CUDA error %s\n", N, K, cudaGetErrorString(e)); return 1; }
-    int st; long long cyc;
+    int st, st2; long long cyc;
     std::vector<float> hD(128 * N);
-    cudaMemcpy(&st, dS, 4, cudaMemcpyDeviceToHost);
+    cudaMemcpy(&st, dS, 4, cudaMemcpyDeviceToHost); cudaMemcpy(&st2, dS + 1, 4, cudaMemcpyDeviceToHost);
     cudaMemcpy(&cyc, dC, 8, cudaMemcpyDeviceToHost);
     cudaMemcpy(hD.data(), dD, hD.size() * 4, cudaMemcpyDeviceToHost);
     double maxerr = 0;
@@ -105,8 +115,8 @@ static int run(int reps) {
             const double d = fabs(s - hD[m * N + n]);
             if (d > maxerr) maxerr = d;
         }
-    printf("N=%d K=%d: status=%d max|err|=%g  D[0][0]=%g D[127][%d]=%g  cycles/rep=%.1f (reps=%d, %d MMAs per rep)\n", N,
-           K, st, maxerr, hD[0], N - 1, hD[127 * N + N - 1], reps > 1 ? (double)cyc / (reps - 1) : 0.0, reps, K / 16);
+    printf("N=%d K=%d: status=%d unaligned_ld_mismatch=%d max|err|=%g  D[0][0]=%g D[127][%d]=%g  cycles/rep=%.1f (reps=%d, %d MMAs per rep)\n", N,
+           K, st, st2, maxerr, hD[0], N - 1, hD[127 * N + N - 1], reps > 1 ? (double)cyc / (reps - 1) : 0.0, reps, K / 16);
     return (st != 0 || maxerr > 1e-3) ? 1 : 0;
 }
 
