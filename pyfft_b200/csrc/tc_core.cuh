@@ -61,10 +61,10 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t mbar, uint32_t parity) {
     uint32_t ok;
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
         "selp.u32 %0, 1, 0, p;\n\t}"
         : "=r"(ok)
-        : "r"(mbar), "r"(parity)
+        : "r"(mbar), "r"(parity), "r"(2000u)      // suspend-time hint (ns): sleep in hardware, do not spin
         : "memory");
     return ok != 0;
 }

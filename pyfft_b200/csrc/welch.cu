@@ -336,24 +336,36 @@ __global__ void __launch_bounds__(256) welch_mean_correct_kernel(double* __restr
 }
 
 // acc[pair][q][f] += sum_part partial[pair][part][q][f]
+// 32 consecutive outputs per block, the parts split over the 8 warps (8 loads in flight each),
+// combined through shared memory: the part loop is short enough not to be latency-bound
 template <typename T>
 __global__ void __launch_bounds__(256) welch_reduce_kernel(const T* __restrict__ partial, int nparts,
                                                            int per_pair, double* __restrict__ acc) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31, g = threadIdx.x >> 5;
+    const int i = blockIdx.x * 32 + lane;
     const int pair = blockIdx.y;
-    if (i >= per_pair) return;
-    const T* p = partial + (size_t)pair * nparts * per_pair + i;
+    __shared__ double sh[8][33];
     double s = 0.0;
-    int k = 0;
-    for (; k + 8 <= nparts; k += 8) {               // 8 independent loads in flight
-        T r[8];
+    if (i < per_pair) {
+        const T* p = partial + (size_t)pair * nparts * per_pair + i;
+        int k = g;
+        for (; k + 56 < nparts; k += 64) {
+            T r[8];
 #pragma unroll
-        for (int u = 0; u < 8; ++u) r[u] = p[(size_t)(k + u) * per_pair];
+            for (int u = 0; u < 8; ++u) r[u] = p[(size_t)(k + 8 * u) * per_pair];
 #pragma unroll
-        for (int u = 0; u < 8; ++u) s += (double)r[u];
+            for (int u = 0; u < 8; ++u) s += (double)r[u];
+        }
+        for (; k < nparts; k += 8) s += (double)p[(size_t)k * per_pair];
     }
-    for (; k < nparts; ++k) s += (double)p[(size_t)k * per_pair];
-    acc[(size_t)pair * per_pair + i] += s;
+    sh[g][lane] = s;
+    __syncthreads();
+    if (g == 0 && i < per_pair) {
+        double t = 0.0;
+#pragma unroll
+        for (int u = 0; u < 8; ++u) t += sh[u][lane];
+        acc[(size_t)pair * per_pair + i] += t;
+    }
 }
 
 // ------------------------------------------------------------------------- //
@@ -507,7 +519,7 @@ static int launch_welch(const void* x, const void* y, int64_t y_stride, int nch,
         PYFFT_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         kern<<<dim3(gx, nch), G::THREADS, smem, st>>>(p);
         PYFFT_LAUNCH_OK("welch_pair_kernel");
-        welch_reduce_kernel<T><<<dim3((4 * G::TPS + 255) / 256, nch), 256, 0, st>>>(p.lin_partial, nparts, 4 * G::TPS, lin);
+        welch_reduce_kernel<T><<<dim3((4 * G::TPS + 31) / 32, nch), 256, 0, st>>>(p.lin_partial, nparts, 4 * G::TPS, lin);
         // coef_x and coef_y are one contiguous (a, b) array: x first, then the y channels
         welch_raw_sums_kernel<<<(nch + 1 + 127) / 128, 128, 0, st>>>(p.dev_sums, coef_x, nch + 1,
                                                                      (double)seg->seg_count * (double)seg->hop, stats);
@@ -517,7 +529,7 @@ static int launch_welch(const void* x, const void* y, int64_t y_stride, int nch,
         kern<<<dim3(gx, nch), G::THREADS, smem, st>>>(p);
         PYFFT_LAUNCH_OK("welch_pair_kernel");
     }
-    welch_reduce_kernel<T><<<dim3((per_pair + 255) / 256, nch), 256, 0, st>>>(p.partial, nparts, per_pair, acc);
+    welch_reduce_kernel<T><<<dim3((per_pair + 31) / 32, nch), 256, 0, st>>>(p.partial, nparts, per_pair, acc);
     PYFFT_LAUNCH_OK("welch_reduce_kernel");
     return PYFFT_OK;
 }
@@ -538,7 +550,7 @@ static int dispatch_welch(int log2l, const void* x, const void* y, int64_t y_str
 }
 
 int welch_reduce_launch_f32(const float* partial, int nparts, int per_pair, int nch, double* acc, cudaStream_t st) {
-    welch_reduce_kernel<float><<<dim3((per_pair + 255) / 256, nch), 256, 0, st>>>(partial, nparts, per_pair, acc);
+    welch_reduce_kernel<float><<<dim3((per_pair + 31) / 32, nch), 256, 0, st>>>(partial, nparts, per_pair, acc);
     PYFFT_LAUNCH_OK("welch_reduce_kernel");
     return PYFFT_OK;
 }

@@ -115,9 +115,9 @@ __global__ void __launch_bounds__(256, 1) welch_tc_kernel(const TcParams p) {
     const float mean_f = (float)p.est[2 * cidx];
     const float sc = (float)p.prescale[cidx];
     const float nms = -mean_f * sc;                                         // exact: sc is a power of two
-    const float* swin = reinterpret_cast<const float*>(sm + OFF_WIN);
-    const float2* stw = reinterpret_cast<const float2*>(sm + OFF_TW);
-    unsigned char* tbuf = sm + OFF_TEAM + team * TEAM_BYTES;
+    const float* __restrict__ swin = reinterpret_cast<const float*>(sm + OFF_WIN);
+    const float2* __restrict__ stw = reinterpret_cast<const float2*>(sm + OFF_TW);
+    unsigned char* __restrict__ tbuf = sm + OFF_TEAM + team * TEAM_BYTES;
     const uint32_t tbuf_addr = sm_addr + OFF_TEAM + team * TEAM_BYTES;
     const uint32_t a1_row = (uint32_t)((tt >> 3) * 1024 + (tt & 7) * 128);  // own row of a 128-row K atom
     const int hb = (int)(p.hop >> 9);                                       // 8-sample chunks inside the hop
@@ -172,11 +172,14 @@ __global__ void __launch_bounds__(256, 1) welch_tc_kernel(const TcParams p) {
                 for (int cc = 0; cc < 4; ++cc) {
                     const int c = 4 * hf + cc;
                     float* u = v + 8 * cc;
+                    float wv[8];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) wv[i] = swin[64 * (8 * c + i) + n2];
 #pragma unroll
                     for (int i = 0; i < 8; ++i) u[i] = fmaf(u[i], sc, nms);               // (x - mean) * scale
                     if (c < hb) devsum += ((u[0] + u[1]) + (u[2] + u[3])) + ((u[4] + u[5]) + (u[6] + u[7]));
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) u[i] *= swin[64 * (8 * c + i) + n2];
+                    for (int i = 0; i < 8; ++i) u[i] *= wv[i];
                     uint4 w;
                     w.x = pack_h2(u[0], u[1]); w.y = pack_h2(u[2], u[3]);
                     w.z = pack_h2(u[4], u[5]); w.w = pack_h2(u[6], u[7]);
@@ -232,13 +235,26 @@ __global__ void __launch_bounds__(256, 1) welch_tc_kernel(const TcParams p) {
             // row offset is r*128 and only the 16-byte chunk index is XOR-ed with (r & 7)
             unsigned char* bp = tbuf + (n2 >> 5) * (N2 * 128) + (n2 & 3) * 4 + (sg * COLS_PER_SEG + ch * YOFF) * 128;
 #pragma unroll
-            for (int k1 = 0; k1 <= 32; ++k1) {
-                const float re = k1 < 32 ? d0[k1] : d1[0];
-                const float im = (k1 >= 1 && k1 <= 31) ? d1[k1] : 0.f;
-                const float2 t = stw[k1 * 64 + n2];
-                const float br = re * t.x - im * t.y;
-                const float bi = re * t.y + im * t.x;
-                *reinterpret_cast<uint32_t*>(bp + k1 * 128 + xorv[k1 & 7]) = pack_h2(br, bi);
+            for (int g = 0; g < 5; ++g) {                        // k1 = 8g .. 8g+7 (g = 4: k1 = 32 only)
+                float2 t[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+                    if (8 * g + i <= 32) t[i] = stw[(8 * g + i) * 64 + n2];      // twiddles of the group first
+                uint32_t w[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int k1 = 8 * g + i;
+                    if (k1 <= 32) {
+                        const float re = k1 < 32 ? d0[k1] : d1[0];
+                        const float im = (k1 >= 1 && k1 <= 31) ? d1[k1] : 0.f;
+                        w[i] = pack_h2(re * t[i].x - im * t[i].y, re * t[i].y + im * t[i].x);
+                    }
+                }
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int k1 = 8 * g + i;
+                    if (k1 <= 32) *reinterpret_cast<uint32_t*>(bp + k1 * 128 + xorv[k1 & 7]) = w[i];
+                }
             }
         }
         tc_fence_before();
@@ -339,49 +355,52 @@ __global__ void __launch_bounds__(256, 1) welch_tc_kernel(const TcParams p) {
 // provisional statistics: mean (rounded to float) and a power-of-two scale that brings the
 // rms of (x - mean) to ~1/8, from the first samples of the span
 // ------------------------------------------------------------------------- //
-__global__ void __launch_bounds__(256) tc_prepare_kernel(const float* __restrict__ x, const float* __restrict__ y,
+// pass 1: est[2c] += sum (x - x0), est[2c+1] += sum (x - x0)^2 with x0 = the first sample of the span
+__global__ void __launch_bounds__(256) tc_moments_kernel(const float* __restrict__ x, const float* __restrict__ y,
                                                          int64_t y_stride, RecMap map, int64_t j_begin, int64_t j_end,
-                                                         double* __restrict__ est, double* __restrict__ prescale) {
-    const int c = blockIdx.x;                       // 0 = x, 1.. = y channels
+                                                         double* __restrict__ est) {
+    const int c = blockIdx.y;                       // 0 = x, 1.. = y channels
     const float* p = c == 0 ? x : y + (int64_t)(c - 1) * y_stride;
-    __shared__ double sh[2][8];
-    __shared__ double mean_sh;
-    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
-    const double n = (double)(j_end - j_begin);
-    for (int pass = 0; pass < 2; ++pass) {
-        const double m = pass ? mean_sh : 0.0;
-        double s0 = 0.0, s1 = 0.0;
-        for (int64_t j = j_begin + threadIdx.x; j < j_end; j += 256) {
-            const double v = (double)p[src_index(map, j)] - m;
-            s0 += v;
-            s1 += v * v;
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            s0 += __shfl_xor_sync(0xffffffffu, s0, o);
-            s1 += __shfl_xor_sync(0xffffffffu, s1, o);
-        }
-        if (l == 0) { sh[0][w] = s0; sh[1][w] = s1; }
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            double a = 0.0, b = 0.0;
-            for (int i = 0; i < 8; ++i) { a += sh[0][i]; b += sh[1][i]; }
-            if (pass == 0) {
-                mean_sh = (double)(float)(a / n);                 // exactly representable in fp32
-            } else {
-                const double rms = sqrt(b / n);
-                int e = 0;
-                if (rms > 0.0 && isfinite(rms)) frexp(rms, &e);   // rms = f * 2^e, f in [0.5, 1)
-                int sh2 = -e - 2;                                  // rms * 2^sh2 in [1/8, 1/4)
-                if (sh2 > 100) sh2 = 100;
-                if (sh2 < -100) sh2 = -100;
-                est[2 * c] = mean_sh;
-                est[2 * c + 1] = 0.0;
-                prescale[c] = ldexp(1.0, sh2);
-            }
-        }
-        __syncthreads();
+    const double x0 = (double)p[src_index(map, j_begin)];
+    double s0 = 0.0, s1 = 0.0;
+    const int64_t step = (int64_t)gridDim.x * 256;
+    for (int64_t j = j_begin + (int64_t)blockIdx.x * 256 + threadIdx.x; j < j_end; j += step) {
+        const double v = (double)p[src_index(map, j)] - x0;
+        s0 += v;
+        s1 += v * v;
     }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        s0 += __shfl_xor_sync(0xffffffffu, s0, o);
+        s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicAdd(&est[2 * c], s0);
+        atomicAdd(&est[2 * c + 1], s1);
+    }
+}
+
+// pass 2: est[2c] = mean (rounded to fp32), est[2c+1] = 0, prescale[c] = 2^k with rms * 2^k in [1/8, 1/4)
+__global__ void tc_prepare_finish_kernel(const float* __restrict__ x, const float* __restrict__ y, int64_t y_stride,
+                                         RecMap map, int64_t j_begin, int64_t j_end, int nch1,
+                                         double* __restrict__ est, double* __restrict__ prescale) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= nch1) return;
+    const float* p = c == 0 ? x : y + (int64_t)(c - 1) * y_stride;
+    const double x0 = (double)p[src_index(map, j_begin)];
+    const double n = (double)(j_end - j_begin);
+    const double md = est[2 * c] / n;
+    double var = est[2 * c + 1] / n - md * md;
+    if (!(var > 0.0)) var = 0.0;
+    const double rms = sqrt(var);
+    int e = 0;
+    if (rms > 0.0 && isfinite(rms)) frexp(rms, &e);   // rms = f * 2^e, f in [0.5, 1)
+    int sh2 = -e - 2;
+    if (sh2 > 100) sh2 = 100;
+    if (sh2 < -100) sh2 = -100;
+    est[2 * c] = (double)(float)(x0 + md);            // exactly representable in fp32
+    est[2 * c + 1] = 0.0;
+    prescale[c] = ldexp(1.0, sh2);
 }
 
 // ------------------------------------------------------------------------- //
@@ -481,8 +500,15 @@ int pyfft_welch_tc_prepare(const void* x, const void* y, int64_t y_stride, int32
     if (!x || !y || !est || !prescale || nch <= 0) return fail(PYFFT_EINVAL, "welch_tc_prepare: bad arguments");
     if ((rc = check_range(m, j_begin, j_end))) return rc;
     if (j_end <= j_begin) return fail(PYFFT_EINVAL, "welch_tc_prepare: empty sample span");
-    tc_prepare_kernel<<<nch + 1, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        static_cast<const float*>(x), static_cast<const float*>(y), y_stride, m, j_begin, j_end, est, prescale);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    PYFFT_CUDA_OK(cudaMemsetAsync(est, 0, sizeof(double) * 2 * (size_t)(nch + 1), st));
+    int gx = (int)((j_end - j_begin + 2047) / 2048);
+    if (gx > 64) gx = 64;
+    tc_moments_kernel<<<dim3(gx, nch + 1), 256, 0, st>>>(static_cast<const float*>(x), static_cast<const float*>(y),
+                                                        y_stride, m, j_begin, j_end, est);
+    tc_prepare_finish_kernel<<<(nch + 1 + 63) / 64, 64, 0, st>>>(static_cast<const float*>(x),
+                                                               static_cast<const float*>(y), y_stride, m, j_begin,
+                                                               j_end, nch + 1, est, prescale);
     PYFFT_LAUNCH_OK("tc_prepare_kernel");
     return PYFFT_OK;
 }

@@ -242,6 +242,7 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
     group = kwargs.pop("group", None)
     return_device = kwargs.pop("return_device", False)
     two_pass = kwargs.pop("two_pass_detrend", False)     # force the K0 + K1 route (testing)
+    tensor_cores = kwargs.pop("tensor_cores", None)      # None: automatic; True / False: force
     if useMLAB:
         raise NotImplementedError("useMLAB=True (matplotlib.mlab backend) is out of scope")
     if plotit:
@@ -315,8 +316,17 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
             # from the head of the shard, exact correction by linearity afterwards
             s_lo, s_hi = lp["stats_span"]
             c_lo, c_hi = lp["k0"] * hop, lp["k1"] * hop          # what the fused kernel sums
-            wp.estimate_mean(x, y, rmap, c_lo, c_hi)
-            wp.accumulate_mean(x, y, rmap, lp["k0"], nseg)
+            # tensor-core DFT (fp16 operands, fp32 accumulation): its per-segment rounding noise
+            # (2^-12 relative, zero mean) averages out as 1/sqrt(K) -- used when enough segments
+            # are averaged for the 1e-5-of-peak contract to hold with margin
+            use_tc = wp.can_use_tc and (nseg >= 16384 if tensor_cores is None else bool(tensor_cores))
+            if use_tc:
+                wp.prepare_tc(x, y, rmap, c_lo, c_hi)
+                wp.accumulate_tc(x, y, rmap, lp["k0"], nseg)
+            else:
+                wp.estimate_mean(x, y, rmap, c_lo, c_hi)
+                wp.accumulate_mean(x, y, rmap, lp["k0"], nseg)
+            fftinfo.tensor_cores = bool(use_tc)
             if s_lo < c_lo:
                 wp.detrend_stats(x, y, rmap, s_lo, c_lo)
             if s_hi > c_hi:

@@ -99,3 +99,28 @@ def test_config2_prefix_against_oracle(cuda_device):
     for a, nm in ((Pxy, "Pxy"), (Pxx, "Pxx"), (Pyy, "Pyy")):
         assert relerr(a, ref[nm]) <= 1e-5, nm
     assert relerr(Cxy, ref["Cxy"], 1.0) <= 1e-4
+
+
+def test_config2_tensor_core_path_vs_cuda_core_path(cuda_device):
+    """The tcgen05 DFT-as-GEMM kernel against the fp32 register-FFT kernel at full size, on the
+    hardest input for it (white noise only: every bin is as high as the peak), plus the
+    sine + noise record of config 2.  Contract: 1e-5 of the spectral peak, 1e-4 on coherence."""
+    import torch
+    from pyfft_b200 import fft_pwelch
+    dev = cuda_device
+    t = np.arange(N) / 1.0e6
+    g = torch.Generator(device=dev).manual_seed(77)
+    xs, ys = _signals(dev)
+    cases = {"sine+noise": (xs, ys)}
+    xn = torch.randn(N, generator=g, device=dev, dtype=torch.float32) * 3.0 + 11.0
+    yn = 0.6 * xn + torch.randn(N, generator=g, device=dev, dtype=torch.float32) * 0.1 - 4.0
+    cases["noise only, coherent pair"] = (xn, yn)
+    kw = dict(Navr=N // H - 1, windowoverlap=0.5, windowfunction="Hanning", detrend_style=1, plotit=False)
+    for name, (x, y) in cases.items():
+        a = fft_pwelch(t, x, y, tensor_cores=True, **kw)
+        b = fft_pwelch(t, x, y, tensor_cores=False, **kw)
+        assert a[6].tensor_cores and not b[6].tensor_cores and a[6].nwins == L
+        for i, nm in ((1, "Pxy"), (2, "Pxx"), (3, "Pyy")):
+            err = np.max(np.abs(a[i] - b[i])) / np.max(np.abs(b[i]))
+            assert err <= 1e-5, (name, nm, err)
+        assert np.max(np.abs(a[4] - b[4])) <= 1e-4, name
