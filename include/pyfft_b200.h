@@ -152,6 +152,40 @@ int pyfft_welch_mean_correct(double* acc, const double* lin, int32_t nfft, int32
                              const double* wlow, void* stream);
 
 /* ------------------------------------------------------------------------- *
+ * K1-TC, the same accumulation on the tcgen05 tensor cores (float32 input,
+ * nfft = 4096, hop a multiple of 512)
+ * replaces: the same reference lines as pyfft_welch_accumulate_mean.
+ * Every segment's 4096-point DFT is computed as two real DFT-matrix GEMMs
+ * (64 x 64 decomposition, fp16 operands split hi + lo for the matrices, fp32
+ * accumulation in tensor memory); the detrended, windowed samples are rounded to
+ * fp16 ONCE after a power-of-two prescale, so every segment carries an independent
+ * relative error of ~2^-11/sqrt(nfft) that averages down with the number of
+ * segments.  The Python host therefore selects this path only for long averages
+ * (Navr >= 16384, where it meets the 1e-5-of-peak bar) and the CUDA-core kernel
+ * otherwise.  acc, lin, stats: exactly as pyfft_welch_accumulate_mean (lin holds
+ * bins 0 .. 7 only, the rest of each row is zero); finish with
+ * pyfft_welch_mean_correct and pyfft_welch_finalize.
+ *   pyfft_welch_tc_prepare: est (pairs, as above; the mean is rounded to float so
+ *     that the kernel's subtraction is the one the correction assumes) and
+ *     prescale = double[nch+1], powers of two bringing the rms of each channel to
+ *     [1/8, 1/4), from the samples of analysed indices [j_begin, j_end).
+ *   status_flag (device int32, zeroed by the caller) is set to 1 if a tensor-core
+ *     completion barrier timed out; the result is then invalid and the host falls
+ *     back to pyfft_welch_accumulate_mean.
+ * ------------------------------------------------------------------------- */
+int64_t pyfft_welch_tc_workspace_bytes(const pyfft_segmentation* seg, int32_t nch);
+
+int pyfft_welch_tc_prepare(const void* x, const void* y, int64_t y_stride, int32_t nch,
+                           const pyfft_record_map* map, int64_t j_begin, int64_t j_end,
+                           double* est, double* prescale, void* stream);
+
+int pyfft_welch_accumulate_tc(const void* x, const void* y, int64_t y_stride, int32_t nch,
+                              const pyfft_record_map* map, const pyfft_segmentation* seg,
+                              const void* window, const double* est, const double* prescale,
+                              double* acc, double* lin, double* stats, void* workspace,
+                              int64_t workspace_bytes, int32_t* status_flag, void* stream);
+
+/* ------------------------------------------------------------------------- *
  * Welch finalize
  * replaces: one-/two-sided selection and doubling (fft_analysis.py:402-428),
  *           scaling by 1/S1^2/ENBW (:432-440), the mean over segments
