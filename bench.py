@@ -159,6 +159,16 @@ def make_slice(torch, dev, g_lo, g_hi, seed, dc, amp, phase):
     return out
 
 
+def traffic_of(kernel, n):
+    """DRAM bytes (read + write) per launch of the dominant kernel from the committed ncu --set full
+    capture (profiles/traffic.json), valid for the single-GPU workload size it was taken on; else None."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))[kernel]
+    except (OSError, KeyError, ValueError):
+        return None
+    return t["dram_bytes_read"] + t["dram_bytes_write"] if n == 2 ** 26 else None
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -329,19 +339,20 @@ def run_ours(args):
         v, sec = cpu_port_msamples(2 ** 23, repeats=2)
         cpu = {"value": v, "unit": UNIT, "cores": 1, "kind": "port",
                "sample": "2 ch x 2^23 samples (1/8 of the workload), float64, best of 2 (%.2f s)" % sec}
+    kname = "welch_tc_kernel (tcgen05)" if use_tc else "welch_pair_kernel<float,12,fused mean>"
     out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
            "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
            "config": workload_config(world, n),
            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                        "frac": achieved / peak, "traffic": None,
-                        "kernel": "welch_tc_kernel (tcgen05)" if use_tc else "welch_pair_kernel<float,12,fused mean>",
+                        "frac": achieved / peak, "traffic": traffic_of(kname, n),
+                        "kernel": kname,
                         "algorithmic_bytes": alg_bytes, "kernel_ms": ms_k1,
                         "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s",
                         "whole_step_frac": alg_bytes / (ms_step / 1e3) / 1e9 / peak,
                         "two_pass_step_ms": ms_two, "cuda_core_kernel_ms": ms_k1_cuda,
                         "vs_two_pass_cuda_core_max_rel": dev_fused, "vs_two_pass_cuda_core_coherence_abs": dev_coh},
-           "cpu_baseline": cpu, "e2e": e2e, "clocks": clk, "gpu_launches": 11 * args.steps}
+           "cpu_baseline": cpu, "e2e": e2e, "clocks": clk, "gpu_launches": 9 * args.steps}
     print(json.dumps(out), flush=True)
     if group is not None:
         dist.destroy_process_group()
