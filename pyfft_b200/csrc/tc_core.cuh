@@ -69,6 +69,42 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t mbar, uint32_t parity) {
     return ok != 0;
 }
 
+// try_wait without a suspend-time hint: the hardware's own (short) time limit applies.  With a hint
+// the compiler emits NANOSLEEP of that length between polls, which quantises every hand-shake of a
+// fine-grained pipeline.
+__device__ __forceinline__ bool mbar_try_wait_nohint(uint32_t mbar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(mbar), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+
+__device__ __forceinline__ void mbar_arrive(uint32_t mbar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(mbar) : "memory");
+}
+
+// Wait inside a multi-role pipeline: gives up when the time-out is hit or when another role has
+// raised the CTA's abort flag, so that a broken hand-shake ends the kernel instead of hanging it.
+__device__ __forceinline__ bool mbar_wait_abortable(uint32_t mbar, uint32_t parity, volatile int* abort_flag) {
+    for (uint32_t i = 0; i < (1u << 22); ++i) {
+        if (mbar_try_wait_nohint(mbar, parity)) return true;
+        if (*abort_flag) return false;
+    }
+    *abort_flag = 1;
+    return false;
+}
+
+// register reallocation between the warpgroups of a warp-specialised kernel
+template <int N>
+__device__ __forceinline__ void setmaxnreg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
+template <int N>
+__device__ __forceinline__ void setmaxnreg_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
+
 // Bounded wait: a wrong descriptor must not hang the GPU box.  Returns false on time-out.
 __device__ __forceinline__ bool mbar_wait(uint32_t mbar, uint32_t parity) {
     for (uint32_t i = 0; i < (1u << 24); ++i)
@@ -114,6 +150,14 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&r)[16]) {
           "=r"(u[8]), "=r"(u[9]), "=r"(u[10]), "=r"(u[11]), "=r"(u[12]), "=r"(u[13]), "=r"(u[14]), "=r"(u[15])
         : "r"(taddr)
         : "memory");
+}
+// 8 consecutive fp32 columns of this thread's TMEM lane
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, float (&r)[8]) {
+    uint32_t* u = reinterpret_cast<uint32_t*>(r);
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3]), "=r"(u[4]), "=r"(u[5]), "=r"(u[6]), "=r"(u[7])
+                 : "r"(taddr)
+                 : "memory");
 }
 __device__ __forceinline__ void tmem_ld2(uint32_t taddr, float& a, float& b) {
     uint32_t x, y;

@@ -12,8 +12,8 @@
 //   twiddle   B[k1, n2] = A1[k1, n2] * W_4096^(n2 k1)                     CUDA cores, out of TMEM
 //   stage 2   X[k1 + 64 k2] = sum_n2 B[k1, n2] W_64^(n2 k2)
 //             D2[(k2, re|im), (seg, ch, k1)] = F2[(k2, c'), (n2, c)] * B2[(seg, ch, k1), (n2, c)]
-//                                                                         M = 128, N = 224, K = 128
-// Lane (k2, c) of D2 holds one component of X and Y of 33 bins for every segment of the batch,
+//                                                                         M = 128, N = 144, K = 128
+// Lane (k2, c) of D2 holds one component of X and Y of 33 bins for both segments of a batch,
 // so the cross-spectral sums are thread-local (one shuffle for the mixed Im term) and every
 // lane owns distinct bins: 132 accumulator registers, no redundancy.  Rows k1 = 33..63 of
 // stage 1 are never computed: bins with f mod 64 > 32 come from lanes k2 >= 32 by Hermitian
@@ -22,6 +22,16 @@
 // terms (hi + lo, 22 significant bits, two MMAs per product); the data is scaled by a power of
 // two to unit-ish rms and rounded ONCE to fp16 at each stage -- a zero-mean relative error of
 // 2^-12 per element that averages out over the segments (use for Navr >~ 10^4).
+//
+// Execution: one persistent CTA per SM, warp-specialised, all hand-shakes through mbarriers:
+//   warpgroup 0  epilogue   D2 (TMEM) -> register accumulators                 (128 threads)
+//   warpgroup 1  twiddle    D1 (TMEM) -> twiddle -> fp16 -> B2 operand (smem)   (128 threads)
+//   warpgroup 2-5 loaders   global -> detrend -> window -> fp16 -> A1 operand; set g (8 warps)
+//                           takes the segments of parity g and owns A1 slot g   (2 x 256 threads)
+//   warp 24      MMA issue  one thread: stage 1 of batch b+1 is issued BEFORE stage 2 of batch b,
+//                           so the tensor pipe has work while the twiddle group prepares B2
+// A1, D1: 2 slots (one per segment parity); B2, D2: 2 slots (one per batch parity).  Registers
+// are moved from the twiddle and MMA warpgroups to the epilogue group with setmaxnreg.
 #include <cuda_fp16.h>
 
 #include <map>
@@ -35,18 +45,31 @@ namespace pyfft {
 
 namespace tcw {
 constexpr int L = 4096, NBIN = L / 2 + 1;
-constexpr int SEGS = 3;                      // segments per batch (per team)
+constexpr int SEGS = 2;                      // segments per stage-2 batch
 constexpr int COLS_PER_SEG = 72;             // D2 columns per segment: X at +0 (33), Y at +36 (33)
 constexpr int YOFF = 36;                     // (multiples of 4 and of 8*k+4: cheap swizzle arithmetic)
-constexpr int N2 = 224;                      // stage-2 MMA N (3 * 72 = 216, padded to a multiple of 16)
+constexpr int N2 = SEGS * COLS_PER_SEG;      // stage-2 MMA N = 144 (a multiple of 16)
 constexpr int NLIN = 8;                      // bins with linear sums (mean correction)
+constexpr int NTHREADS = 896;
+constexpr int HEAD = 3 * L;                  // samples per channel of the materialised reflect zone
 // constant block (global -> shared), byte offsets
 constexpr int OFF_GHI = 0, OFF_GLO = 8192, OFF_F2HI = 16384, OFF_F2LO = 49152, OFF_TW = 81920;
 constexpr int CONST_BYTES = 81920 + 33 * 64 * 8;           // 98816
-constexpr int OFF_WIN = CONST_BYTES;                         // float[4096]
-constexpr int OFF_TEAM = 115712;                             // 1024-aligned
-constexpr int TEAM_BYTES = N2 * 128 * 2;                     // B2: 224 rows x 128 halves (2 K atoms) = 57344
-constexpr int SMEM_BYTES = OFF_TEAM + 2 * TEAM_BYTES + 1024; // + alignment slack
+constexpr int WIN_LD = 68;                                   // window stored [n2][n1], padded: conflict-free LDS.128
+constexpr int OFF_WIN = CONST_BYTES;                         // float[64][WIN_LD] = 17408 bytes
+constexpr int OFF_A1 = 116736;                               // 1024-aligned; 2 slots of 128 rows x 64 halves
+constexpr int A1_BYTES = 16384;
+constexpr int OFF_B2 = OFF_A1 + 2 * A1_BYTES;                // 2 slots of N2 rows x 128 halves (2 K atoms)
+constexpr int B2_BYTES = N2 * 128 * 2;                       // 36864
+constexpr int SMEM_BYTES = OFF_B2 + 2 * B2_BYTES + 1024;     // + alignment slack = 224256
+static_assert(OFF_WIN + 64 * WIN_LD * 4 <= OFF_A1, "window table overlaps the operand slots");
+// tensor memory columns
+constexpr int TM_D1 = 0;                                     // 2 slots x 64 columns
+constexpr int TM_D2 = 128;                                   // 2 slots x N2 columns
+// mbarriers
+enum { A1_FULL = 0, S1_DONE = 2, D1_FREE = 4, B2_FULL = 6, S2_DONE = 8, D2_FREE = 10, NBARS = 12 };
+// registers per thread after reallocation (launch: 72; released 512*16 + 128*(16 + 32) = requested 128*112)
+constexpr int REGS_EPI = 184, REGS_TWD = 56, REGS_LDR = 56, REGS_MMA = 40;
 }  // namespace tcw
 
 struct TcParams {
@@ -59,254 +82,156 @@ struct TcParams {
     const double* est;        // (mean, -) pairs: x first, then the y channels
     const double* prescale;   // power-of-two scale per channel, same order
     const unsigned char* consts;
+    const float* head;        // [nch+1][HEAD]: analysed samples j < head_len materialised (reflect zone)
+    int64_t head_len;         // segments that start before map.reflect read from head instead of x / y
     float* partial;           // [nch][nparts][4][NBIN]
     int nparts;
     float* lin_partial;       // [nch][nparts][4][L/16]  (zeroed by the host; bins < NLIN written)
     double* dev_sums;         // [nch+1]
     int* status;
+    long long* trace;         // debug: [batch][16] clock64 stamps of CTA (0, 0), or NULL
 };
-
-__device__ __forceinline__ void team_sync(int team) { asm volatile("bar.sync %0, 128;" ::"r"(team + 1) : "memory"); }
 
 __device__ __forceinline__ uint32_t pack_h2(float a, float b) {
     __half2 h = __floats2half2_rn(a, b);
     return *reinterpret_cast<uint32_t*>(&h);
 }
 
-__global__ void __launch_bounds__(256, 1) welch_tc_kernel(const TcParams p) {
+#define PYFFT_TC_TRACE(EV, B) \
+    if (trace_on) p.trace[(B) * 16 + (EV)] = clock64();
+
+// one cross-spectral update of a lane's accumulators for bin slot k1
+#define PYFFT_TC_ACC(K1, XX, YY)                                              \
+    {                                                                         \
+        const float xo_ = __shfl_xor_sync(0xffffffffu, (XX), 1);              \
+        acc[K1][0] = fmaf((XX), (XX), acc[K1][0]);                            \
+        acc[K1][1] = fmaf((YY), (YY), acc[K1][1]);                            \
+        acc[K1][2] = fmaf((YY), (XX), acc[K1][2]);                            \
+        acc[K1][3] = fmaf((YY), xo_, acc[K1][3]);                             \
+    }
+
+__global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcParams p) {
     using namespace tcw;
     using namespace tc;
     extern __shared__ unsigned char smem_raw[];
-    __shared__ __align__(8) unsigned long long mbar_store[2];
+    __shared__ __align__(8) unsigned long long bars[NBARS];
     __shared__ uint32_t tmem_slot;
+    __shared__ int abort_store;
 
     const uint32_t raw = (uint32_t)__cvta_generic_to_shared(smem_raw);
     const uint32_t pad = (1024u - (raw & 1023u)) & 1023u;
     unsigned char* sm = smem_raw + pad;
     const uint32_t sm_addr = raw + pad;
+    const uint32_t bar0 = (uint32_t)__cvta_generic_to_shared(&bars[0]);
+    volatile int* abort_flag = &abort_store;
 
-    const int tid = threadIdx.x;
-    const int team = tid >> 7, tt = tid & 127, warp_t = tt >> 5;
+    const int tid = threadIdx.x, warp = tid >> 5, wg = warp >> 2;
     const int pair = blockIdx.y;
+    const bool trace_on = p.trace != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && (tid & 127) == 0;
+    if (p.trace != nullptr && tid == 0) {
+        unsigned long long t_;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));
+        p.trace[2048 + 4 * (blockIdx.y * gridDim.x + blockIdx.x)] = (long long)t_;
+        p.trace[2048 + 4 * (blockIdx.y * gridDim.x + blockIdx.x) + 2] = clock64();
+    }
 
     // ---- one-time setup: constants, window, barriers, tensor memory ---------------------- //
     {
         const uint4* src = reinterpret_cast<const uint4*>(p.consts);
         uint4* dst = reinterpret_cast<uint4*>(sm);
-        for (int i = tid; i < CONST_BYTES / 16; i += 256) dst[i] = src[i];
+        for (int i = tid; i < CONST_BYTES / 16; i += NTHREADS) dst[i] = src[i];
         float* sw = reinterpret_cast<float*>(sm + OFF_WIN);
-        for (int i = tid; i < L; i += 256) sw[i] = p.window[i];
+        for (int n = tid; n < L; n += NTHREADS) sw[(n & 63) * WIN_LD + (n >> 6)] = p.window[n];
     }
-    const uint32_t mbar = (uint32_t)__cvta_generic_to_shared(&mbar_store[team]);
-    if (tt == 0) { mbar_init(mbar, 1); fence_mbar_init(); }
-    if (tid < 32) tmem_alloc((uint32_t)__cvta_generic_to_shared(&tmem_slot), 512);
+    if (tid == 0) {
+        abort_store = 0;
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(bar0 + 8 * (A1_FULL + i), 256);
+            mbar_init(bar0 + 8 * (S1_DONE + i), 1);
+            mbar_init(bar0 + 8 * (D1_FREE + i), 128);
+            mbar_init(bar0 + 8 * (B2_FULL + i), 128);
+            mbar_init(bar0 + 8 * (S2_DONE + i), 1);
+            mbar_init(bar0 + 8 * (D2_FREE + i), 128);
+        }
+        fence_mbar_init();
+    }
+    if (warp == 0) tmem_alloc((uint32_t)__cvta_generic_to_shared(&tmem_slot), 512);
     fence_async_smem();
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tcol = tmem_slot + (uint32_t)team * 256u;                // this team's column base
-    const uint32_t tlane = tcol + ((uint32_t)(warp_t * 32) << 16);          // + this warp's lane quarter
+    const uint32_t tbase = tmem_slot;
 
-    // ---- per-thread roles ------------------------------------------------------------------ //
-    // loader / twiddle stage: row r = tt = (ch, n2) of the stage-1 operand
-    const int ch = tt >> 6, n2 = tt & 63;
-    const int cidx = ch == 0 ? 0 : 1 + pair;
-    const float* __restrict__ src = ch == 0 ? p.x : p.y + (int64_t)pair * p.y_stride;
-    const float mean_f = (float)p.est[2 * cidx];
-    const float sc = (float)p.prescale[cidx];
-    const float nms = -mean_f * sc;                                         // exact: sc is a power of two
-    const float* __restrict__ swin = reinterpret_cast<const float*>(sm + OFF_WIN);
-    const float2* __restrict__ stw = reinterpret_cast<const float2*>(sm + OFF_TW);
-    unsigned char* __restrict__ tbuf = sm + OFF_TEAM + team * TEAM_BYTES;
-    const uint32_t tbuf_addr = sm_addr + OFF_TEAM + team * TEAM_BYTES;
-    const uint32_t a1_row = (uint32_t)((tt >> 3) * 1024 + (tt & 7) * 128);  // own row of a 128-row K atom
-    const int hb = (int)(p.hop >> 9);                                       // 8-sample chunks inside the hop
-    // stage-2 operand: 16-byte chunk of this thread's (n2, re|im) pair inside row r, XOR (r & 7);
-    // r & 7 = (k1 + 4 ch) & 7 because the row bases are multiples of 8 (x) or 8m + 4 (y)
-    uint32_t xorv[8];
-#pragma unroll
-    for (int i = 0; i < 8; ++i) xorv[i] = (uint32_t)((((n2 & 31) >> 2) ^ ((i + 4 * ch) & 7)) << 4);
-
-    // epilogue: lane (k2, c) of the stage-2 accumulator
-    float acc[33][4];
-    float linx[NLIN], liny[NLIN];
-#pragma unroll
-    for (int k = 0; k < 33; ++k)
-#pragma unroll
-        for (int q = 0; q < 4; ++q) acc[k][q] = 0.f;
-#pragma unroll
-    for (int k = 0; k < NLIN; ++k) { linx[k] = 0.f; liny[k] = 0.f; }
-    float devsum = 0.f;
-
-    const int part = blockIdx.x * 2 + team;
     const int64_t c0 = (int64_t)blockIdx.x * p.chunk;
     const int64_t c1 = (c0 + p.chunk < p.seg_count) ? c0 + p.chunk : p.seg_count;
-    uint32_t parity = 0;
-    bool ok = true;
+    const int nb = c1 > c0 ? (int)((c1 - c0 + 1) >> 1) : 0;                  // batches of two segments
 
-    for (int64_t kb = c0 + (int64_t)team * SEGS; kb < c1; kb += 2 * SEGS) {
-        // ================= P1: gather -> detrend -> window -> fp16 -> stage-1 operand ======== //
+    if (wg == 0) {
+        // ================= epilogue: D2 -> cross-spectral sums in registers =================== //
+        setmaxnreg_inc<REGS_EPI>();
+        const uint32_t tl = tbase + ((uint32_t)(warp * 32) << 16) + TM_D2;   // this warp's lane quarter
+        float acc[33][4];
+        float linx[NLIN], liny[NLIN];
+#pragma unroll
+        for (int k = 0; k < 33; ++k)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) acc[k][q] = 0.f;
+#pragma unroll
+        for (int k = 0; k < NLIN; ++k) { linx[k] = 0.f; liny[k] = 0.f; }
+
 #pragma unroll 1
-        for (int sg = 0; sg < SEGS; ++sg) {
-            const int64_t k = kb + sg;
-            unsigned char* rowp = tbuf + sg * 16384 + a1_row;
-            if (k >= c1) {
-#pragma unroll
-                for (int c = 0; c < 8; ++c) *reinterpret_cast<uint4*>(rowp + (c << 4)) = make_uint4(0, 0, 0, 0);
-                continue;
-            }
-            const int64_t j0 = (p.seg_first + k) * p.hop;
-            const bool plain = j0 >= p.map.reflect;
-            const float* __restrict__ q = src + (j0 - p.map.reflect + p.map.i0 - p.map.src_base) + n2;
-#pragma unroll
-            for (int hf = 0; hf < 2; ++hf) {                   // 32 loads in flight per thread
-                float v[32];
-                if (plain) {
-#pragma unroll
-                    for (int i = 0; i < 32; ++i) v[i] = q[64 * (32 * hf + i)];
-                } else {
-#pragma unroll
-                    for (int i = 0; i < 32; ++i) v[i] = src[src_index(p.map, j0 + 64 * (32 * hf + i) + n2)];
-                }
-#pragma unroll
-                for (int cc = 0; cc < 4; ++cc) {
-                    const int c = 4 * hf + cc;
-                    float* u = v + 8 * cc;
-                    float wv[8];
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) wv[i] = swin[64 * (8 * c + i) + n2];
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) u[i] = fmaf(u[i], sc, nms);               // (x - mean) * scale
-                    if (c < hb) devsum += ((u[0] + u[1]) + (u[2] + u[3])) + ((u[4] + u[5]) + (u[6] + u[7]));
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) u[i] *= wv[i];
-                    uint4 w;
-                    w.x = pack_h2(u[0], u[1]); w.y = pack_h2(u[2], u[3]);
-                    w.z = pack_h2(u[4], u[5]); w.w = pack_h2(u[6], u[7]);
-                    *reinterpret_cast<uint4*>(rowp + ((c ^ (tt & 7)) << 4)) = w;
-                }
-            }
-        }
-        // pull this team's next batch into L2 while the tensor core works on this one
-        {
-            const int64_t kn = kb + 2 * SEGS;
-            const int64_t jn = (p.seg_first + kn) * p.hop;
-            if (kn < c1 && jn >= p.map.reflect) {
-                const float* nb = src + (jn - p.map.reflect + p.map.i0 - p.map.src_base);
-                const int64_t nsamp = (int64_t)(SEGS - 1) * p.hop + L;
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const int64_t off = ((int64_t)n2 * 4 + i) * 32;
-                    if (off < nsamp) asm volatile("prefetch.global.L2 [%0];" ::"l"(nb + off));
-                }
-            }
-        }
-        fence_async_smem();
-        team_sync(team);
-
-        // ================= P2: stage-1 MMAs (one thread) ===================================== //
-        if (tt == 0) {
+        for (int b = 0; b < nb; ++b) {
+            const int s = b & 1;
+            if (!mbar_wait_abortable(bar0 + 8 * (S2_DONE + s), (uint32_t)(b >> 1) & 1u, abort_flag)) break;
             tc_fence_after();
-            constexpr uint32_t id1 = idesc_f16(128, 64);
-#pragma unroll 1
+            PYFFT_TC_TRACE(10, b)
+#pragma unroll
             for (int sg = 0; sg < SEGS; ++sg) {
-#pragma unroll
-                for (int h = 0; h < 2; ++h)
-#pragma unroll
-                    for (int ks = 0; ks < 4; ++ks)
-                        mma_f16(tcol + sg * 64, sw128_desc(tbuf_addr + sg * 16384 + ks * 32),
-                                sw128_desc(sm_addr + (h ? OFF_GLO : OFF_GHI) + ks * 32), id1, (h | ks) ? 1u : 0u);
-            }
-            mma_commit(mbar);
-        }
-        ok = mbar_wait(mbar, parity) && ok;
-        parity ^= 1;
-        tc_fence_after();
-
-        // ================= P3: twiddle, fp16, stage-2 operand ================================= //
-#pragma unroll 1
-        for (int sg = 0; sg < SEGS; ++sg) {
-            float d0[32], d1[32];
-            tmem_ld32(tlane + sg * 64, d0);
-            tmem_ld32(tlane + sg * 64 + 32, d1);
-            tmem_ld_wait();
-            // d0[k1] = Re A1[k1] (k1 < 32), d1[0] = Re A1[32], d1[k1] = Im A1[k1] (k1 = 1..31)
-            // row r = sg*72 + ch*36 + k1 of the stage-2 operand; 8-row groups are contiguous, so the
-            // row offset is r*128 and only the 16-byte chunk index is XOR-ed with (r & 7)
-            unsigned char* bp = tbuf + (n2 >> 5) * (N2 * 128) + (n2 & 3) * 4 + (sg * COLS_PER_SEG + ch * YOFF) * 128;
-#pragma unroll
-            for (int g = 0; g < 5; ++g) {                        // k1 = 8g .. 8g+7 (g = 4: k1 = 32 only)
-                float2 t[8];
-#pragma unroll
-                for (int i = 0; i < 8; ++i)
-                    if (8 * g + i <= 32) t[i] = stw[(8 * g + i) * 64 + n2];      // twiddles of the group first
-                uint32_t w[8];
+                const uint32_t col = tl + s * N2 + sg * COLS_PER_SEG;
+                // software pipeline over chunks of 8 bins: the next chunk is in flight during the FMAs
+                float xa[8], ya[8], xb[8], yb[8];
+                tmem_ld8(col, xa);
+                tmem_ld8(col + YOFF, ya);
+                tmem_ld_wait();
+                tmem_ld8(col + 8, xb);
+                tmem_ld8(col + YOFF + 8, yb);
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
-                    const int k1 = 8 * g + i;
-                    if (k1 <= 32) {
-                        const float re = k1 < 32 ? d0[k1] : d1[0];
-                        const float im = (k1 >= 1 && k1 <= 31) ? d1[k1] : 0.f;
-                        w[i] = pack_h2(re * t[i].x - im * t[i].y, re * t[i].y + im * t[i].x);
-                    }
+                    PYFFT_TC_ACC(i, xa[i], ya[i]);
+                    if (i < NLIN) { linx[i] += xa[i]; liny[i] += ya[i]; }
                 }
+                tmem_ld_wait();
+                tmem_ld8(col + 16, xa);
+                tmem_ld8(col + YOFF + 16, ya);
 #pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    const int k1 = 8 * g + i;
-                    if (k1 <= 32) *reinterpret_cast<uint32_t*>(bp + k1 * 128 + xorv[k1 & 7]) = w[i];
+                for (int i = 0; i < 8; ++i) PYFFT_TC_ACC(8 + i, xb[i], yb[i]);
+                tmem_ld_wait();
+                tmem_ld8(col + 24, xb);
+                tmem_ld8(col + YOFF + 24, yb);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) PYFFT_TC_ACC(16 + i, xa[i], ya[i]);
+                tmem_ld_wait();
+                float x32, y32, d0, d1;
+                tmem_ld2(col + 32, x32, d0);
+                tmem_ld2(col + YOFF + 32, y32, d1);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) PYFFT_TC_ACC(24 + i, xb[i], yb[i]);
+                tmem_ld_wait();
+                if (sg == SEGS - 1) {                                        // D2 slot is in registers now
+                    tc_fence_before();
+                    mbar_arrive(bar0 + 8 * (D2_FREE + s));
+                    PYFFT_TC_TRACE(11, b)
                 }
+                PYFFT_TC_ACC(32, x32, y32);
             }
         }
-        tc_fence_before();
-        fence_async_smem();
-        team_sync(team);
 
-        // ================= P4: stage-2 MMAs (one thread) ===================================== //
-        if (tt == 0) {
-            tc_fence_after();
-            constexpr uint32_t id2 = idesc_f16(128, N2);
-#pragma unroll
-            for (int h = 0; h < 2; ++h)
-#pragma unroll
-                for (int ks = 0; ks < 8; ++ks)
-                    mma_f16(tcol, sw128_desc(sm_addr + (h ? OFF_F2LO : OFF_F2HI) + (ks >> 2) * (128 * 128) + (ks & 3) * 32),
-                            sw128_desc(tbuf_addr + (ks >> 2) * (N2 * 128) + (ks & 3) * 32), id2, (h | ks) ? 1u : 0u);
-            mma_commit(mbar);
-        }
-        ok = mbar_wait(mbar, parity) && ok;
-        parity ^= 1;
-        tc_fence_after();
-
-        // ================= P5: cross-spectral accumulation out of TMEM ======================== //
-#pragma unroll 1
-        for (int sg = 0; sg < SEGS; ++sg) {
-            float xv[32], yv[32], x32, y32, pad0, pad1;
-            tmem_ld32(tlane + sg * COLS_PER_SEG, xv);
-            tmem_ld2(tlane + sg * COLS_PER_SEG + 32, x32, pad0);
-            tmem_ld32(tlane + sg * COLS_PER_SEG + YOFF, yv);
-            tmem_ld2(tlane + sg * COLS_PER_SEG + YOFF + 32, y32, pad1);
-            tmem_ld_wait();
-#pragma unroll
-            for (int k1 = 0; k1 <= 32; ++k1) {
-                const float xx = k1 < 32 ? xv[k1] : x32;
-                const float yy = k1 < 32 ? yv[k1] : y32;
-                const float xo = __shfl_xor_sync(0xffffffffu, xx, 1);   // the other component of X
-                acc[k1][0] = fmaf(xx, xx, acc[k1][0]);
-                acc[k1][1] = fmaf(yy, yy, acc[k1][1]);
-                acc[k1][2] = fmaf(yy, xx, acc[k1][2]);
-                acc[k1][3] = fmaf(yy, xo, acc[k1][3]);
-                if (k1 < NLIN) { linx[k1] += xx; liny[k1] += yy; }
-            }
-        }
-        tc_fence_before();
-    }
-
-    // ---- write the team's partial sums ------------------------------------------------------- //
-    {
+        // ---- write the CTA's partial sums ---------------------------------------------------- //
         const float sx = (float)p.prescale[0], sy = (float)p.prescale[1 + pair];
         const float i00 = 1.f / (sx * sx), i11 = 1.f / (sy * sy), i01 = 1.f / (sx * sy);
-        const int k2 = tt >> 1, c = tt & 1;
-        float* out = p.partial + ((size_t)pair * p.nparts + part) * 4 * NBIN;
+        const int k2 = tid >> 1, c = tid & 1;
+        float* out = p.partial + ((size_t)pair * p.nparts + blockIdx.x) * 4 * NBIN;
 #pragma unroll
         for (int k1 = 0; k1 <= 32; ++k1) {
             const float t0 = acc[k1][0] + __shfl_xor_sync(0xffffffffu, acc[k1][0], 1);
@@ -332,24 +257,218 @@ __global__ void __launch_bounds__(256, 1) welch_tc_kernel(const TcParams p) {
             }
         }
         if (k2 == 0) {
-            float* lo = p.lin_partial + ((size_t)pair * p.nparts + part) * 4 * (L / 16);
+            float* lo = p.lin_partial + ((size_t)pair * p.nparts + blockIdx.x) * 4 * (L / 16);
 #pragma unroll
             for (int k1 = 0; k1 < NLIN; ++k1) {
                 lo[(0 + c) * (L / 16) + k1] = linx[k1] / sx;       // rows 0/1: Re/Im sum U
                 lo[(2 + c) * (L / 16) + k1] = liny[k1] / sy;       // rows 2/3: Re/Im sum V
             }
         }
+    } else if (wg == 1) {
+        // ================= twiddle: D1 -> W_4096^(n2 k1) -> fp16 -> stage-2 operand ========== //
+        setmaxnreg_dec<REGS_TWD>();
+        const int ln = tid - 128;                                            // TMEM lane = row (ch, n2) of D1
+        const int ch = ln >> 6, n2 = ln & 63;
+        const uint32_t tl = tbase + ((uint32_t)((warp & 3) * 32) << 16) + TM_D1;
+        const float2* __restrict__ tw = reinterpret_cast<const float2*>(sm + OFF_TW) + n2;
+        // row r = sg*72 + ch*36 + k1 of the operand; 8-row groups are contiguous, so the row offset
+        // is r*128 and only the 16-byte chunk index is XOR-ed with r & 7 = (k1 + 4 ch) & 7
+        const uint32_t thread_off = (uint32_t)((n2 >> 5) * (N2 * 128) + (n2 & 3) * 4 + ch * YOFF * 128);
+        const uint32_t xbase = (uint32_t)((((n2 & 31) >> 2) ^ (4 * ch)) << 4);   // chunk ^ (k1 & 7) = xbase ^ (i << 4)
+
+#pragma unroll 1
+        for (int b = 0; b < nb; ++b) {
+            const int s = b & 1;
+            // the stage-2 MMAs of batch b-2 have finished reading this B2 slot
+            if (b >= 2 && !mbar_wait_abortable(bar0 + 8 * (S2_DONE + s), ((uint32_t)(b >> 1) & 1u) ^ 1u, abort_flag)) break;
+            bool live = true;
+#pragma unroll 1
+            for (int g = 0; g < SEGS; ++g) {
+                if (!mbar_wait_abortable(bar0 + 8 * (S1_DONE + g), (uint32_t)b & 1u, abort_flag)) { live = false; break; }
+                tc_fence_after();
+                PYFFT_TC_TRACE(7 + g, b)
+                const uint32_t col = tl + g * 64;
+                unsigned char* bp = sm + OFF_B2 + s * B2_BYTES + thread_off + g * (COLS_PER_SEG * 128);
+                float ra[8], ia[8], rb[8], ib[8];
+                tmem_ld8(col, ra);
+                tmem_ld8(col + 32, ia);                   // ia[0] = Re A1[32]; Im A1[0] = 0
+                tmem_ld_wait();
+                const float re32 = ia[0];
+                ia[0] = 0.f;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {             // k1 = 8q .. 8q+7
+                    const float* re = (q & 1) ? rb : ra;
+                    const float* im = (q & 1) ? ib : ia;
+                    if (q < 3) {                          // next group in flight during the math
+                        if (q & 1) {
+                            tmem_ld8(col + 8 * (q + 1), ra);
+                            tmem_ld8(col + 32 + 8 * (q + 1), ia);
+                        } else {
+                            tmem_ld8(col + 8 * (q + 1), rb);
+                            tmem_ld8(col + 32 + 8 * (q + 1), ib);
+                        }
+                    }
+                    float2 t[8];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) t[i] = tw[(8 * q + i) * 64];
+                    uint32_t w[8];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i)
+                        w[i] = pack_h2(re[i] * t[i].x - im[i] * t[i].y, re[i] * t[i].y + im[i] * t[i].x);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i)
+                        *reinterpret_cast<uint32_t*>(bp + (8 * q + i) * 128 + (xbase ^ (uint32_t)(i << 4))) = w[i];
+                    if (q < 3) tmem_ld_wait();
+                    if (q == 2) {                         // the last D1 columns are in registers: slot free
+                        tc_fence_before();
+                        mbar_arrive(bar0 + 8 * (D1_FREE + g));
+                    }
+                }
+                {
+                    const float2 t32 = tw[32 * 64];
+                    *reinterpret_cast<uint32_t*>(bp + 32 * 128 + xbase) = pack_h2(re32 * t32.x, re32 * t32.y);
+                }
+            }
+            if (!live) break;
+            fence_async_smem();
+            mbar_arrive(bar0 + 8 * (B2_FULL + s));
+            PYFFT_TC_TRACE(9, b)
+        }
+    } else if (wg <= 5) {
+        // ================= loaders: gather -> detrend -> window -> fp16 -> stage-1 operand ==== //
+        // Two sets of 8 warps; set g takes the segments of parity g and owns A1 slot g.  Thread
+        // (half, ch, n2) converts the 32 samples n = 64 (32 half + i) + n2 of its operand row.  The
+        // loads of the set's next segment are issued before it waits for the slot, so their latency
+        // overlaps the stage-1 MMAs of the previous batch and the other set's conversion.
+        setmaxnreg_dec<REGS_LDR>();
+        const int lt = tid - 256;
+        const int g = lt >> 8;                                               // set = segment parity = A1 slot
+        const int hf = (lt >> 7) & 1, tt = lt & 127;
+        const int ch = tt >> 6, n2 = tt & 63;                                // operand row (ch, n2)
+        const int cidx = ch == 0 ? 0 : 1 + pair;
+        const float* __restrict__ src = ch == 0 ? p.x : p.y + (int64_t)pair * p.y_stride;
+        const float sc = (float)p.prescale[cidx];
+        const float nms = -(float)p.est[2 * cidx] * sc;                      // exact: sc is a power of two
+        const float4* __restrict__ wrow =
+            reinterpret_cast<const float4*>(sm + OFF_WIN + n2 * (WIN_LD * 4) + hf * 128);
+        unsigned char* rowp = sm + OFF_A1 + g * A1_BYTES + (tt >> 3) * 1024 + (tt & 7) * 128;
+        const int sw = tt & 7;
+        const int hb = (int)(p.hop >> 9) - 4 * hf;                           // chunks of this half inside the hop
+        // segments that start in the reflect-padded zone read the materialised head of the record
+        const float* __restrict__ hsrc = p.head + (int64_t)cidx * HEAD + n2 + 2048 * hf;
+        const float* __restrict__ psrc = src + (p.map.i0 - p.map.reflect - p.map.src_base) + n2 + 2048 * hf;
+        // L2 prefetch two segments of this set ahead: 128 lines of 128 bytes per channel, half hf
+        // of the lines, one per thread n2
+        const float* pf = src + (p.map.i0 - p.map.reflect - p.map.src_base) + (hf * 64 + n2) * 32;
+        const int64_t first = p.seg_first + c0 + g;
+        float devsum = 0.f;
+
+#pragma unroll 1
+        for (int b = 0; b < nb; ++b) {
+            const bool have = c0 + 2 * b + g < c1;
+            float v[32];
+            if (have) {
+                const int64_t j0 = (first + 2 * b) * p.hop;
+                const float* __restrict__ q = (j0 < p.map.reflect ? hsrc : psrc) + j0;
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] = q[64 * i];
+                if (c0 + 2 * b + g + 4 < c1) {
+                    const int64_t jn = (first + 2 * b + 4) * p.hop;
+                    if (jn >= p.map.reflect) asm volatile("prefetch.global.L2 [%0];" ::"l"(pf + jn));
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] = 0.f;
+            }
+            // the stage-1 MMAs of the previous batch have finished reading this A1 slot
+            if (b >= 1 && !mbar_wait_abortable(bar0 + 8 * (S1_DONE + g), (uint32_t)(b - 1) & 1u, abort_flag)) break;
+            if (hf == 0) { PYFFT_TC_TRACE(2 * g, b) }
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                float* u = v + 8 * c;
+                const float4 w0 = wrow[2 * c], w1 = wrow[2 * c + 1];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) u[i] = fmaf(u[i], sc, nms);                   // (x - mean) * scale
+                if (have && c < hb) devsum += ((u[0] + u[1]) + (u[2] + u[3])) + ((u[4] + u[5]) + (u[6] + u[7]));
+                uint4 o;
+                o.x = pack_h2(u[0] * w0.x, u[1] * w0.y); o.y = pack_h2(u[2] * w0.z, u[3] * w0.w);
+                o.z = pack_h2(u[4] * w1.x, u[5] * w1.y); o.w = pack_h2(u[6] * w1.z, u[7] * w1.w);
+                if (!have) o = make_uint4(0, 0, 0, 0);
+                *reinterpret_cast<uint4*>(rowp + (((4 * hf + c) ^ sw) << 4)) = o;
+            }
+            fence_async_smem();
+            mbar_arrive(bar0 + 8 * (A1_FULL + g));
+            if (hf == 0) { PYFFT_TC_TRACE(2 * g + 1, b) }
+        }
         double ds = (double)devsum / (double)sc;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) ds += __shfl_xor_sync(0xffffffffu, ds, o);
-        if ((tt & 31) == 0 && (ch == 1 || pair == 0)) atomicAdd(&p.dev_sums[cidx], ds);
+        if ((tid & 31) == 0 && (ch == 1 || pair == 0)) atomicAdd(&p.dev_sums[cidx], ds);
+    } else {
+        // ================= MMA issue (one thread) ============================================ //
+        setmaxnreg_dec<REGS_MMA>();
+        if (tid == 768) {
+            constexpr uint32_t id1 = idesc_f16(128, 64), id2 = idesc_f16(128, N2);
+#pragma unroll 1
+            for (int b = 0; b <= nb; ++b) {
+                bool live = true;
+                if (b < nb) {
+                    // stage 1 of batch b: one 128 x 64 x 64 product (hi + lo) per segment
+#pragma unroll 1
+                    for (int g = 0; g < SEGS; ++g) {
+                        live = live && mbar_wait_abortable(bar0 + 8 * (A1_FULL + g), (uint32_t)b & 1u, abort_flag);
+                        if (b >= 1)
+                            live = live && mbar_wait_abortable(bar0 + 8 * (D1_FREE + g), (uint32_t)(b - 1) & 1u, abort_flag);
+                        if (!live) break;
+                        tc_fence_after();
+                        const uint32_t a1 = sm_addr + OFF_A1 + g * A1_BYTES;
+#pragma unroll
+                        for (int h = 0; h < 2; ++h)
+#pragma unroll
+                            for (int ks = 0; ks < 4; ++ks)
+                                mma_f16(tbase + TM_D1 + g * 64, sw128_desc(a1 + ks * 32),
+                                        sw128_desc(sm_addr + (h ? OFF_GLO : OFF_GHI) + ks * 32), id1, (h | ks) ? 1u : 0u);
+                        mma_commit(bar0 + 8 * (S1_DONE + g));
+                        PYFFT_TC_TRACE(4 + g, b)
+                    }
+                }
+                if (!live) break;
+                if (b >= 1) {
+                    // stage 2 of batch b-1: 128 x 144 x 128 (hi + lo)
+                    const int bb = b - 1, s = bb & 1;
+                    live = mbar_wait_abortable(bar0 + 8 * (B2_FULL + s), (uint32_t)(bb >> 1) & 1u, abort_flag);
+                    if (bb >= 2)
+                        live = live && mbar_wait_abortable(bar0 + 8 * (D2_FREE + s), ((uint32_t)(bb >> 1) & 1u) ^ 1u, abort_flag);
+                    if (!live) break;
+                    tc_fence_after();
+                    const uint32_t b2 = sm_addr + OFF_B2 + s * B2_BYTES;
+#pragma unroll
+                    for (int h = 0; h < 2; ++h)
+#pragma unroll
+                        for (int ks = 0; ks < 8; ++ks)
+                            mma_f16(tbase + TM_D2 + s * N2,
+                                    sw128_desc(sm_addr + (h ? OFF_F2LO : OFF_F2HI) + (ks >> 2) * (128 * 128) + (ks & 3) * 32),
+                                    sw128_desc(b2 + (ks >> 2) * (N2 * 128) + (ks & 3) * 32), id2, (h | ks) ? 1u : 0u);
+                    mma_commit(bar0 + 8 * (S2_DONE + s));
+                    PYFFT_TC_TRACE(6, bb)
+                }
+            }
+        }
     }
-    if (!ok && tt == 0) atomicExch(p.status, 1);
 
     tc_fence_before();
     __syncthreads();
-    if (tid < 32) tmem_free(tmem_slot, 512);
+    if (tid == 0 && *abort_flag) atomicExch(p.status, 1);
+    if (p.trace != nullptr && tid == 0) {
+        unsigned long long t_;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));
+        p.trace[2048 + 4 * (blockIdx.y * gridDim.x + blockIdx.x) + 1] = (long long)t_;
+        p.trace[2048 + 4 * (blockIdx.y * gridDim.x + blockIdx.x) + 3] = clock64();
+    }
+    if (warp == 0) tmem_free(tbase, 512);
 }
+#undef PYFFT_TC_ACC
+#undef PYFFT_TC_TRACE
 
 // ------------------------------------------------------------------------- //
 // provisional statistics: mean (rounded to float) and a power-of-two scale that brings the
@@ -403,10 +522,23 @@ __global__ void tc_prepare_finish_kernel(const float* __restrict__ x, const floa
     prescale[c] = ldexp(1.0, sh2);
 }
 
+// materialises the analysed samples j < n of every channel (the reflect-padded zone and the
+// segments that reach into it), so that the loaders never evaluate the record map
+__global__ void __launch_bounds__(256) tc_head_kernel(const float* __restrict__ x, const float* __restrict__ y,
+                                                      int64_t y_stride, int pair0, RecMap map, int64_t n,
+                                                      float* __restrict__ head) {
+    const int c = blockIdx.y;                       // 0 = x, 1.. = y channels
+    const float* p = c == 0 ? x : y + (int64_t)(c - 1) * y_stride;
+    const int64_t j = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    if (j < n) head[(int64_t)c * tcw::HEAD + j] = p[src_index(map, j)];
+    (void)pair0;
+}
+
 // ------------------------------------------------------------------------- //
 // host side
 // ------------------------------------------------------------------------- //
 static std::mutex g_tc_mutex;
+static long long* g_tc_trace = nullptr;     // debug hook, see pyfft_debug_set_tc_trace
 static std::map<int, unsigned char*> g_tc_consts;
 
 static void put_half(std::vector<unsigned char>& buf, size_t off, __half h) {
@@ -473,7 +605,7 @@ static int tc_grid_x(int64_t seg_count, int nch) {
     int sms = device_sm_count();
     if (sms <= 0) sms = 148;
     int64_t want = (sms + nch - 1) / nch;
-    const int64_t maxb = (seg_count + 2 * tcw::SEGS - 1) / (2 * tcw::SEGS);
+    const int64_t maxb = (seg_count + tcw::SEGS - 1) / tcw::SEGS;
     if (want > maxb) want = maxb;
     if (want < 1) want = 1;
     return (int)want;
@@ -485,10 +617,18 @@ using namespace pyfft;
 
 extern "C" {
 
+// debug: device buffer of 16 long long per batch that CTA (0, 0) of the next launches fills with
+// clock64() stamps of its pipeline events (NULL switches it off); used by tools/tc_trace.py
+int pyfft_debug_set_tc_trace(void* buf) {
+    g_tc_trace = static_cast<long long*>(buf);
+    return PYFFT_OK;
+}
+
 int64_t pyfft_welch_tc_workspace_bytes(const pyfft_segmentation* seg, int32_t nch) {
     if (!seg || nch <= 0) return fail(PYFFT_EINVAL, "welch_tc_workspace_bytes: bad arguments");
     const int gx = tc_grid_x(seg->seg_count, nch);
-    return (int64_t)nch * gx * 2 * 4 * (tcw::NBIN + tcw::L / 16) * 4 + 8 * (int64_t)(nch + 1) + 16;
+    return (int64_t)nch * gx * 4 * (tcw::NBIN + tcw::L / 16) * 4 + 8 * (int64_t)(nch + 1) + 16 +
+           (int64_t)(nch + 1) * tcw::HEAD * 4;
 }
 
 int pyfft_welch_tc_prepare(const void* x, const void* y, int64_t y_stride, int32_t nch,
@@ -535,11 +675,22 @@ int pyfft_welch_accumulate_tc(const void* x, const void* y, int64_t y_stride, in
     if (!consts) return status;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const int gx = tc_grid_x(seg->seg_count, nch);
-    const int nparts = gx * 2;
+    const int nparts = gx;                        // one partial per CTA
     const int64_t main_bytes = (int64_t)nch * nparts * 4 * NBIN * 4;
     const int64_t lin_bytes = (int64_t)nch * nparts * 4 * (L / 16) * 4;
-    if (!workspace || workspace_bytes < main_bytes + lin_bytes + 8 * (int64_t)(nch + 1))
+    const int64_t sums_bytes = (8 * (int64_t)(nch + 1) + 15) & ~(int64_t)15;
+    const int64_t head_bytes = (int64_t)(nch + 1) * HEAD * 4;
+    if (!workspace || workspace_bytes < main_bytes + lin_bytes + sums_bytes + head_bytes)
         return fail(PYFFT_EINVAL, "welch_accumulate_tc: workspace too small");
+    // segments that start before map.reflect read a materialised copy of the head of the record
+    int64_t head_len = 0;
+    if (j_lo < m.reflect) {
+        const int64_t last = (m.reflect - 1) / seg->hop;                        // last segment that starts in the zone
+        const int64_t last_here = last < seg->seg_first + seg->seg_count - 1 ? last : seg->seg_first + seg->seg_count - 1;
+        head_len = last_here * seg->hop + L;
+        if (head_len > HEAD)
+            return fail(PYFFT_EUNSUPPORTED, "the tensor-core path supports reflect padding up to %d samples", 2 * L - 1);
+    }
     TcParams p;
     p.x = static_cast<const float*>(x);
     p.y = static_cast<const float*>(y);
@@ -548,23 +699,30 @@ int pyfft_welch_accumulate_tc(const void* x, const void* y, int64_t y_stride, in
     p.hop = seg->hop;
     p.seg_first = seg->seg_first;
     p.seg_count = seg->seg_count;
-    // chunk: a multiple of one round of both teams (6 segments) so that batches stay full
+    // chunk: a multiple of the batch size so that only the very last batch can be ragged
     int64_t chunk = (seg->seg_count + gx - 1) / gx;
-    chunk = (chunk + 2 * SEGS - 1) / (2 * SEGS) * (2 * SEGS);
+    chunk = (chunk + SEGS - 1) / SEGS * SEGS;
     p.chunk = chunk;
     p.window = static_cast<const float*>(window);
     p.est = est;
     p.prescale = prescale;
     p.consts = consts;
+    float* head = reinterpret_cast<float*>(static_cast<char*>(workspace) + main_bytes + lin_bytes + sums_bytes);
+    p.head = head;
+    p.head_len = head_len;
     p.partial = static_cast<float*>(workspace);
     p.nparts = nparts;
     p.lin_partial = reinterpret_cast<float*>(static_cast<char*>(workspace) + main_bytes);
     p.dev_sums = reinterpret_cast<double*>(static_cast<char*>(workspace) + main_bytes + lin_bytes);
     p.status = status_flag;
-    // teams that get no segment still write zeros; the linear sums are sparse -> clear them
+    p.trace = g_tc_trace;
+    // CTAs that get no segment still write zeros; the linear sums are sparse -> clear them
     PYFFT_CUDA_OK(cudaMemsetAsync(p.partial, 0, (size_t)(main_bytes + lin_bytes) + sizeof(double) * (size_t)(nch + 1), st));
+    if (head_len > 0)
+        tc_head_kernel<<<dim3((unsigned)((head_len + 255) / 256), nch + 1), 256, 0, st>>>(
+            p.x, p.y, y_stride, 0, m, head_len, head);
     PYFFT_CUDA_OK(cudaFuncSetAttribute(welch_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-    welch_tc_kernel<<<dim3(gx, nch), 256, SMEM_BYTES, st>>>(p);
+    welch_tc_kernel<<<dim3(gx, nch), NTHREADS, SMEM_BYTES, st>>>(p);
     PYFFT_LAUNCH_OK("welch_tc_kernel");
     if ((rc = welch_reduce_launch_f32(p.lin_partial, nparts, 4 * (L / 16), nch, lin, st))) return rc;
     if ((rc = welch_raw_sums_launch(p.dev_sums, est, nch + 1, (double)seg->seg_count * (double)seg->hop, stats, st)))

@@ -129,6 +129,8 @@ int main() {
     bad += run<64, 64>(200);
     bad += run<208, 128>(200);
     bad += run<256, 128>(200);
+    bad += run<144, 128>(200);
+    bad += run<128, 64>(200);
     printf(bad ? "PROBE FAILED\n" : "PROBE OK\n");
     return bad;
 }
