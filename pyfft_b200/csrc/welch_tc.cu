@@ -30,7 +30,7 @@
 //                           takes the segments of parity g and owns A1 slot g   (2 x 256 threads)
 //   warp 24      MMA issue  one thread: stage 1 of batch b+1 is issued BEFORE stage 2 of batch b,
 //                           so the tensor pipe has work while the twiddle group prepares B2
-// A1, D1: 2 slots (one per segment parity); B2, D2: 2 slots (one per batch parity).  Registers
+// A1: 2 slots (segment parity); D1: 3 slots (segment index % 3); B2, D2: 2 slots (batch parity).  Registers
 // are moved from the twiddle and MMA warpgroups to the epilogue group with setmaxnreg.
 #include <cuda_fp16.h>
 
@@ -64,12 +64,12 @@ constexpr int B2_BYTES = N2 * 128 * 2;                       // 36864
 constexpr int SMEM_BYTES = OFF_B2 + 2 * B2_BYTES + 1024;     // + alignment slack = 224256
 static_assert(OFF_WIN + 64 * WIN_LD * 4 <= OFF_A1, "window table overlaps the operand slots");
 // tensor memory columns
-constexpr int TM_D1 = 0;                                     // 2 slots x 64 columns
-constexpr int TM_D2 = 128;                                   // 2 slots x N2 columns
+constexpr int TM_D1 = 288;                                   // 3 slots x 64 columns (segment index % 3)
+constexpr int TM_D2 = 0;                                     // 2 slots x N2 columns (batch parity)
 // mbarriers
-enum { A1_FULL = 0, S1_DONE = 2, D1_FREE = 4, B2_FULL = 6, S2_DONE = 8, D2_FREE = 10, NBARS = 12 };
-// registers per thread after reallocation (launch: 72; released 512*16 + 128*(16 + 32) = requested 128*112)
-constexpr int REGS_EPI = 184, REGS_TWD = 56, REGS_LDR = 56, REGS_MMA = 40;
+enum { A1_FULL = 0, S1_DONE = 2, D1_FREE = 5, B2_FULL = 8, S2_DONE = 10, D2_FREE = 12, NBARS = 14 };
+// registers per thread after reallocation (launch: 72; released 512*16 + 128*16 + 128*24 = requested 128*104)
+constexpr int REGS_EPI = 176, REGS_TWD = 56, REGS_LDR = 56, REGS_MMA = 48;
 }  // namespace tcw
 
 struct TcParams {
@@ -148,11 +148,14 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
 #pragma unroll
         for (int i = 0; i < 2; ++i) {
             mbar_init(bar0 + 8 * (A1_FULL + i), 256);
-            mbar_init(bar0 + 8 * (S1_DONE + i), 1);
-            mbar_init(bar0 + 8 * (D1_FREE + i), 128);
             mbar_init(bar0 + 8 * (B2_FULL + i), 128);
             mbar_init(bar0 + 8 * (S2_DONE + i), 1);
             mbar_init(bar0 + 8 * (D2_FREE + i), 128);
+        }
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+            mbar_init(bar0 + 8 * (S1_DONE + i), 1);
+            mbar_init(bar0 + 8 * (D1_FREE + i), 128);
         }
         fence_mbar_init();
     }
@@ -266,6 +269,8 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
         }
     } else if (wg == 1) {
         // ================= twiddle: D1 -> W_4096^(n2 k1) -> fp16 -> stage-2 operand ========== //
+        // Both segments of a batch in lock-step (each twiddle factor is read once for the two), in
+        // groups of 4 k1 with the next group's TMEM loads in flight during the arithmetic.
         setmaxnreg_dec<REGS_TWD>();
         const int ln = tid - 128;                                            // TMEM lane = row (ch, n2) of D1
         const int ch = ln >> 6, n2 = ln & 63;
@@ -279,57 +284,60 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
 #pragma unroll 1
         for (int b = 0; b < nb; ++b) {
             const int s = b & 1;
+            const int s0 = 2 * b, s1 = 2 * b + 1;                            // segment indices; D1 slot = index % 3
+            const int d0 = s0 % 3, d1 = s1 % 3;
             // the stage-2 MMAs of batch b-2 have finished reading this B2 slot
             if (b >= 2 && !mbar_wait_abortable(bar0 + 8 * (S2_DONE + s), ((uint32_t)(b >> 1) & 1u) ^ 1u, abort_flag)) break;
-            bool live = true;
-#pragma unroll 1
-            for (int g = 0; g < SEGS; ++g) {
-                if (!mbar_wait_abortable(bar0 + 8 * (S1_DONE + g), (uint32_t)b & 1u, abort_flag)) { live = false; break; }
-                tc_fence_after();
-                PYFFT_TC_TRACE(7 + g, b)
-                const uint32_t col = tl + g * 64;
-                unsigned char* bp = sm + OFF_B2 + s * B2_BYTES + thread_off + g * (COLS_PER_SEG * 128);
-                float ra[8], ia[8], rb[8], ib[8];
-                tmem_ld8(col, ra);
-                tmem_ld8(col + 32, ia);                   // ia[0] = Re A1[32]; Im A1[0] = 0
-                tmem_ld_wait();
-                const float re32 = ia[0];
-                ia[0] = 0.f;
+            if (!mbar_wait_abortable(bar0 + 8 * (S1_DONE + d0), (uint32_t)(s0 / 3) & 1u, abort_flag)) break;
+            PYFFT_TC_TRACE(7, b)
+            if (!mbar_wait_abortable(bar0 + 8 * (S1_DONE + d1), (uint32_t)(s1 / 3) & 1u, abort_flag)) break;
+            tc_fence_after();
+            PYFFT_TC_TRACE(8, b)
+            const uint32_t ca = tl + d0 * 64, cb = tl + d1 * 64;
+            unsigned char* bp = sm + OFF_B2 + s * B2_BYTES + thread_off;     // segment 1: + COLS_PER_SEG rows
+            // group buffers: [0..3] Re seg 0, [4..7] Im seg 0, [8..11] Re seg 1, [12..15] Im seg 1
+            float ga[16], gb[16];
+            tmem_ld4(ca, &ga[0]);
+            tmem_ld4(ca + 32, &ga[4]);                    // first value = Re A1[32]; Im A1[0] = 0
+            tmem_ld4(cb, &ga[8]);
+            tmem_ld4(cb + 32, &ga[12]);
+            tmem_ld_wait();
+            const float re32a = ga[4], re32b = ga[12];
+            ga[4] = 0.f;
+            ga[12] = 0.f;
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {             // k1 = 8q .. 8q+7
-                    const float* re = (q & 1) ? rb : ra;
-                    const float* im = (q & 1) ? ib : ia;
-                    if (q < 3) {                          // next group in flight during the math
-                        if (q & 1) {
-                            tmem_ld8(col + 8 * (q + 1), ra);
-                            tmem_ld8(col + 32 + 8 * (q + 1), ia);
-                        } else {
-                            tmem_ld8(col + 8 * (q + 1), rb);
-                            tmem_ld8(col + 32 + 8 * (q + 1), ib);
-                        }
-                    }
-                    float2 t[8];
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) t[i] = tw[(8 * q + i) * 64];
-                    uint32_t w[8];
-#pragma unroll
-                    for (int i = 0; i < 8; ++i)
-                        w[i] = pack_h2(re[i] * t[i].x - im[i] * t[i].y, re[i] * t[i].y + im[i] * t[i].x);
-#pragma unroll
-                    for (int i = 0; i < 8; ++i)
-                        *reinterpret_cast<uint32_t*>(bp + (8 * q + i) * 128 + (xbase ^ (uint32_t)(i << 4))) = w[i];
-                    if (q < 3) tmem_ld_wait();
-                    if (q == 2) {                         // the last D1 columns are in registers: slot free
-                        tc_fence_before();
-                        mbar_arrive(bar0 + 8 * (D1_FREE + g));
-                    }
+            for (int j = 0; j < 8; ++j) {                 // k1 = 4j .. 4j+3
+                const float* cur = (j & 1) ? gb : ga;
+                float* nxt = (j & 1) ? ga : gb;
+                if (j < 7) {
+                    tmem_ld4(ca + 4 * (j + 1), &nxt[0]);
+                    tmem_ld4(ca + 32 + 4 * (j + 1), &nxt[4]);
+                    tmem_ld4(cb + 4 * (j + 1), &nxt[8]);
+                    tmem_ld4(cb + 32 + 4 * (j + 1), &nxt[12]);
                 }
-                {
-                    const float2 t32 = tw[32 * 64];
-                    *reinterpret_cast<uint32_t*>(bp + 32 * 128 + xbase) = pack_h2(re32 * t32.x, re32 * t32.y);
+                float2 t[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) t[i] = tw[(4 * j + i) * 64];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const uint32_t off = (uint32_t)((4 * j + i) * 128) + (xbase ^ (uint32_t)(((4 * j + i) & 7) << 4));
+                    *reinterpret_cast<uint32_t*>(bp + off) =
+                        pack_h2(cur[i] * t[i].x - cur[4 + i] * t[i].y, cur[i] * t[i].y + cur[4 + i] * t[i].x);
+                    *reinterpret_cast<uint32_t*>(bp + COLS_PER_SEG * 128 + off) =
+                        pack_h2(cur[8 + i] * t[i].x - cur[12 + i] * t[i].y, cur[8 + i] * t[i].y + cur[12 + i] * t[i].x);
+                }
+                if (j < 7) tmem_ld_wait();
+                if (j == 6) {                             // the last D1 columns are in registers: slots free
+                    tc_fence_before();
+                    mbar_arrive(bar0 + 8 * (D1_FREE + d0));
+                    mbar_arrive(bar0 + 8 * (D1_FREE + d1));
                 }
             }
-            if (!live) break;
+            {
+                const float2 t32 = tw[32 * 64];
+                *reinterpret_cast<uint32_t*>(bp + 32 * 128 + xbase) = pack_h2(re32a * t32.x, re32a * t32.y);
+                *reinterpret_cast<uint32_t*>(bp + (COLS_PER_SEG + 32) * 128 + xbase) = pack_h2(re32b * t32.x, re32b * t32.y);
+            }
             fence_async_smem();
             mbar_arrive(bar0 + 8 * (B2_FULL + s));
             PYFFT_TC_TRACE(9, b)
@@ -381,7 +389,10 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
                 for (int i = 0; i < 32; ++i) v[i] = 0.f;
             }
             // the stage-1 MMAs of the previous batch have finished reading this A1 slot
-            if (b >= 1 && !mbar_wait_abortable(bar0 + 8 * (S1_DONE + g), (uint32_t)(b - 1) & 1u, abort_flag)) break;
+            if (b >= 1) {
+                const int sp = 2 * (b - 1) + g;
+                if (!mbar_wait_abortable(bar0 + 8 * (S1_DONE + sp % 3), (uint32_t)(sp / 3) & 1u, abort_flag)) break;
+            }
             if (hf == 0) { PYFFT_TC_TRACE(2 * g, b) }
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
@@ -409,6 +420,7 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
         setmaxnreg_dec<REGS_MMA>();
         if (tid == 768) {
             constexpr uint32_t id1 = idesc_f16(128, 64), id2 = idesc_f16(128, N2);
+            const uint32_t g_lo = sw128_desc_lo(sm_addr + OFF_GHI), f2_lo = sw128_desc_lo(sm_addr + OFF_F2HI);
 #pragma unroll 1
             for (int b = 0; b <= nb; ++b) {
                 bool live = true;
@@ -416,19 +428,20 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
                     // stage 1 of batch b: one 128 x 64 x 64 product (hi + lo) per segment
 #pragma unroll 1
                     for (int g = 0; g < SEGS; ++g) {
+                        const int si = 2 * b + g, d = si % 3;            // segment index, D1 slot
                         live = live && mbar_wait_abortable(bar0 + 8 * (A1_FULL + g), (uint32_t)b & 1u, abort_flag);
-                        if (b >= 1)
-                            live = live && mbar_wait_abortable(bar0 + 8 * (D1_FREE + g), (uint32_t)(b - 1) & 1u, abort_flag);
+                        if (si >= 3)
+                            live = live && mbar_wait_abortable(bar0 + 8 * (D1_FREE + d), ((uint32_t)(si / 3) & 1u) ^ 1u, abort_flag);
                         if (!live) break;
                         tc_fence_after();
-                        const uint32_t a1 = sm_addr + OFF_A1 + g * A1_BYTES;
+                        const uint32_t a1 = sw128_desc_lo(sm_addr + OFF_A1 + g * A1_BYTES);
 #pragma unroll
                         for (int h = 0; h < 2; ++h)
 #pragma unroll
                             for (int ks = 0; ks < 4; ++ks)
-                                mma_f16(tbase + TM_D1 + g * 64, sw128_desc(a1 + ks * 32),
-                                        sw128_desc(sm_addr + (h ? OFF_GLO : OFF_GHI) + ks * 32), id1, (h | ks) ? 1u : 0u);
-                        mma_commit(bar0 + 8 * (S1_DONE + g));
+                                mma_f16_lo(tbase + TM_D1 + d * 64, a1 + ks * 2,
+                                           g_lo + (h ? (OFF_GLO - OFF_GHI) / 16 : 0) + ks * 2, id1, (h | ks) ? 1u : 0u);
+                        mma_commit(bar0 + 8 * (S1_DONE + d));
                         PYFFT_TC_TRACE(4 + g, b)
                     }
                 }
@@ -441,14 +454,14 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
                         live = live && mbar_wait_abortable(bar0 + 8 * (D2_FREE + s), ((uint32_t)(bb >> 1) & 1u) ^ 1u, abort_flag);
                     if (!live) break;
                     tc_fence_after();
-                    const uint32_t b2 = sm_addr + OFF_B2 + s * B2_BYTES;
+                    const uint32_t b2 = sw128_desc_lo(sm_addr + OFF_B2 + s * B2_BYTES);
 #pragma unroll
                     for (int h = 0; h < 2; ++h)
 #pragma unroll
                         for (int ks = 0; ks < 8; ++ks)
-                            mma_f16(tbase + TM_D2 + s * N2,
-                                    sw128_desc(sm_addr + (h ? OFF_F2LO : OFF_F2HI) + (ks >> 2) * (128 * 128) + (ks & 3) * 32),
-                                    sw128_desc(b2 + (ks >> 2) * (N2 * 128) + (ks & 3) * 32), id2, (h | ks) ? 1u : 0u);
+                            mma_f16_lo(tbase + TM_D2 + s * N2,
+                                       f2_lo + ((h ? OFF_F2LO - OFF_F2HI : 0) + (ks >> 2) * (128 * 128) + (ks & 3) * 32) / 16,
+                                       b2 + ((ks >> 2) * (N2 * 128) + (ks & 3) * 32) / 16, id2, (h | ks) ? 1u : 0u);
                     mma_commit(bar0 + 8 * (S2_DONE + s));
                     PYFFT_TC_TRACE(6, bb)
                 }
