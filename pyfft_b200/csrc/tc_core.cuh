@@ -62,6 +62,18 @@ __device__ __forceinline__ void mma_f16_lo(uint32_t d_tmem, uint32_t a_lo, uint3
         : "memory");
 }
 
+// A operand in tensor memory (lane = row, one 32-bit column = two consecutive K halves, 8 columns per
+// K = 16 step), B from shared memory by the low word of its descriptor
+__device__ __forceinline__ void mma_f16_ts_lo(uint32_t d_tmem, uint32_t a_tmem, uint32_t b_lo, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 db;\n\t"
+        "mov.b64 db, {%2, %5};\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], db, %3, p;\n\t}"
+        ::"r"(d_tmem), "r"(a_tmem), "r"(b_lo), "r"(idesc), "r"(accumulate), "r"(SW128_DESC_HI)
+        : "memory");
+}
+
 // arrive on an mbarrier when all previously issued MMAs of this thread have completed
 __device__ __forceinline__ void mma_commit(uint32_t mbar_smem_addr) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(mbar_smem_addr)
@@ -113,6 +125,15 @@ __device__ __forceinline__ bool mbar_wait_abortable(uint32_t mbar, uint32_t pari
     }
     *abort_flag = 1;
     return false;
+}
+
+// Warp-collective form: lane 0 polls, the result is broadcast (the shuffle also orders the lanes'
+// memory accesses after the acquire).  One poller per warp keeps the barrier unit responsive for
+// the thread that issues the MMAs -- with 32 pollers per warp its own waits took ~300 cycles each.
+__device__ __forceinline__ bool mbar_wait_warp(uint32_t mbar, uint32_t parity, volatile int* abort_flag) {
+    int ok = 1;
+    if ((threadIdx.x & 31) == 0) ok = mbar_wait_abortable(mbar, parity, abort_flag) ? 1 : 0;
+    return __shfl_sync(0xffffffffu, ok, 0) != 0;
 }
 
 // register reallocation between the warpgroups of a warp-specialised kernel
@@ -189,6 +210,13 @@ __device__ __forceinline__ void tmem_ld2(uint32_t taddr, float& a, float& b) {
     a = __uint_as_float(x);
     b = __uint_as_float(y);
 }
+// 8 consecutive 32-bit columns of this thread's TMEM lane <- registers
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, uint32_t a, uint32_t b, uint32_t c, uint32_t d, uint32_t e,
+                                         uint32_t f, uint32_t g, uint32_t h) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+                 ::"r"(taddr), "r"(a), "r"(b), "r"(c), "r"(d), "r"(e), "r"(f), "r"(g), "r"(h) : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 }  // namespace tc

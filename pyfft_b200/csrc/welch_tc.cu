@@ -28,8 +28,8 @@
 //   warpgroup 1  twiddle    D1 (TMEM) -> twiddle -> fp16 -> B2 operand (smem)   (128 threads)
 //   warpgroup 2-5 loaders   global -> detrend -> window -> fp16 -> A1 operand; set g (8 warps)
 //                           takes the segments of parity g and owns A1 slot g   (2 x 256 threads)
-//   warp 24      MMA issue  one thread: stage 1 of batch b+1 is issued BEFORE stage 2 of batch b,
-//                           so the tensor pipe has work while the twiddle group prepares B2
+//   warps 24, 25 MMA issue  one thread each for stage 1 and stage 2 (independent instruction
+//                           streams; the stages meet only through the mbarriers)
 // A1: 2 slots (segment parity); D1: 3 slots (segment index % 3); B2, D2: 2 slots (batch parity).  Registers
 // are moved from the twiddle and MMA warpgroups to the epilogue group with setmaxnreg.
 #include <cuda_fp16.h>
@@ -45,29 +45,35 @@ namespace pyfft {
 
 namespace tcw {
 constexpr int L = 4096, NBIN = L / 2 + 1;
-constexpr int SEGS = 2;                      // segments per stage-2 batch
-constexpr int COLS_PER_SEG = 72;             // D2 columns per segment: X at +0 (33), Y at +36 (33)
-constexpr int YOFF = 36;                     // (multiples of 4 and of 8*k+4: cheap swizzle arithmetic)
+constexpr int SEGS = 2;                      // segments per batch (one B2 slot, one twiddle pass)
+constexpr int YOFF = 36;                     // D2 columns of a segment: X at +0 (33 bins), Y at +36 (33 bins); rows of B2 alike
+constexpr int COLS_PER_SEG = 72;             // D2 columns / B2 rows per segment
 constexpr int N2 = SEGS * COLS_PER_SEG;      // stage-2 MMA N = 144 (a multiple of 16)
 constexpr int NLIN = 8;                      // bins with linear sums (mean correction)
 constexpr int NTHREADS = 896;
 constexpr int HEAD = 3 * L;                  // samples per channel of the materialised reflect zone
-// constant block (global -> shared), byte offsets
-constexpr int OFF_GHI = 0, OFF_GLO = 8192, OFF_F2HI = 16384, OFF_F2LO = 49152, OFF_TW = 81920;
-constexpr int CONST_BYTES = 81920 + 33 * 64 * 8;           // 98816
+// constant block in global memory: [shared part][F2 hi, plain rows][F2 lo, plain rows]
+// shared part (copied to shared memory), byte offsets
+constexpr int OFF_GHI = 0, OFF_GLO = 8192, OFF_TW = 16384;
+constexpr int CONST_SMEM_BYTES = 16384 + 33 * 64 * 8;        // 33280
+// stage-2 matrix F2[(k2, c')][(n2, c)] as 128 rows of 64 packed half2, loaded into tensor memory
+constexpr int OFF_F2T_HI = CONST_SMEM_BYTES, OFF_F2T_LO = OFF_F2T_HI + 128 * 64 * 4;
+constexpr int CONST_BYTES = OFF_F2T_LO + 128 * 64 * 4;       // 98816
 constexpr int WIN_LD = 68;                                   // window stored [n2][n1], padded: conflict-free LDS.128
-constexpr int OFF_WIN = CONST_BYTES;                         // float[64][WIN_LD] = 17408 bytes
-constexpr int OFF_A1 = 116736;                               // 1024-aligned; 2 slots of 128 rows x 64 halves
+constexpr int OFF_WIN = CONST_SMEM_BYTES;                    // float[64][WIN_LD] = 17408 bytes
+constexpr int OFF_A1 = 51200;                                // 1024-aligned; 2 slots of 128 rows x 64 halves
 constexpr int A1_BYTES = 16384;
 constexpr int OFF_B2 = OFF_A1 + 2 * A1_BYTES;                // 2 slots of N2 rows x 128 halves (2 K atoms)
 constexpr int B2_BYTES = N2 * 128 * 2;                       // 36864
-constexpr int SMEM_BYTES = OFF_B2 + 2 * B2_BYTES + 1024;     // + alignment slack = 224256
+constexpr int B2_SEG_BYTES = COLS_PER_SEG * 128;             // row offset of segment 1 inside a K atom
+constexpr int SMEM_BYTES = OFF_B2 + 2 * B2_BYTES + 1024;     // + alignment slack = 158720
 static_assert(OFF_WIN + 64 * WIN_LD * 4 <= OFF_A1, "window table overlaps the operand slots");
-// tensor memory columns
-constexpr int TM_D1 = 288;                                   // 3 slots x 64 columns (segment index % 3)
-constexpr int TM_D2 = 0;                                     // 2 slots x N2 columns (batch parity)
+// tensor memory columns (480 of 512)
+constexpr int TM_F2HI = 0, TM_F2LO = 64;                     // stage-2 A operand: 128 lanes x 64 columns of half2
+constexpr int TM_D1 = 128;                                   // 3 slots x 64 columns (segment index % 3)
+constexpr int TM_D2 = 320;                                   // 1 slot of N2 columns
 // mbarriers
-enum { A1_FULL = 0, S1_DONE = 2, D1_FREE = 5, B2_FULL = 8, S2_DONE = 10, D2_FREE = 12, NBARS = 14 };
+enum { A1_FULL = 0, S1_DONE = 2, D1_FREE = 5, B2_FULL = 8, B2_FREE = 10, S2_DONE = 12, D2_FREE = 14, NBARS = 16 };
 // registers per thread after reallocation (launch: 72; released 512*16 + 128*16 + 128*24 = requested 128*104)
 constexpr int REGS_EPI = 176, REGS_TWD = 56, REGS_LDR = 56, REGS_MMA = 48;
 }  // namespace tcw
@@ -127,7 +133,8 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
 
     const int tid = threadIdx.x, warp = tid >> 5, wg = warp >> 2;
     const int pair = blockIdx.y;
-    const bool trace_on = p.trace != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && (tid & 127) == 0;
+    const bool trace_on = p.trace != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && (tid & 31) == 0 &&
+                          ((tid & 127) == 0 || tid == 800);
     if (p.trace != nullptr && tid == 0) {
         unsigned long long t_;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));
@@ -139,7 +146,7 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
     {
         const uint4* src = reinterpret_cast<const uint4*>(p.consts);
         uint4* dst = reinterpret_cast<uint4*>(sm);
-        for (int i = tid; i < CONST_BYTES / 16; i += NTHREADS) dst[i] = src[i];
+        for (int i = tid; i < CONST_SMEM_BYTES / 16; i += NTHREADS) dst[i] = src[i];
         float* sw = reinterpret_cast<float*>(sm + OFF_WIN);
         for (int n = tid; n < L; n += NTHREADS) sw[(n & 63) * WIN_LD + (n >> 6)] = p.window[n];
     }
@@ -149,6 +156,7 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
         for (int i = 0; i < 2; ++i) {
             mbar_init(bar0 + 8 * (A1_FULL + i), 256);
             mbar_init(bar0 + 8 * (B2_FULL + i), 128);
+            mbar_init(bar0 + 8 * (B2_FREE + i), 1);
             mbar_init(bar0 + 8 * (S2_DONE + i), 1);
             mbar_init(bar0 + 8 * (D2_FREE + i), 128);
         }
@@ -165,6 +173,23 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
     __syncthreads();
     tc_fence_after();
     const uint32_t tbase = tmem_slot;
+    if (tid < 128) {
+        // stage-2 matrix into tensor memory: thread = lane = row (k2, c'), 64 columns of half2 each for hi / lo
+        const uint32_t tl = tbase + ((uint32_t)(warp * 32) << 16);
+#pragma unroll 1
+        for (int part = 0; part < 2; ++part) {
+            const uint4* row = reinterpret_cast<const uint4*>(p.consts + (part ? OFF_F2T_LO : OFF_F2T_HI) + tid * 256);
+#pragma unroll 1
+            for (int c = 0; c < 64; c += 8) {
+                const uint4 u0 = row[c / 4], u1 = row[c / 4 + 1];
+                tmem_st8(tl + (part ? TM_F2LO : TM_F2HI) + c, u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w);
+            }
+        }
+        tmem_st_wait();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
 
     const int64_t c0 = (int64_t)blockIdx.x * p.chunk;
     const int64_t c1 = (c0 + p.chunk < p.seg_count) ? c0 + p.chunk : p.seg_count;
@@ -183,15 +208,17 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
 #pragma unroll
         for (int k = 0; k < NLIN; ++k) { linx[k] = 0.f; liny[k] = 0.f; }
 
+        bool live = true;
 #pragma unroll 1
-        for (int b = 0; b < nb; ++b) {
-            const int s = b & 1;
-            if (!mbar_wait_abortable(bar0 + 8 * (S2_DONE + s), (uint32_t)(b >> 1) & 1u, abort_flag)) break;
-            tc_fence_after();
-            PYFFT_TC_TRACE(10, b)
+        for (int b = 0; b < nb && live; ++b) {
 #pragma unroll
             for (int sg = 0; sg < SEGS; ++sg) {
-                const uint32_t col = tl + s * N2 + sg * COLS_PER_SEG;
+                if (sg == 0) {
+                    if (!mbar_wait_abortable(bar0 + 8 * S2_DONE, (uint32_t)b & 1u, abort_flag)) { live = false; break; }
+                    tc_fence_after();
+                    PYFFT_TC_TRACE(10, b)
+                }
+                const uint32_t col = tl + sg * COLS_PER_SEG;
                 // software pipeline over chunks of 8 bins: the next chunk is in flight during the FMAs
                 float xa[8], ya[8], xb[8], yb[8];
                 tmem_ld8(col, xa);
@@ -221,9 +248,9 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
 #pragma unroll
                 for (int i = 0; i < 8; ++i) PYFFT_TC_ACC(24 + i, xb[i], yb[i]);
                 tmem_ld_wait();
-                if (sg == SEGS - 1) {                                        // D2 slot is in registers now
+                if (sg == SEGS - 1) {                                        // D2 is in registers now
                     tc_fence_before();
-                    mbar_arrive(bar0 + 8 * (D2_FREE + s));
+                    mbar_arrive(bar0 + 8 * D2_FREE);
                     PYFFT_TC_TRACE(11, b)
                 }
                 PYFFT_TC_ACC(32, x32, y32);
@@ -278,7 +305,7 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
         const float2* __restrict__ tw = reinterpret_cast<const float2*>(sm + OFF_TW) + n2;
         // row r = sg*72 + ch*36 + k1 of the operand; 8-row groups are contiguous, so the row offset
         // is r*128 and only the 16-byte chunk index is XOR-ed with r & 7 = (k1 + 4 ch) & 7
-        const uint32_t thread_off = (uint32_t)((n2 >> 5) * (N2 * 128) + (n2 & 3) * 4 + ch * YOFF * 128);
+        const uint32_t thread_off = (uint32_t)((n2 >> 5) * (N2 * 128) + (n2 & 3) * 4 + ch * YOFF * 128);   // inside a segment block
         const uint32_t xbase = (uint32_t)((((n2 & 31) >> 2) ^ (4 * ch)) << 4);   // chunk ^ (k1 & 7) = xbase ^ (i << 4)
 
 #pragma unroll 1
@@ -287,14 +314,14 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
             const int s0 = 2 * b, s1 = 2 * b + 1;                            // segment indices; D1 slot = index % 3
             const int d0 = s0 % 3, d1 = s1 % 3;
             // the stage-2 MMAs of batch b-2 have finished reading this B2 slot
-            if (b >= 2 && !mbar_wait_abortable(bar0 + 8 * (S2_DONE + s), ((uint32_t)(b >> 1) & 1u) ^ 1u, abort_flag)) break;
+            if (b >= 2 && !mbar_wait_abortable(bar0 + 8 * (B2_FREE + s), ((uint32_t)(b >> 1) & 1u) ^ 1u, abort_flag)) break;
             if (!mbar_wait_abortable(bar0 + 8 * (S1_DONE + d0), (uint32_t)(s0 / 3) & 1u, abort_flag)) break;
             PYFFT_TC_TRACE(7, b)
             if (!mbar_wait_abortable(bar0 + 8 * (S1_DONE + d1), (uint32_t)(s1 / 3) & 1u, abort_flag)) break;
             tc_fence_after();
             PYFFT_TC_TRACE(8, b)
             const uint32_t ca = tl + d0 * 64, cb = tl + d1 * 64;
-            unsigned char* bp = sm + OFF_B2 + s * B2_BYTES + thread_off;     // segment 1: + COLS_PER_SEG rows
+            unsigned char* bp = sm + OFF_B2 + s * B2_BYTES + thread_off;     // segment 1: + B2_SEG_BYTES
             // group buffers: [0..3] Re seg 0, [4..7] Im seg 0, [8..11] Re seg 1, [12..15] Im seg 1
             float ga[16], gb[16];
             tmem_ld4(ca, &ga[0]);
@@ -323,7 +350,7 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
                     const uint32_t off = (uint32_t)((4 * j + i) * 128) + (xbase ^ (uint32_t)(((4 * j + i) & 7) << 4));
                     *reinterpret_cast<uint32_t*>(bp + off) =
                         pack_h2(cur[i] * t[i].x - cur[4 + i] * t[i].y, cur[i] * t[i].y + cur[4 + i] * t[i].x);
-                    *reinterpret_cast<uint32_t*>(bp + COLS_PER_SEG * 128 + off) =
+                    *reinterpret_cast<uint32_t*>(bp + B2_SEG_BYTES + off) =
                         pack_h2(cur[8 + i] * t[i].x - cur[12 + i] * t[i].y, cur[8 + i] * t[i].y + cur[12 + i] * t[i].x);
                 }
                 if (j < 7) tmem_ld_wait();
@@ -336,7 +363,7 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
             {
                 const float2 t32 = tw[32 * 64];
                 *reinterpret_cast<uint32_t*>(bp + 32 * 128 + xbase) = pack_h2(re32a * t32.x, re32a * t32.y);
-                *reinterpret_cast<uint32_t*>(bp + (COLS_PER_SEG + 32) * 128 + xbase) = pack_h2(re32b * t32.x, re32b * t32.y);
+                *reinterpret_cast<uint32_t*>(bp + B2_SEG_BYTES + 32 * 128 + xbase) = pack_h2(re32b * t32.x, re32b * t32.y);
             }
             fence_async_smem();
             mbar_arrive(bar0 + 8 * (B2_FULL + s));
@@ -345,126 +372,149 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
     } else if (wg <= 5) {
         // ================= loaders: gather -> detrend -> window -> fp16 -> stage-1 operand ==== //
         // Two sets of 8 warps; set g takes the segments of parity g and owns A1 slot g.  Thread
-        // (half, ch, n2) converts the 32 samples n = 64 (32 half + i) + n2 of its operand row.  The
-        // loads of the set's next segment are issued before it waits for the slot, so their latency
-        // overlaps the stage-1 MMAs of the previous batch and the other set's conversion.
+        // (quarter, n2) converts the 16 samples n = 64 (16 quarter + i) + n2 of BOTH channels, so each
+        // window value is read once for the two.  The loads of the set's next segment are issued
+        // before it waits for the slot: their latency overlaps the stage-1 MMAs of the previous batch
+        // and the other set's conversion.
         setmaxnreg_dec<REGS_LDR>();
         const int lt = tid - 256;
         const int g = lt >> 8;                                               // set = segment parity = A1 slot
-        const int hf = (lt >> 7) & 1, tt = lt & 127;
-        const int ch = tt >> 6, n2 = tt & 63;                                // operand row (ch, n2)
-        const int cidx = ch == 0 ? 0 : 1 + pair;
-        const float* __restrict__ src = ch == 0 ? p.x : p.y + (int64_t)pair * p.y_stride;
-        const float sc = (float)p.prescale[cidx];
-        const float nms = -(float)p.est[2 * cidx] * sc;                      // exact: sc is a power of two
+        const int qt = (lt >> 6) & 3, n2 = lt & 63;
+        const float* __restrict__ ysrc = p.y + (int64_t)pair * p.y_stride;
+        const float scx = (float)p.prescale[0], scy = (float)p.prescale[1 + pair];
+        const float nmx = -(float)p.est[0] * scx, nmy = -(float)p.est[2 * (1 + pair)] * scy;   // exact: powers of two
         const float4* __restrict__ wrow =
-            reinterpret_cast<const float4*>(sm + OFF_WIN + n2 * (WIN_LD * 4) + hf * 128);
-        unsigned char* rowp = sm + OFF_A1 + g * A1_BYTES + (tt >> 3) * 1024 + (tt & 7) * 128;
-        const int sw = tt & 7;
-        const int hb = (int)(p.hop >> 9) - 4 * hf;                           // chunks of this half inside the hop
+            reinterpret_cast<const float4*>(sm + OFF_WIN + n2 * (WIN_LD * 4) + qt * 64);
+        // rows n2 (x) and 64 + n2 (y) of the slot, 16-byte chunks 2 qt and 2 qt + 1
+        unsigned char* rowx = sm + OFF_A1 + g * A1_BYTES + (n2 >> 3) * 1024 + (n2 & 7) * 128;
+        const uint32_t ck0 = (uint32_t)(((2 * qt) ^ (n2 & 7)) << 4), ck1 = (uint32_t)(((2 * qt + 1) ^ (n2 & 7)) << 4);
+        const int hb = (int)(p.hop >> 9) - 2 * qt;                           // chunks of this quarter inside the hop
+        const float in0 = hb > 0 ? 1.f : 0.f, in1 = hb > 1 ? 1.f : 0.f;
         // segments that start in the reflect-padded zone read the materialised head of the record
-        const float* __restrict__ hsrc = p.head + (int64_t)cidx * HEAD + n2 + 2048 * hf;
-        const float* __restrict__ psrc = src + (p.map.i0 - p.map.reflect - p.map.src_base) + n2 + 2048 * hf;
-        // L2 prefetch two segments of this set ahead: 128 lines of 128 bytes per channel, half hf
-        // of the lines, one per thread n2
-        const float* pf = src + (p.map.i0 - p.map.reflect - p.map.src_base) + (hf * 64 + n2) * 32;
+        const int64_t poff = p.map.i0 - p.map.reflect - p.map.src_base + n2 + 1024 * qt;
+        const float* __restrict__ hx = p.head + n2 + 1024 * qt;
+        const float* __restrict__ hy = hx + (int64_t)(1 + pair) * HEAD;
+        // L2 prefetch two segments of this set ahead: 128 lines of 128 bytes per channel; threads
+        // (qt, n2 < 32) take line qt*32 + n2 of x, threads n2 >= 32 the same line of y
+        const float* pf = (n2 < 32 ? p.x : ysrc) + (p.map.i0 - p.map.reflect - p.map.src_base) + (qt * 32 + (n2 & 31)) * 32;
         const int64_t first = p.seg_first + c0 + g;
-        float devsum = 0.f;
+        float sumx = 0.f, sumy = 0.f;
 
 #pragma unroll 1
         for (int b = 0; b < nb; ++b) {
             const bool have = c0 + 2 * b + g < c1;
-            float v[32];
+            float vx[16], vy[16];
             if (have) {
                 const int64_t j0 = (first + 2 * b) * p.hop;
-                const float* __restrict__ q = (j0 < p.map.reflect ? hsrc : psrc) + j0;
+                const bool zone = j0 < p.map.reflect;
+                const float* __restrict__ qx = zone ? hx + j0 : p.x + (j0 + poff);
+                const float* __restrict__ qy = zone ? hy + j0 : ysrc + (j0 + poff);
 #pragma unroll
-                for (int i = 0; i < 32; ++i) v[i] = q[64 * i];
+                for (int i = 0; i < 16; ++i) vx[i] = qx[64 * i];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) vy[i] = qy[64 * i];
                 if (c0 + 2 * b + g + 4 < c1) {
                     const int64_t jn = (first + 2 * b + 4) * p.hop;
                     if (jn >= p.map.reflect) asm volatile("prefetch.global.L2 [%0];" ::"l"(pf + jn));
                 }
             } else {
 #pragma unroll
-                for (int i = 0; i < 32; ++i) v[i] = 0.f;
+                for (int i = 0; i < 16; ++i) { vx[i] = 0.f; vy[i] = 0.f; }
             }
-            // the stage-1 MMAs of the previous batch have finished reading this A1 slot
+            // the stage-1 MMAs of this set's previous segment have finished reading the A1 slot
             if (b >= 1) {
                 const int sp = 2 * (b - 1) + g;
                 if (!mbar_wait_abortable(bar0 + 8 * (S1_DONE + sp % 3), (uint32_t)(sp / 3) & 1u, abort_flag)) break;
             }
-            if (hf == 0) { PYFFT_TC_TRACE(2 * g, b) }
+            if (qt == 0) { PYFFT_TC_TRACE(2 * g, b) }
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                float* u = v + 8 * c;
+            for (int c = 0; c < 2; ++c) {
+                float* ux = vx + 8 * c;
+                float* uy = vy + 8 * c;
                 const float4 w0 = wrow[2 * c], w1 = wrow[2 * c + 1];
 #pragma unroll
-                for (int i = 0; i < 8; ++i) u[i] = fmaf(u[i], sc, nms);                   // (x - mean) * scale
-                if (have && c < hb) devsum += ((u[0] + u[1]) + (u[2] + u[3])) + ((u[4] + u[5]) + (u[6] + u[7]));
-                uint4 o;
-                o.x = pack_h2(u[0] * w0.x, u[1] * w0.y); o.y = pack_h2(u[2] * w0.z, u[3] * w0.w);
-                o.z = pack_h2(u[4] * w1.x, u[5] * w1.y); o.w = pack_h2(u[6] * w1.z, u[7] * w1.w);
-                if (!have) o = make_uint4(0, 0, 0, 0);
-                *reinterpret_cast<uint4*>(rowp + (((4 * hf + c) ^ sw) << 4)) = o;
+                for (int i = 0; i < 8; ++i) { ux[i] = fmaf(ux[i], scx, nmx); uy[i] = fmaf(uy[i], scy, nmy); }   // (x - mean) * scale
+                if (have) {
+                    const float in = c ? in1 : in0;
+                    sumx = fmaf(in, ((ux[0] + ux[1]) + (ux[2] + ux[3])) + ((ux[4] + ux[5]) + (ux[6] + ux[7])), sumx);
+                    sumy = fmaf(in, ((uy[0] + uy[1]) + (uy[2] + uy[3])) + ((uy[4] + uy[5]) + (uy[6] + uy[7])), sumy);
+                }
+                uint4 ox, oy;
+                ox.x = pack_h2(ux[0] * w0.x, ux[1] * w0.y); ox.y = pack_h2(ux[2] * w0.z, ux[3] * w0.w);
+                ox.z = pack_h2(ux[4] * w1.x, ux[5] * w1.y); ox.w = pack_h2(ux[6] * w1.z, ux[7] * w1.w);
+                oy.x = pack_h2(uy[0] * w0.x, uy[1] * w0.y); oy.y = pack_h2(uy[2] * w0.z, uy[3] * w0.w);
+                oy.z = pack_h2(uy[4] * w1.x, uy[5] * w1.y); oy.w = pack_h2(uy[6] * w1.z, uy[7] * w1.w);
+                if (!have) { ox = make_uint4(0, 0, 0, 0); oy = ox; }
+                *reinterpret_cast<uint4*>(rowx + (c ? ck1 : ck0)) = ox;
+                *reinterpret_cast<uint4*>(rowx + 8192 + (c ? ck1 : ck0)) = oy;
             }
             fence_async_smem();
             mbar_arrive(bar0 + 8 * (A1_FULL + g));
-            if (hf == 0) { PYFFT_TC_TRACE(2 * g + 1, b) }
+            if (qt == 0) { PYFFT_TC_TRACE(2 * g + 1, b) }
         }
-        double ds = (double)devsum / (double)sc;
+        double dx = (double)sumx / (double)scx, dy = (double)sumy / (double)scy;
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) ds += __shfl_xor_sync(0xffffffffu, ds, o);
-        if ((tid & 31) == 0 && (ch == 1 || pair == 0)) atomicAdd(&p.dev_sums[cidx], ds);
+        for (int o = 16; o > 0; o >>= 1) {
+            dx += __shfl_xor_sync(0xffffffffu, dx, o);
+            dy += __shfl_xor_sync(0xffffffffu, dy, o);
+        }
+        if ((tid & 31) == 0) {
+            if (pair == 0) atomicAdd(&p.dev_sums[0], dx);
+            atomicAdd(&p.dev_sums[1 + pair], dy);
+        }
     } else {
-        // ================= MMA issue (one thread) ============================================ //
+        // ================= MMA issue: one thread per GEMM stage ================================ //
+        // Two warps so that the two serial instruction streams (waits, descriptors, issue) run on
+        // different schedulers; the stages only meet through the mbarriers.
         setmaxnreg_dec<REGS_MMA>();
         if (tid == 768) {
-            constexpr uint32_t id1 = idesc_f16(128, 64), id2 = idesc_f16(128, N2);
-            const uint32_t g_lo = sw128_desc_lo(sm_addr + OFF_GHI), f2_lo = sw128_desc_lo(sm_addr + OFF_F2HI);
+            // stage 1: one 128 x 64 x 64 product (hi + lo) per segment
+            constexpr uint32_t id1 = idesc_f16(128, 64);
+            const uint32_t g_lo = sw128_desc_lo(sm_addr + OFF_GHI);
+            const int nseg = 2 * nb;
 #pragma unroll 1
-            for (int b = 0; b <= nb; ++b) {
-                bool live = true;
-                if (b < nb) {
-                    // stage 1 of batch b: one 128 x 64 x 64 product (hi + lo) per segment
-#pragma unroll 1
-                    for (int g = 0; g < SEGS; ++g) {
-                        const int si = 2 * b + g, d = si % 3;            // segment index, D1 slot
-                        live = live && mbar_wait_abortable(bar0 + 8 * (A1_FULL + g), (uint32_t)b & 1u, abort_flag);
-                        if (si >= 3)
-                            live = live && mbar_wait_abortable(bar0 + 8 * (D1_FREE + d), ((uint32_t)(si / 3) & 1u) ^ 1u, abort_flag);
-                        if (!live) break;
-                        tc_fence_after();
-                        const uint32_t a1 = sw128_desc_lo(sm_addr + OFF_A1 + g * A1_BYTES);
-#pragma unroll
-                        for (int h = 0; h < 2; ++h)
-#pragma unroll
-                            for (int ks = 0; ks < 4; ++ks)
-                                mma_f16_lo(tbase + TM_D1 + d * 64, a1 + ks * 2,
-                                           g_lo + (h ? (OFF_GLO - OFF_GHI) / 16 : 0) + ks * 2, id1, (h | ks) ? 1u : 0u);
-                        mma_commit(bar0 + 8 * (S1_DONE + d));
-                        PYFFT_TC_TRACE(4 + g, b)
-                    }
-                }
+            for (int si = 0; si < nseg; ++si) {
+                const int g = si & 1, b = si >> 1, d = si % 3;                // A1 slot, batch, D1 slot
+                if (g == 0) { PYFFT_TC_TRACE(12, b) }
+                bool live = mbar_wait_abortable(bar0 + 8 * (A1_FULL + g), (uint32_t)b & 1u, abort_flag);
+                if (si >= 3)
+                    live = live && mbar_wait_abortable(bar0 + 8 * (D1_FREE + d), ((uint32_t)(si / 3) & 1u) ^ 1u, abort_flag);
                 if (!live) break;
-                if (b >= 1) {
-                    // stage 2 of batch b-1: 128 x 144 x 128 (hi + lo)
-                    const int bb = b - 1, s = bb & 1;
-                    live = mbar_wait_abortable(bar0 + 8 * (B2_FULL + s), (uint32_t)(bb >> 1) & 1u, abort_flag);
-                    if (bb >= 2)
-                        live = live && mbar_wait_abortable(bar0 + 8 * (D2_FREE + s), ((uint32_t)(bb >> 1) & 1u) ^ 1u, abort_flag);
-                    if (!live) break;
-                    tc_fence_after();
-                    const uint32_t b2 = sw128_desc_lo(sm_addr + OFF_B2 + s * B2_BYTES);
+                tc_fence_after();
+                if (g == 0) { PYFFT_TC_TRACE(13, b) }
+                const uint32_t a1 = sw128_desc_lo(sm_addr + OFF_A1 + g * A1_BYTES);
 #pragma unroll
-                    for (int h = 0; h < 2; ++h)
+                for (int h = 0; h < 2; ++h)
 #pragma unroll
-                        for (int ks = 0; ks < 8; ++ks)
-                            mma_f16_lo(tbase + TM_D2 + s * N2,
-                                       f2_lo + ((h ? OFF_F2LO - OFF_F2HI : 0) + (ks >> 2) * (128 * 128) + (ks & 3) * 32) / 16,
-                                       b2 + ((ks >> 2) * (N2 * 128) + (ks & 3) * 32) / 16, id2, (h | ks) ? 1u : 0u);
-                    mma_commit(bar0 + 8 * (S2_DONE + s));
-                    PYFFT_TC_TRACE(6, bb)
-                }
+                    for (int ks = 0; ks < 4; ++ks)
+                        mma_f16_lo(tbase + TM_D1 + d * 64, a1 + ks * 2,
+                                   g_lo + (h ? (OFF_GLO - OFF_GHI) / 16 : 0) + ks * 2, id1, (h | ks) ? 1u : 0u);
+                mma_commit(bar0 + 8 * (S1_DONE + d));
+                PYFFT_TC_TRACE(4 + g, b)
+            }
+        } else if (tid == 800) {
+            // stage 2: 128 x 144 x 128 (hi + lo) per batch; the matrix comes from tensor memory, only
+            // the data operand is read from shared memory
+            constexpr uint32_t id2 = idesc_f16(128, N2);
+#pragma unroll 1
+            for (int bb = 0; bb < nb; ++bb) {
+                const int s = bb & 1;
+                PYFFT_TC_TRACE(14, bb)
+                bool live = mbar_wait_abortable(bar0 + 8 * (B2_FULL + s), (uint32_t)(bb >> 1) & 1u, abort_flag);
+                if (bb >= 1) live = live && mbar_wait_abortable(bar0 + 8 * D2_FREE, (uint32_t)(bb - 1) & 1u, abort_flag);
+                if (!live) break;
+                tc_fence_after();
+                PYFFT_TC_TRACE(15, bb)
+                const uint32_t b2 = sw128_desc_lo(sm_addr + OFF_B2 + s * B2_BYTES);
+#pragma unroll
+                for (int h = 0; h < 2; ++h)
+#pragma unroll
+                    for (int ks = 0; ks < 8; ++ks)
+                        mma_f16_ts_lo(tbase + TM_D2, tbase + (h ? TM_F2LO : TM_F2HI) + ks * 8,
+                                      b2 + ((ks >> 2) * (N2 * 128) + (ks & 3) * 32) / 16, id2, (h | ks) ? 1u : 0u);
+                mma_commit(bar0 + 8 * S2_DONE);
+                mma_commit(bar0 + 8 * (B2_FREE + s));
+                PYFFT_TC_TRACE(6, bb)
             }
         }
     }
@@ -591,8 +641,9 @@ static const unsigned char* tc_constants(int* status) {
             const long double m[2][2] = {{cs, sn}, {-sn, cs}};     // [co][ci]
             for (int co = 0; co < 2; ++co)
                 for (int ci = 0; ci < 2; ++ci) {
-                    const uint32_t o = tc::sw128_offset(128, 2 * k2 + co, 2 * n2 + ci);
-                    split(m[co][ci], OFF_F2HI + o, OFF_F2LO + o);
+                    // plain rows: row (k2, co), halves (n2, ci) -> column n2 of the tensor-memory copy
+                    const size_t o = ((size_t)(2 * k2 + co) * 128 + 2 * n2 + ci) * 2;
+                    split(m[co][ci], OFF_F2T_HI + o, OFF_F2T_LO + o);
                 }
         }
     // twiddles W_4096^(n2 k1) = (cos, -sin), [k1][n2]

@@ -84,7 +84,8 @@ __global__ void __launch_bounds__(128) probe_kernel(const __half* A, const __hal
 
 // A operand from tensor memory: thread m writes row m of A, two halves (k = 2c, 2c+1) per 32-bit column
 template <int N, int K>
-__global__ void __launch_bounds__(128) probe_ts_kernel(const __half* A, const __half* B, float* D, int* status) {
+__global__ void __launch_bounds__(128) probe_ts_kernel(const __half* A, const __half* B, float* D, int* status, int reps,
+                                                      long long* cycles) {
     extern __shared__ __align__(1024) unsigned char smem[];
     __shared__ __align__(8) unsigned long long mbar;
     __shared__ uint32_t tmem_base_slot;
@@ -119,20 +120,28 @@ __global__ void __launch_bounds__(128) probe_ts_kernel(const __half* A, const __
     __syncthreads();
     tc_fence_after();
     const uint32_t sb_addr = (uint32_t)__cvta_generic_to_shared(sb);
-    if (tid == 0) {
-        for (int kk = 0; kk < K / 16; ++kk) {
-            const int atom = kk / 4, s = kk % 4;
-            const uint64_t bd = sw128_desc(sb_addr + atom * N * 128 + s * 32);
-            const uint32_t acc = kk > 0 ? 1u : 0u;
-            asm volatile(
-                "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
-                ::"r"(tbase), "r"(tbase + a_col + kk * 8), "l"(bd), "r"(idesc_f16(128, N)), "r"(acc)
-                : "memory");
+    bool ok = true;
+    uint32_t parity = 0;
+    long long t0 = 0;
+    for (int rep = 0; rep < reps; ++rep) {
+        if (tid == 0) {
+            if (rep == 1) t0 = clock64();
+            for (int kk = 0; kk < K / 16; ++kk) {
+                const int atom = kk / 4, s = kk % 4;
+                const uint64_t bd = sw128_desc(sb_addr + atom * N * 128 + s * 32);
+                const uint32_t acc = kk > 0 ? 1u : 0u;
+                asm volatile(
+                    "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                    "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+                    ::"r"(tbase), "r"(tbase + a_col + kk * 8), "l"(bd), "r"(idesc_f16(128, N)), "r"(acc)
+                    : "memory");
+            }
+            mma_commit(mb);
         }
-        mma_commit(mb);
+        ok = mbar_wait(mb, parity) && ok;
+        parity ^= 1;
     }
-    const bool ok = mbar_wait(mb, 0);
+    if (tid == 0) cycles[0] = clock64() - t0;
     tc_fence_after();
     if (ok) {
         for (int c0 = 0; c0 < N; c0 += 32) {
@@ -150,20 +159,20 @@ __global__ void __launch_bounds__(128) probe_ts_kernel(const __half* A, const __
 }
 
 template <int N, int K>
-static int run_ts() {
+static int run_ts(int reps) {
     std::vector<__half> hA(128 * K), hB(N * K);
     std::vector<float> fA(128 * K), fB(N * K);
     srand(4321 + N + K);
     for (size_t i = 0; i < hA.size(); ++i) { fA[i] = (float)((rand() % 17) - 8) / 8.0f; hA[i] = __float2half(fA[i]); }
     for (size_t i = 0; i < hB.size(); ++i) { fB[i] = (float)((rand() % 13) - 6) / 4.0f; hB[i] = __float2half(fB[i]); }
-    __half *dA, *dB; float* dD; int* dS;
-    cudaMalloc(&dA, hA.size() * 2); cudaMalloc(&dB, hB.size() * 2); cudaMalloc(&dD, 128 * N * 4); cudaMalloc(&dS, 8);
+    __half *dA, *dB; float* dD; int* dS; long long* dC;
+    cudaMalloc(&dA, hA.size() * 2); cudaMalloc(&dB, hB.size() * 2); cudaMalloc(&dD, 128 * N * 4); cudaMalloc(&dS, 8); cudaMalloc(&dC, 8);
     cudaMemcpy(dA, hA.data(), hA.size() * 2, cudaMemcpyHostToDevice);
     cudaMemcpy(dB, hB.data(), hB.size() * 2, cudaMemcpyHostToDevice);
     cudaMemset(dS, 0, 8); cudaMemset(dD, 0, 128 * N * 4);
     const int smem = N * K * 2 + 1024;
     cudaFuncSetAttribute(probe_ts_kernel<N, K>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    probe_ts_kernel<N, K><<<1, 128, smem>>>(dA, dB, dD, dS);
+    probe_ts_kernel<N, K><<<1, 128, smem>>>(dA, dB, dD, dS, reps, dC);
     cudaError_t e = cudaDeviceSynchronize();
     if (e != cudaSuccess) { printf("TS N=%d K=%d: CUDA error %s\n", N, K, cudaGetErrorString(e)); return 1; }
     int st; std::vector<float> hD(128 * N);
@@ -177,8 +186,9 @@ static int run_ts() {
             const double d = fabs(s - hD[m * N + n]);
             if (d > maxerr) maxerr = d;
         }
-    printf("TS (A from TMEM) N=%d K=%d: status=%d max|err|=%g D[0][0]=%g D[127][%d]=%g\n", N, K, st, maxerr, hD[0], N - 1,
-           hD[127 * N + N - 1]);
+    long long cyc; cudaMemcpy(&cyc, dC, 8, cudaMemcpyDeviceToHost);
+    printf("TS (A from TMEM) N=%d K=%d: status=%d max|err|=%g D[0][0]=%g D[127][%d]=%g cycles/rep=%.1f (%d MMAs)\n", N, K, st, maxerr,
+           hD[0], N - 1, hD[127 * N + N - 1], reps > 1 ? (double)cyc / (reps - 1) : 0.0, K / 16);
     return (st != 0 || maxerr > 1e-3) ? 1 : 0;
 }
 
@@ -232,8 +242,11 @@ int main() {
     bad += run<256, 128>(200);
     bad += run<144, 128>(200);
     bad += run<128, 64>(200);
-    bad += run_ts<80, 128>();
-    bad += run_ts<144, 64>();
+    bad += run_ts<80, 128>(1);
+    bad += run_ts<80, 128>(200);
+    bad += run_ts<144, 128>(200);
+    bad += run_ts<256, 128>(200);
+    bad += run<80, 128>(200);
     printf(bad ? "PROBE FAILED\n" : "PROBE OK\n");
     return bad;
 }
