@@ -118,10 +118,14 @@ __device__ __forceinline__ void mbar_arrive(uint32_t mbar) {
 
 // Wait inside a multi-role pipeline: gives up when the time-out is hit or when another role has
 // raised the CTA's abort flag, so that a broken hand-shake ends the kernel instead of hanging it.
+// SLEEP_NS > 0: back off between polls (roles with slack must not steal issue slots from the others).
+template <int SLEEP_NS = 0>
 __device__ __forceinline__ bool mbar_wait_abortable(uint32_t mbar, uint32_t parity, volatile int* abort_flag) {
+#pragma unroll 1
     for (uint32_t i = 0; i < (1u << 22); ++i) {
         if (mbar_try_wait_nohint(mbar, parity)) return true;
         if (*abort_flag) return false;
+        if (SLEEP_NS > 0) __nanosleep(SLEEP_NS);
     }
     *abort_flag = 1;
     return false;

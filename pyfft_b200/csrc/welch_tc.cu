@@ -211,7 +211,7 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
         bool live = true;
 #pragma unroll 1
         for (int b = 0; b < nb && live; ++b) {
-#pragma unroll
+#pragma unroll 1                                             // keeps the loop body small for the instruction cache
             for (int sg = 0; sg < SEGS; ++sg) {
                 if (sg == 0) {
                     if (!mbar_wait_abortable(bar0 + 8 * S2_DONE, (uint32_t)b & 1u, abort_flag)) { live = false; break; }
@@ -315,7 +315,8 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
             const int d0 = s0 % 3, d1 = s1 % 3;
             // the stage-2 MMAs of batch b-2 have finished reading this B2 slot
             if (b >= 2 && !mbar_wait_abortable(bar0 + 8 * (B2_FREE + s), ((uint32_t)(b >> 1) & 1u) ^ 1u, abort_flag)) break;
-            if (!mbar_wait_abortable(bar0 + 8 * (S1_DONE + d0), (uint32_t)(s0 / 3) & 1u, abort_flag)) break;
+            // stage 1 of the batch's second segment done implies the first one (same issuing thread,
+            // the tensor pipe completes in order)
             PYFFT_TC_TRACE(7, b)
             if (!mbar_wait_abortable(bar0 + 8 * (S1_DONE + d1), (uint32_t)(s1 / 3) & 1u, abort_flag)) break;
             tc_fence_after();
@@ -424,7 +425,7 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
             // the stage-1 MMAs of this set's previous segment have finished reading the A1 slot
             if (b >= 1) {
                 const int sp = 2 * (b - 1) + g;
-                if (!mbar_wait_abortable(bar0 + 8 * (S1_DONE + sp % 3), (uint32_t)(sp / 3) & 1u, abort_flag)) break;
+                if (!mbar_wait_abortable<200>(bar0 + 8 * (S1_DONE + sp % 3), (uint32_t)(sp / 3) & 1u, abort_flag)) break;
             }
             if (qt == 0) { PYFFT_TC_TRACE(2 * g, b) }
 #pragma unroll
@@ -500,12 +501,13 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
             for (int bb = 0; bb < nb; ++bb) {
                 const int s = bb & 1;
                 PYFFT_TC_TRACE(14, bb)
+                const uint32_t b2 = sw128_desc_lo(sm_addr + OFF_B2 + s * B2_BYTES);
+                // the operand is ready long before the epilogue has drained the single D2 slot
                 bool live = mbar_wait_abortable(bar0 + 8 * (B2_FULL + s), (uint32_t)(bb >> 1) & 1u, abort_flag);
                 if (bb >= 1) live = live && mbar_wait_abortable(bar0 + 8 * D2_FREE, (uint32_t)(bb - 1) & 1u, abort_flag);
                 if (!live) break;
                 tc_fence_after();
                 PYFFT_TC_TRACE(15, bb)
-                const uint32_t b2 = sw128_desc_lo(sm_addr + OFF_B2 + s * B2_BYTES);
 #pragma unroll
                 for (int h = 0; h < 2; ++h)
 #pragma unroll
