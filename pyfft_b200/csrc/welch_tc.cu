@@ -180,9 +180,14 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
         for (int part = 0; part < 2; ++part) {
             const uint4* row = reinterpret_cast<const uint4*>(p.consts + (part ? OFF_F2T_LO : OFF_F2T_HI) + tid * 256);
 #pragma unroll 1
-            for (int c = 0; c < 64; c += 8) {
-                const uint4 u0 = row[c / 4], u1 = row[c / 4 + 1];
-                tmem_st8(tl + (part ? TM_F2LO : TM_F2HI) + c, u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w);
+            for (int c = 0; c < 64; c += 32) {            // 8 independent 16-byte loads in flight
+                uint4 u[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) u[i] = row[c / 4 + i];
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    tmem_st8(tl + (part ? TM_F2LO : TM_F2HI) + c + 8 * i, u[2 * i].x, u[2 * i].y, u[2 * i].z, u[2 * i].w,
+                             u[2 * i + 1].x, u[2 * i + 1].y, u[2 * i + 1].z, u[2 * i + 1].w);
             }
         }
         tmem_st_wait();
