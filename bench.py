@@ -229,9 +229,10 @@ def run_ours(args):
             wp.detrend_stats(x, y, rmap, s_lo, c_lo)
         if s_hi > c_hi:
             wp.detrend_stats(x, y, rmap, c_hi, s_hi)
+        if group is None:
+            return wp.finalize(scale, onesided=True, K=K, correct_nana=nana)     # correction folded in
         wp.mean_correct(nana, group)
-        if group is not None:
-            dist.all_reduce(wp.acc, group=group)
+        dist.all_reduce(wp.acc, group=group)
         return wp.finalize(scale, onesided=True, K=K)
 
     def step_two_pass():
@@ -352,7 +353,7 @@ def run_ours(args):
                         "whole_step_frac": alg_bytes / (ms_step / 1e3) / 1e9 / peak,
                         "two_pass_step_ms": ms_two, "cuda_core_kernel_ms": ms_k1_cuda,
                         "vs_two_pass_cuda_core_max_rel": dev_fused, "vs_two_pass_cuda_core_coherence_abs": dev_coh},
-           "cpu_baseline": cpu, "e2e": e2e, "clocks": clk, "gpu_launches": 11 * args.steps}
+           "cpu_baseline": cpu, "e2e": e2e, "clocks": clk, "gpu_launches": (7 if world == 1 else 8) * args.steps}
     print(json.dumps(out), flush=True)
     if group is not None:
         dist.destroy_process_group()

@@ -88,6 +88,12 @@ int pyfft_detrend_stats(int dtype, const void* ptr, int64_t ch_stride, int32_t n
                         const pyfft_record_map* map, int64_t j_begin, int64_t j_end,
                         double* stats, void* stream);
 
+/* The same sums for x and the nch y channels in ONE launch: stats = double[2*(nch+1)], x first
+ * (the layout pyfft_welch_accumulate_mean and pyfft_welch_mean_correct use). */
+int pyfft_detrend_stats_xy(int dtype, const void* x, const void* y, int64_t y_stride, int32_t nch,
+                           const pyfft_record_map* map, int64_t j_begin, int64_t j_end,
+                           double* stats, void* stream);
+
 /* Turns the (all-reduced) stats into per-channel trend coefficients
  *     coef[2*c+0] = a, coef[2*c+1] = b   with   detrended(j) = x(j) - (a + b*j)
  * for mode MEAN (b = 0) or LINEAR (least-squares line over j = 0..nsig-1). */
@@ -203,6 +209,15 @@ int pyfft_welch_finalize(const double* acc, int32_t nfft, int32_t nch, int64_t K
                          double scale, int32_t onesided,
                          double* Pxx, double* Pyy, double* Pxy,
                          double* Cxy, double* Cxy2, double* phi, void* stream);
+
+/* pyfft_welch_mean_correct + pyfft_welch_finalize in one launch for the unsharded case: the
+ * correction is applied while acc is read (acc is left as accumulated); arguments as in the two
+ * functions, K = number of segments in acc. */
+int pyfft_welch_finalize_mean(const double* acc, const double* lin, int32_t nfft, int32_t nch,
+                              int64_t K, const double* est, const double* stats, int64_t nana,
+                              const double* wlow, double scale, int32_t onesided,
+                              double* Pxx, double* Pyy, double* Pxy, double* Cxy, double* Cxy2,
+                              double* phi, void* stream);
 
 /* ------------------------------------------------------------------------- *
  * K3a  correlation epilogue

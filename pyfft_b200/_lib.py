@@ -43,6 +43,7 @@ _PROTOS = {
     "pyfft_shutdown": (C.c_int, []),
     "pyfft_sm_count": (C.c_int, []),
     "pyfft_detrend_stats": (C.c_int, [C.c_int, _vp, _i64, _i32, _pmap, _i64, _i64, _vp, _vp]),
+    "pyfft_detrend_stats_xy": (C.c_int, [C.c_int, _vp, _vp, _i64, _i32, _pmap, _i64, _i64, _vp, _vp]),
     "pyfft_detrend_coef": (C.c_int, [C.c_int, _vp, _i32, _i64, _vp, _vp]),
     "pyfft_welch_workspace_bytes": (_i64, [C.c_int, _pseg, _i32]),
     "pyfft_welch_accumulate": (C.c_int, [C.c_int, _vp, _vp, _i64, _i32, _pmap, _pseg, _vp, _vp, _vp,
@@ -56,6 +57,8 @@ _PROTOS = {
                                             _vp, _i64, _vp, _vp]),
     "pyfft_welch_finalize": (C.c_int, [_vp, _i32, _i32, _i64, _dbl, _i32, _vp, _vp, _vp, _vp, _vp,
                                        _vp, _vp]),
+    "pyfft_welch_finalize_mean": (C.c_int, [_vp, _vp, _i32, _i32, _i64, _vp, _vp, _i64, _vp, _dbl, _i32,
+                                            _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "pyfft_welch_correlation": (C.c_int, [_vp, _i32, _i32, _i32, _i32, _vp, _vp]),
     "pyfft_stft": (C.c_int, [C.c_int, _i32, _vp, _i64, _i32, _pmap, _pseg, _vp, _vp, _i32, _i32, _i32,
                              _vp, _i32, _vp, _vp, _vp]),

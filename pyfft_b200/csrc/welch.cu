@@ -12,11 +12,12 @@ namespace pyfft {
 // K0: per-channel sum x(j) and sum j*x(j) over analysed indices
 // ------------------------------------------------------------------------- //
 template <typename T>
-__global__ void __launch_bounds__(256) detrend_stats_kernel(const T* __restrict__ ptr, int64_t ch_stride,
-                                                            RecMap map, int64_t j_begin, int64_t j_end,
-                                                            double* __restrict__ stats) {
+__global__ void __launch_bounds__(256) detrend_stats_kernel(const T* __restrict__ first, const T* __restrict__ ptr,
+                                                            int64_t ch_stride, RecMap map, int64_t j_begin,
+                                                            int64_t j_end, double* __restrict__ stats) {
+    // channel c of the stats: `first` (when given) is channel 0 and ptr holds the following ones
     const int c = blockIdx.y;
-    const T* p = ptr + (int64_t)c * ch_stride;
+    const T* p = first ? (c == 0 ? first : ptr + (int64_t)(c - 1) * ch_stride) : ptr + (int64_t)c * ch_stride;
     double s0 = 0.0, s1 = 0.0;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -371,7 +372,17 @@ __global__ void __launch_bounds__(256) welch_reduce_kernel(const T* __restrict__
 // ------------------------------------------------------------------------- //
 // finalize
 // ------------------------------------------------------------------------- //
-__global__ void __launch_bounds__(256) welch_finalize_kernel(const double* __restrict__ acc, int nfft, int nch,
+// mean correction of welch_mean_correct_kernel applied while reading acc (lin == NULL: none)
+struct MeanFix {
+    const double* lin;
+    const double* est;
+    const double* stats;
+    const double* W;
+    int nlin;
+    double K, nana;
+};
+
+__global__ void __launch_bounds__(256) welch_finalize_kernel(const double* __restrict__ acc, MeanFix fix, int nfft, int nch,
                                                              double scale_over_k, int onesided, int F,
                                                              double* __restrict__ Pxx, double* __restrict__ Pyy,
                                                              double* __restrict__ Pxy, double* __restrict__ Cxy,
@@ -394,8 +405,21 @@ __global__ void __launch_bounds__(256) welch_finalize_kernel(const double* __res
     }
     const double* a = acc + (size_t)c * 4 * nbin;
     const double s = scale_over_k * wgt;
-    const double pxx = a[0 * nbin + f] * s, pyy = a[1 * nbin + f] * s;
-    const double pr = a[2 * nbin + f] * s, pi = (conj ? -a[3 * nbin + f] : a[3 * nbin + f]) * s;
+    double a0 = a[0 * nbin + f], a1 = a[1 * nbin + f], a2 = a[2 * nbin + f], a3 = a[3 * nbin + f];
+    if (fix.lin && f < fix.nlin) {
+        const int nlin = fix.nlin;
+        const double dx = fix.stats[0] / fix.nana - fix.est[0];
+        const double dy = fix.stats[2 * (1 + c)] / fix.nana - fix.est[2 * (1 + c)];
+        const double wr = fix.W[2 * f], wi = fix.W[2 * f + 1], w2 = wr * wr + wi * wi;
+        const double* l = fix.lin + (size_t)c * 4 * nlin;
+        const double sur = l[f], sui = l[nlin + f], svr = l[2 * nlin + f], svi = l[3 * nlin + f];
+        a0 += -2.0 * dx * (wr * sur + wi * sui) + fix.K * dx * dx * w2;
+        a1 += -2.0 * dy * (wr * svr + wi * svi) + fix.K * dy * dy * w2;
+        a2 += -dx * (wr * svr + wi * svi) - dy * (wr * sur + wi * sui) + fix.K * dx * dy * w2;
+        a3 += -dx * (wr * svi - wi * svr) - dy * (wi * sur - wr * sui);
+    }
+    const double pxx = a0 * s, pyy = a1 * s;
+    const double pr = a2 * s, pi = (conj ? -a3 : a3) * s;
     if (Pxx && c == 0) { Pxx[2 * o] = pxx; Pxx[2 * o + 1] = 0.0; }
     if (Pyy) { Pyy[2 * idx] = pyy; Pyy[2 * idx + 1] = 0.0; }
     if (Pxy) { Pxy[2 * idx] = pr; Pxy[2 * idx + 1] = pi; }
@@ -568,13 +592,30 @@ using namespace pyfft;
 
 extern "C" {
 
+static int detrend_stats_launch(int dtype, const void* first, const void* ptr, int64_t ch_stride, int32_t nch,
+                                const pyfft_record_map* map, int64_t j_begin, int64_t j_end, double* stats,
+                                void* stream);
+
 int pyfft_detrend_stats(int dtype, const void* ptr, int64_t ch_stride, int32_t nch,
                         const pyfft_record_map* map, int64_t j_begin, int64_t j_end,
                         double* stats, void* stream) {
+    if (!ptr || !stats || nch <= 0) return fail(PYFFT_EINVAL, "detrend_stats: NULL pointer or nch <= 0");
+    return detrend_stats_launch(dtype, nullptr, ptr, ch_stride, nch, map, j_begin, j_end, stats, stream);
+}
+
+int pyfft_detrend_stats_xy(int dtype, const void* x, const void* y, int64_t y_stride, int32_t nch,
+                           const pyfft_record_map* map, int64_t j_begin, int64_t j_end,
+                           double* stats, void* stream) {
+    if (!x || !y || !stats || nch <= 0) return fail(PYFFT_EINVAL, "detrend_stats_xy: NULL pointer or nch <= 0");
+    return detrend_stats_launch(dtype, x, y, y_stride, nch + 1, map, j_begin, j_end, stats, stream);
+}
+
+static int detrend_stats_launch(int dtype, const void* first, const void* ptr, int64_t ch_stride, int32_t nch,
+                                const pyfft_record_map* map, int64_t j_begin, int64_t j_end, double* stats,
+                                void* stream) {
     RecMap m;
     int rc = check_map(map, &m);
     if (rc) return rc;
-    if (!ptr || !stats || nch <= 0) return fail(PYFFT_EINVAL, "detrend_stats: NULL pointer or nch <= 0");
     if ((rc = check_range(m, j_begin, j_end))) return rc;
     if (j_begin == j_end) return PYFFT_OK;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -586,9 +627,11 @@ int pyfft_detrend_stats(int dtype, const void* ptr, int64_t ch_stride, int32_t n
     if (blocks < 1) blocks = 1;
     dim3 grid((unsigned)blocks, (unsigned)nch);
     if (dtype == PYFFT_F32)
-        detrend_stats_kernel<float><<<grid, 256, 0, st>>>(static_cast<const float*>(ptr), ch_stride, m, j_begin, j_end, stats);
+        detrend_stats_kernel<float><<<grid, 256, 0, st>>>(static_cast<const float*>(first), static_cast<const float*>(ptr),
+                                                          ch_stride, m, j_begin, j_end, stats);
     else if (dtype == PYFFT_F64)
-        detrend_stats_kernel<double><<<grid, 256, 0, st>>>(static_cast<const double*>(ptr), ch_stride, m, j_begin, j_end, stats);
+        detrend_stats_kernel<double><<<grid, 256, 0, st>>>(static_cast<const double*>(first), static_cast<const double*>(ptr),
+                                                           ch_stride, m, j_begin, j_end, stats);
     else
         return fail(PYFFT_EINVAL, "unknown dtype %d", dtype);
     PYFFT_LAUNCH_OK("detrend_stats_kernel");
@@ -679,8 +722,24 @@ int pyfft_welch_finalize(const double* acc, int32_t nfft, int32_t nch, int64_t K
         return fail(PYFFT_EINVAL, "welch_finalize: bad arguments (even nfft, nch > 0, K > 0 required)");
     const int F = onesided ? nfft / 2 : nfft;
     const int total = F * nch;
+    MeanFix fix{};
     welch_finalize_kernel<<<(total + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        acc, nfft, nch, scale / (double)K, onesided, F, Pxx, Pyy, Pxy, Cxy, Cxy2, phi);
+        acc, fix, nfft, nch, scale / (double)K, onesided, F, Pxx, Pyy, Pxy, Cxy, Cxy2, phi);
+    PYFFT_LAUNCH_OK("welch_finalize_kernel");
+    return PYFFT_OK;
+}
+
+int pyfft_welch_finalize_mean(const double* acc, const double* lin, int32_t nfft, int32_t nch, int64_t K,
+                              const double* est, const double* stats, int64_t nana, const double* wlow,
+                              double scale, int32_t onesided, double* Pxx, double* Pyy, double* Pxy,
+                              double* Cxy, double* Cxy2, double* phi, void* stream) {
+    if (!acc || !lin || !est || !stats || !wlow || nfft < 16 || (nfft & 1) || nch <= 0 || K <= 0 || nana <= 0)
+        return fail(PYFFT_EINVAL, "welch_finalize_mean: bad arguments");
+    const int F = onesided ? nfft / 2 : nfft;
+    const int total = F * nch;
+    MeanFix fix{lin, est, stats, wlow, nfft / 16, (double)K, (double)nana};
+    welch_finalize_kernel<<<(total + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        acc, fix, nfft, nch, scale / (double)K, onesided, F, Pxx, Pyy, Pxy, Cxy, Cxy2, phi);
     PYFFT_LAUNCH_OK("welch_finalize_kernel");
     return PYFFT_OK;
 }

@@ -544,10 +544,12 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
 // provisional statistics: mean (rounded to float) and a power-of-two scale that brings the
 // rms of (x - mean) to ~1/8, from the first samples of the span
 // ------------------------------------------------------------------------- //
-// pass 1: est[2c] += sum (x - x0), est[2c+1] += sum (x - x0)^2 with x0 = the first sample of the span
-__global__ void __launch_bounds__(256) tc_moments_kernel(const float* __restrict__ x, const float* __restrict__ y,
+// est[2c] += sum (x - x0), est[2c+1] += sum (x - x0)^2 with x0 = the first sample of the span; the
+// last block of a channel to finish (ticket in prescale[c], zeroed by the host) turns the sums into
+// est[2c] = mean (rounded to fp32), est[2c+1] = 0, prescale[c] = 2^k with rms * 2^k in [1/8, 1/4)
+__global__ void __launch_bounds__(256) tc_prepare_kernel(const float* __restrict__ x, const float* __restrict__ y,
                                                          int64_t y_stride, RecMap map, int64_t j_begin, int64_t j_end,
-                                                         double* __restrict__ est) {
+                                                         double* __restrict__ est, double* __restrict__ prescale) {
     const int c = blockIdx.y;                       // 0 = x, 1.. = y channels
     const float* p = c == 0 ? x : y + (int64_t)(c - 1) * y_stride;
     const double x0 = (double)p[src_index(map, j_begin)];
@@ -563,23 +565,21 @@ __global__ void __launch_bounds__(256) tc_moments_kernel(const float* __restrict
         s0 += __shfl_xor_sync(0xffffffffu, s0, o);
         s1 += __shfl_xor_sync(0xffffffffu, s1, o);
     }
-    if ((threadIdx.x & 31) == 0) {
-        atomicAdd(&est[2 * c], s0);
-        atomicAdd(&est[2 * c + 1], s1);
-    }
-}
-
-// pass 2: est[2c] = mean (rounded to fp32), est[2c+1] = 0, prescale[c] = 2^k with rms * 2^k in [1/8, 1/4)
-__global__ void tc_prepare_finish_kernel(const float* __restrict__ x, const float* __restrict__ y, int64_t y_stride,
-                                         RecMap map, int64_t j_begin, int64_t j_end, int nch1,
-                                         double* __restrict__ est, double* __restrict__ prescale) {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= nch1) return;
-    const float* p = c == 0 ? x : y + (int64_t)(c - 1) * y_stride;
-    const double x0 = (double)p[src_index(map, j_begin)];
+    __shared__ double sh[2][8];
+    if ((threadIdx.x & 31) == 0) { sh[0][threadIdx.x >> 5] = s0; sh[1][threadIdx.x >> 5] = s1; }
+    __syncthreads();
+    if (threadIdx.x != 0) return;
+    s0 = s1 = 0.0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) { s0 += sh[0][w]; s1 += sh[1][w]; }
+    atomicAdd(&est[2 * c], s0);
+    atomicAdd(&est[2 * c + 1], s1);
+    __threadfence();
+    if (atomicAdd(&prescale[c], 1.0) != (double)(gridDim.x - 1)) return;     // not the last block of the channel
+    __threadfence();
     const double n = (double)(j_end - j_begin);
-    const double md = est[2 * c] / n;
-    double var = est[2 * c + 1] / n - md * md;
+    const double md = atomicAdd(&est[2 * c], 0.0) / n;                         // read through L2
+    double var = atomicAdd(&est[2 * c + 1], 0.0) / n - md * md;
     if (!(var > 0.0)) var = 0.0;
     const double rms = sqrt(var);
     int e = 0;
@@ -591,6 +591,51 @@ __global__ void tc_prepare_finish_kernel(const float* __restrict__ x, const floa
     est[2 * c + 1] = 0.0;
     prescale[c] = ldexp(1.0, sh2);
 }
+
+// after the main kernel, in one launch: acc += sum of the per-CTA partial spectra, lin += sum of the
+// partial linear sums (bins < NLIN), stats[2c] += raw sum of the covered samples
+__global__ void __launch_bounds__(256) tc_finish_kernel(const float* __restrict__ partial,
+                                                        const float* __restrict__ lin_partial, int nparts,
+                                                        const double* __restrict__ dev_sums,
+                                                        const double* __restrict__ est, double count, int nch1,
+                                                        double* __restrict__ acc, double* __restrict__ lin,
+                                                        double* __restrict__ stats) {
+    using namespace tcw;
+    constexpr int PER_PAIR = 4 * NBIN, MAIN_BLOCKS = (PER_PAIR + 31) / 32;
+    const int lane = threadIdx.x & 31, g = threadIdx.x >> 5;
+    const int pair = blockIdx.y;
+    const bool is_lin = blockIdx.x == MAIN_BLOCKS;
+    if (is_lin && pair == 0 && threadIdx.x >= 32)
+        for (int c = threadIdx.x - 32; c < nch1; c += 224) stats[2 * c] += dev_sums[c] + count * est[2 * c];
+    // 32 consecutive outputs per block, the parts split over the 8 warps, combined through shared memory
+    const int per = is_lin ? 4 * (L / 16) : PER_PAIR;
+    int i = blockIdx.x * 32 + lane;
+    if (is_lin) i = (lane >> 3) * (L / 16) + (lane & 7);         // row (re/im of U, V) and bin < NLIN = 8
+    const float* src = is_lin ? lin_partial : partial;
+    __shared__ double sh[8][33];
+    double s = 0.0;
+    if (i < per) {
+        const float* p = src + (size_t)pair * nparts * per + i;
+        int k = g;
+        for (; k + 56 < nparts; k += 64) {
+            float r[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) r[u] = p[(size_t)(k + 8 * u) * per];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) s += (double)r[u];
+        }
+        for (; k < nparts; k += 8) s += (double)p[(size_t)k * per];
+    }
+    sh[g][lane] = s;
+    __syncthreads();
+    if (g == 0 && i < per) {
+        double t = 0.0;
+#pragma unroll
+        for (int u = 0; u < 8; ++u) t += sh[u][lane];
+        (is_lin ? lin : acc)[(size_t)pair * per + i] += t;
+    }
+}
+static_assert(tcw::NLIN == 8, "tc_finish_kernel maps 32 lanes onto 4 rows x 8 bins");
 
 // materialises the analysed samples j < n of every channel (the reflect-padded zone and the
 // segments that reach into it), so that the loaders never evaluate the record map
@@ -713,13 +758,11 @@ int pyfft_welch_tc_prepare(const void* x, const void* y, int64_t y_stride, int32
     if (j_end <= j_begin) return fail(PYFFT_EINVAL, "welch_tc_prepare: empty sample span");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     PYFFT_CUDA_OK(cudaMemsetAsync(est, 0, sizeof(double) * 2 * (size_t)(nch + 1), st));
+    PYFFT_CUDA_OK(cudaMemsetAsync(prescale, 0, sizeof(double) * (size_t)(nch + 1), st));
     int gx = (int)((j_end - j_begin + 2047) / 2048);
     if (gx > 64) gx = 64;
-    tc_moments_kernel<<<dim3(gx, nch + 1), 256, 0, st>>>(static_cast<const float*>(x), static_cast<const float*>(y),
-                                                        y_stride, m, j_begin, j_end, est);
-    tc_prepare_finish_kernel<<<(nch + 1 + 63) / 64, 64, 0, st>>>(static_cast<const float*>(x),
-                                                               static_cast<const float*>(y), y_stride, m, j_begin,
-                                                               j_end, nch + 1, est, prescale);
+    tc_prepare_kernel<<<dim3(gx, nch + 1), 256, 0, st>>>(static_cast<const float*>(x), static_cast<const float*>(y),
+                                                        y_stride, m, j_begin, j_end, est, prescale);
     PYFFT_LAUNCH_OK("tc_prepare_kernel");
     return PYFFT_OK;
 }
@@ -795,10 +838,11 @@ int pyfft_welch_accumulate_tc(const void* x, const void* y, int64_t y_stride, in
     PYFFT_CUDA_OK(cudaFuncSetAttribute(welch_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
     welch_tc_kernel<<<dim3(gx, nch), NTHREADS, SMEM_BYTES, st>>>(p);
     PYFFT_LAUNCH_OK("welch_tc_kernel");
-    if ((rc = welch_reduce_launch_f32(p.lin_partial, nparts, 4 * (L / 16), nch, lin, st))) return rc;
-    if ((rc = welch_raw_sums_launch(p.dev_sums, est, nch + 1, (double)seg->seg_count * (double)seg->hop, stats, st)))
-        return rc;
-    return welch_reduce_launch_f32(p.partial, nparts, 4 * NBIN, nch, acc, st);
+    tc_finish_kernel<<<dim3((4 * NBIN + 31) / 32 + 1, nch), 256, 0, st>>>(
+        p.partial, p.lin_partial, nparts, p.dev_sums, est, (double)seg->seg_count * (double)seg->hop, nch + 1, acc, lin,
+        stats);
+    PYFFT_LAUNCH_OK("tc_finish_kernel");
+    return PYFFT_OK;
 }
 
 }  // extern "C"

@@ -125,11 +125,8 @@ class WelchPlan(object):
     # -- detrend ------------------------------------------------------------ #
     def detrend_stats(self, x, y, rmap, j_begin, j_end):
         """Adds sum x(j), sum j x(j) for j in [j_begin, j_end) (x first, then the y channels)."""
-        check(lib.pyfft_detrend_stats(self.code, _ptr(x), 0, 1, C.byref(rmap), j_begin, j_end,
-                                      _ptr(self.stats), _stream()))
-        check(lib.pyfft_detrend_stats(self.code, _ptr(y), y.stride(0), self.nch, C.byref(rmap),
-                                      j_begin, j_end, C.c_void_p(self.stats.data_ptr() + 16),
-                                      _stream()))
+        check(lib.pyfft_detrend_stats_xy(self.code, _ptr(x), _ptr(y), y.stride(0), self.nch, C.byref(rmap),
+                                         j_begin, j_end, _ptr(self.stats), _stream()))
 
     def solve_detrend(self, mode, nsig, group=None):
         if mode == _lib.DETREND_NONE:
@@ -227,8 +224,10 @@ class WelchPlan(object):
         self.K = int(k.item())
 
     # -- finalize ----------------------------------------------------------- #
-    def finalize(self, scale, onesided=True, K=None):
-        """-> dict of device tensors Pxx (F,), Pyy/Pxy/Cxy/Cxy2 (F, nch) complex128, phi (F, nch)."""
+    def finalize(self, scale, onesided=True, K=None, correct_nana=None):
+        """-> dict of device tensors Pxx (F,), Pyy/Pxy/Cxy/Cxy2 (F, nch) complex128, phi (F, nch).
+        correct_nana: unsharded fused-mean route -- apply the mean correction (instead of a separate
+        mean_correct call) while acc is read; stats must cover the whole analysed record."""
         K = self.K if K is None else int(K)
         F = self.nfft // 2 if onesided else self.nfft
         dev = self.device
@@ -238,6 +237,15 @@ class WelchPlan(object):
                    Cxy=torch.empty((F, self.nch), dtype=torch.complex128, device=dev),
                    Cxy2=torch.empty((F, self.nch), dtype=torch.complex128, device=dev),
                    phi_xy=torch.empty((F, self.nch), dtype=torch.float64, device=dev))
+        if correct_nana is not None:
+            check(lib.pyfft_welch_finalize_mean(_ptr(self.acc), _ptr(self.lin), self.nfft, self.nch, K,
+                                                _ptr(self.est), _ptr(self.stats), int(correct_nana),
+                                                _ptr(self.wlow), float(scale), 1 if onesided else 0,
+                                                _ptr(out["Pxx"]), _ptr(out["Pyy"]), _ptr(out["Pxy"]),
+                                                _ptr(out["Cxy"]), _ptr(out["Cxy2"]), _ptr(out["phi_xy"]),
+                                                _stream()))
+            self.coef = None
+            return out
         check(lib.pyfft_welch_finalize(_ptr(self.acc), self.nfft, self.nch, K, float(scale),
                                        1 if onesided else 0, _ptr(out["Pxx"]), _ptr(out["Pyy"]),
                                        _ptr(out["Pxy"]), _ptr(out["Cxy"]), _ptr(out["Cxy2"]),

@@ -310,6 +310,7 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
             rank, world = torch.distributed.get_rank(group), torch.distributed.get_world_size(group)
         lp = _dist.local_plan(K, hop, nwins, plan.nana, plan.i0, refl, rank, world)
         nseg = lp["k1"] - lp["k0"]
+        fix_nana = None
         if mode == _lib.DETREND_MEAN and wp.can_fuse_mean and nseg > 0 and hop <= nwins \
                 and not two_pass:
             # global mean (:356-357) fused into the single pass over the data: provisional mean
@@ -331,7 +332,10 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
                 wp.detrend_stats(x, y, rmap, s_lo, c_lo)
             if s_hi > c_hi:
                 wp.detrend_stats(x, y, rmap, c_hi, s_hi)
-            wp.mean_correct(plan.nana, group)
+            if group is not None:
+                wp.mean_correct(plan.nana, group)       # per rank, before the sums are all-reduced
+            else:
+                fix_nana = plan.nana                    # single device: folded into finalize
         else:
             if mode != _lib.DETREND_NONE:
                 # global detrend over the whole analysed record (:356-357): each rank sums its slice
@@ -341,7 +345,7 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
         if group is not None:
             wp.all_reduce(group)
         scale = 1.0 / (fftinfo.S1 ** 2) / fftinfo.ENBW             # :432-440
-        res = wp.finalize(scale, onesided=bool(onesided), K=K)
+        res = wp.finalize(scale, onesided=bool(onesided), K=K, correct_nana=fix_nana)
         corr = {}
         for nm, key, halve in (("Rxx", "Pxx", True), ("Ryy", "Pyy", True), ("Rxy", "Pxy", True),
                                ("iCxy", "Cxy", False)):
