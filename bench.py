@@ -215,10 +215,7 @@ def run_ours(args):
         # ONE pass over HBM: provisional mean (+ scale) from 64 Ki samples, fused Welch
         # accumulation (tensor-core DFT when available), exact mean correction by linearity
         # after the (all-reduced) raw sums are known
-        wp.acc.zero_()
-        wp.lin.zero_()
-        wp.stats.zero_()
-        wp.K = wp.K_local = 0
+        wp.reset()
         if use_tc:
             wp.prepare_tc(x, y, rmap, c_lo, c_hi)
             wp.accumulate_tc(x, y, rmap, k0, k1 - k0)
@@ -229,16 +226,13 @@ def run_ours(args):
             wp.detrend_stats(x, y, rmap, s_lo, c_lo)
         if s_hi > c_hi:
             wp.detrend_stats(x, y, rmap, c_hi, s_hi)
-        if group is None:
-            return wp.finalize(scale, onesided=True, K=K, correct_nana=nana)     # correction folded in
-        wp.mean_correct(nana, group)
-        dist.all_reduce(wp.acc, group=group)
-        return wp.finalize(scale, onesided=True, K=K)
+        if group is not None:
+            wp.rereference()                       # shards to a common reference, then ONE collective
+            wp.all_reduce_state(group)
+        return wp.finalize(scale, onesided=True, K=K, correct_nana=nana)         # correction folded in
 
     def step_two_pass():
-        wp.acc.zero_()
-        wp.stats.zero_()
-        wp.K = 0
+        wp.reset()
         wp.detrend_stats(x, y, rmap, s_lo, s_hi)
         wp.solve_detrend(_lib.DETREND_MEAN, nana, group)
         wp.accumulate(x, y, rmap, k0, k1 - k0)

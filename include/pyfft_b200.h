@@ -157,6 +157,14 @@ int pyfft_welch_mean_correct(double* acc, const double* lin, int32_t nfft, int32
                              int64_t K, const double* est, const double* stats, int64_t nana,
                              const double* wlow, void* stream);
 
+/* Sharded records with ONE collective: every rank moves its sums from its
+ * own provisional means to the common reference 0 (acc and lin become the sums of the raw
+ * windowed spectra for bins f < nfft/16; K = segments in THIS acc), the ranks all-reduce
+ * acc | lin | stats together, and pyfft_welch_finalize_mean is called with est = 0 and the
+ * global K.  Replaces the pair (all-reduce stats, pyfft_welch_mean_correct per rank). */
+int pyfft_welch_rereference(double* acc, double* lin, int32_t nfft, int32_t nch, int64_t K,
+                            const double* est, const double* wlow, void* stream);
+
 /* ------------------------------------------------------------------------- *
  * K1-TC, the same accumulation on the tcgen05 tensor cores (float32 input,
  * nfft = 4096, hop a multiple of 512)

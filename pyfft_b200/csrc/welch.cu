@@ -336,6 +336,32 @@ __global__ void __launch_bounds__(256) welch_mean_correct_kernel(double* __restr
     a[3 * nbin + f] += -dx * (wr * svi - wi * svr) - dy * (wi * sur - wr * sui);
 }
 
+// Moves the sums of ONE shard from its provisional means est to the common reference 0 (the
+// spectra of the raw windowed samples, bins f < nlin), lin included, so that shards analysed
+// about different provisional means can be added (one all-reduce of acc | lin | stats) and
+// corrected once with est = 0:  U0 = U~ + ex W,  V0 = V~ + ey W.
+__global__ void __launch_bounds__(256) welch_rereference_kernel(double* __restrict__ acc, double* __restrict__ lin,
+                                                                int nlin, int nbin, int nch, double K,
+                                                                const double* __restrict__ est,
+                                                                const double* __restrict__ W) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= nch * nlin) return;
+    const int c = idx / nlin, f = idx - c * nlin;
+    const double dx = -est[0], dy = -est[2 * (1 + c)];
+    const double wr = W[2 * f], wi = W[2 * f + 1], w2 = wr * wr + wi * wi;
+    double* l = lin + (size_t)c * 4 * nlin;
+    const double sur = l[f], sui = l[nlin + f], svr = l[2 * nlin + f], svi = l[3 * nlin + f];
+    double* a = acc + (size_t)c * 4 * nbin;
+    a[f] += -2.0 * dx * (wr * sur + wi * sui) + K * dx * dx * w2;
+    a[nbin + f] += -2.0 * dy * (wr * svr + wi * svi) + K * dy * dy * w2;
+    a[2 * nbin + f] += -dx * (wr * svr + wi * svi) - dy * (wr * sur + wi * sui) + K * dx * dy * w2;
+    a[3 * nbin + f] += -dx * (wr * svi - wi * svr) - dy * (wi * sur - wr * sui);
+    l[f] = sur - K * dx * wr;
+    l[nlin + f] = sui - K * dx * wi;
+    l[2 * nlin + f] = svr - K * dy * wr;
+    l[3 * nlin + f] = svi - K * dy * wi;
+}
+
 // acc[pair][q][f] += sum_part partial[pair][part][q][f]
 // 32 consecutive outputs per block, the parts split over the 8 warps (8 loads in flight each),
 // combined through shared memory: the part loop is short enough not to be latency-bound
@@ -712,6 +738,17 @@ int pyfft_welch_mean_correct(double* acc, const double* lin, int32_t nfft, int32
     welch_mean_correct_kernel<<<(nch * nlin + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
         acc, lin, nlin, nbin, nch, (double)K, est, stats, (double)nana, wlow);
     PYFFT_LAUNCH_OK("welch_mean_correct_kernel");
+    return PYFFT_OK;
+}
+
+int pyfft_welch_rereference(double* acc, double* lin, int32_t nfft, int32_t nch, int64_t K,
+                            const double* est, const double* wlow, void* stream) {
+    if (!acc || !lin || !est || !wlow || nfft < 16 || nch <= 0 || K < 0)
+        return fail(PYFFT_EINVAL, "welch_rereference: bad arguments");
+    const int nlin = nfft / 16, nbin = nfft / 2 + 1;
+    welch_rereference_kernel<<<(nch * nlin + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        acc, lin, nlin, nbin, nch, (double)K, est, wlow);
+    PYFFT_LAUNCH_OK("welch_rereference_kernel");
     return PYFFT_OK;
 }
 

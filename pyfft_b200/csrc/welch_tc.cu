@@ -830,8 +830,9 @@ int pyfft_welch_accumulate_tc(const void* x, const void* y, int64_t y_stride, in
     p.dev_sums = reinterpret_cast<double*>(static_cast<char*>(workspace) + main_bytes + lin_bytes);
     p.status = status_flag;
     p.trace = g_tc_trace;
-    // CTAs that get no segment still write zeros; the linear sums are sparse -> clear them
-    PYFFT_CUDA_OK(cudaMemsetAsync(p.partial, 0, (size_t)(main_bytes + lin_bytes) + sizeof(double) * (size_t)(nch + 1), st));
+    // every CTA (also one that gets no segment) writes all of its partial sums and the NLIN bins of
+    // the linear sums that tc_finish_kernel reads: only the raw-sum accumulators need clearing
+    PYFFT_CUDA_OK(cudaMemsetAsync(p.dev_sums, 0, sizeof(double) * (size_t)(nch + 1), st));
     if (head_len > 0)
         tc_head_kernel<<<dim3((unsigned)((head_len + 255) / 256), nch + 1), 256, 0, st>>>(
             p.x, p.y, y_stride, 0, m, head_len, head);

@@ -97,19 +97,22 @@ class WelchPlan(object):
         if win.shape != (self.nfft,):
             raise ValueError("window must have nfft = %d points" % self.nfft)
         self.window = torch.from_numpy(win).to(self.device, _TORCH_REAL[precision])
-        self.acc = torch.zeros((self.nch, 4, self.nbin), dtype=torch.float64, device=self.device)
-        self.stats = torch.zeros(2 * (self.nch + 1), dtype=torch.float64, device=self.device)
+        # acc | lin | stats share one buffer: one fill resets them, one all-reduce adds shards
+        self.nlin = self.nfft // 16
+        n_acc, n_lin, n_st = self.nch * 4 * self.nbin, self.nch * 4 * self.nlin, 2 * (self.nch + 1)
+        self.state = torch.zeros(n_acc + n_lin + n_st, dtype=torch.float64, device=self.device)
+        self.acc = self.state[:n_acc].view(self.nch, 4, self.nbin)
+        self.lin = self.state[n_acc:n_acc + n_lin].view(self.nch, 4, self.nlin)
+        self.stats = self.state[n_acc + n_lin:]
         self.coef = None
         self.K = 0
         self._ws = None
         # mean-fused route (pyfft_welch_accumulate_mean): usable when the window's transform
         # is negligible beyond the nfft/16 bins the kernel keeps linear sums for
-        self.nlin = self.nfft // 16
         W = np.fft.fft(win)
         p = np.abs(W) ** 2
         leak = float(p[self.nlin:self.nfft // 2 + 1].max() / (win ** 2).sum()) if self.nfft >= 1024 else 1.0
         self.can_fuse_mean = self.nfft >= 1024 and leak < (1e-9 if precision == "fp32" else 1e-18)
-        self.lin = torch.zeros((self.nch, 4, self.nlin), dtype=torch.float64, device=self.device)
         self.wlow = torch.from_numpy(np.ascontiguousarray(
             np.stack([W.real[:self.nlin], W.imag[:self.nlin]], 1))).to(self.device)
         self.est = None
@@ -121,6 +124,13 @@ class WelchPlan(object):
                            and self.hop <= self.nfft and leak8 < 1e-9)
         self.prescale = None
         self._tc_status = None
+        self._zero_est = None
+        self._tc_est = None
+
+    def reset(self):
+        """Zeroes acc, lin, stats and the segment counts (one fill)."""
+        self.state.zero_()
+        self.K = self.K_local = 0
 
     # -- detrend ------------------------------------------------------------ #
     def detrend_stats(self, x, y, rmap, j_begin, j_end):
@@ -169,8 +179,10 @@ class WelchPlan(object):
     def prepare_tc(self, x, y, rmap, j_begin, j_end, nsample=65536):
         """Provisional means and power-of-two scales from the head of the shard."""
         j1 = min(j_end, j_begin + nsample)
-        self.est = torch.zeros(2 * (self.nch + 1), dtype=torch.float64, device=self.device)
-        self.prescale = torch.empty(self.nch + 1, dtype=torch.float64, device=self.device)
+        if self._tc_est is None:                       # zeroed by the entry point itself
+            self._tc_est = torch.empty(2 * (self.nch + 1), dtype=torch.float64, device=self.device)
+            self.prescale = torch.empty(self.nch + 1, dtype=torch.float64, device=self.device)
+        self.est = self._tc_est
         check(lib.pyfft_welch_tc_prepare(_ptr(x), _ptr(y), y.stride(0), self.nch, C.byref(rmap), j_begin, j1,
                                          _ptr(self.est), _ptr(self.prescale), _stream()))
 
@@ -202,6 +214,20 @@ class WelchPlan(object):
                                            self.K_local, _ptr(self.est), _ptr(self.stats), int(nana),
                                            _ptr(self.wlow), _stream()))
         self.coef = None
+
+    def rereference(self):
+        """Sharded fused-mean route: moves this shard's sums to the common reference 0, so ONE
+        all-reduce of `state` (all_reduce_state) followed by finalize(..., correct_nana=nana)
+        replaces the pair (all-reduce stats + mean_correct, all-reduce acc)."""
+        check(lib.pyfft_welch_rereference(_ptr(self.acc), _ptr(self.lin), self.nfft, self.nch, self.K_local,
+                                          _ptr(self.est), _ptr(self.wlow), _stream()))
+        if self._zero_est is None:
+            self._zero_est = torch.zeros(2 * (self.nch + 1), dtype=torch.float64, device=self.device)
+        self.est = self._zero_est
+
+    def all_reduce_state(self, group=None):
+        """The one collective of the sharded fused-mean route: acc | lin | stats in one buffer."""
+        torch.distributed.all_reduce(self.state, group=group)
 
     # -- accumulate --------------------------------------------------------- #
     def accumulate(self, x, y, rmap, seg_first, seg_count):

@@ -332,17 +332,18 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
                 wp.detrend_stats(x, y, rmap, s_lo, c_lo)
             if s_hi > c_hi:
                 wp.detrend_stats(x, y, rmap, c_hi, s_hi)
+            fix_nana = plan.nana                        # mean correction folded into finalize
             if group is not None:
-                wp.mean_correct(plan.nana, group)       # per rank, before the sums are all-reduced
-            else:
-                fix_nana = plan.nana                    # single device: folded into finalize
+                wp.rereference()                        # common reference, then ONE collective
+                wp.all_reduce_state(group)
+                wp.K = K
         else:
             if mode != _lib.DETREND_NONE:
                 # global detrend over the whole analysed record (:356-357): each rank sums its slice
                 wp.detrend_stats(x, y, rmap, lp["stats_span"][0], lp["stats_span"][1])
                 wp.solve_detrend(mode, plan.nana, group)
             wp.accumulate(x, y, rmap, lp["k0"], nseg)
-        if group is not None:
+        if group is not None and fix_nana is None:
             wp.all_reduce(group)
         scale = 1.0 / (fftinfo.S1 ** 2) / fftinfo.ENBW             # :432-440
         res = wp.finalize(scale, onesided=bool(onesided), K=K, correct_nana=fix_nana)

@@ -167,3 +167,54 @@ def test_against_the_oracle(cuda_device):
         err = np.max(np.abs(out[i] - ref[nm])) / np.max(np.abs(ref[nm]))
         assert err <= tol, (nm, err)
     assert np.max(np.abs(out[4] - ref["Cxy"])) <= 1e-4 * np.sqrt(16384 / 2047)
+
+
+@pytest.mark.parametrize("route", ["tc", "cuda"])
+def test_rereferenced_shards_one_collective(route, cuda_device):
+    """Sharded fused-mean route with ONE collective (pyfft_welch_rereference): two shards analysed
+    about different provisional means are moved to the common reference 0, their packed states
+    (acc | lin | stats) added -- what the all-reduce does -- and corrected inside finalize; equals the
+    single-shard result (mean_correct + finalize) to double-precision rounding of the correction."""
+    import torch
+    from pyfft_b200 import engine
+    from pyfft_b200.windows import windows
+    dev = cuda_device
+    hop, n = 2048, 2 ** 20
+    x, y = _signals(n, 2, 17)
+    x = (x + np.linspace(0.0, 3.0, n)).astype(np.float32)       # drift: the shards' provisional means differ
+    K = (n - L) // hop + 1
+    win = windows("Hanning", nwins=L, verbose=False)
+    xd, yd = torch.from_numpy(x).to(dev), torch.from_numpy(y).to(dev).contiguous()
+    rmap = engine.record_map(n, 0, 0, 0, n)
+
+    def shard(k0, k1, tail):
+        wp = engine.WelchPlan(L, hop, 2, "fp32", win, dev)
+        if route == "tc":
+            wp.prepare_tc(xd, yd, rmap, k0 * hop, k1 * hop)
+            wp.accumulate_tc(xd, yd, rmap, k0, k1 - k0)
+            assert not wp.tc_failed()
+        else:
+            wp.estimate_mean(xd, yd, rmap, k0 * hop, k1 * hop)
+            wp.accumulate_mean(xd, yd, rmap, k0, k1 - k0)
+        if tail and k1 * hop < n:
+            wp.detrend_stats(xd, yd, rmap, k1 * hop, n)
+        return wp
+
+    one = shard(0, K, True)
+    one.mean_correct(n)
+    ref = one.finalize(1.0, onesided=True, K=K)
+
+    a, b = shard(0, 201, False), shard(201, K, True)
+    assert abs(float(a.est[0]) - float(b.est[0])) > 0.5
+    a.rereference()
+    b.rereference()
+    a.state += b.state                                          # the all-reduce
+    got = a.finalize(1.0, onesided=True, K=K, correct_nana=n)
+    for nm in ("Pxx", "Pyy", "Pxy"):
+        den = float(ref[nm].abs().max())
+        err = float((got[nm] - ref[nm]).abs().max()) / den
+        # the re-referencing itself is exact in double.  CUDA-core route: only the order of the fp32
+        # partial sums differs; tensor-core route: another provisional mean means another fp16
+        # rounding of every sample, i.e. the route's own 1/sqrt(K) noise
+        assert err <= (2e-6 if route == "cuda" else 6e-4 / np.sqrt(K)), (nm, err)
+    assert float((got["Cxy"] - ref["Cxy"]).abs().max()) <= (1e-5 if route == "cuda" else 1e-4 * np.sqrt(16384 / K))
