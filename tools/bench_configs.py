@@ -72,7 +72,7 @@ def main():
 
     # ---- c3: 64 channels x 2^24, nfft 2048, 75 % overlap, complex64 spectrogram output --------- #
     if not only or "c3" in only:
-        C, n, L, hop = 64, 2 ** 24, 2048, 512
+        C, n, L, hop = int(os.environ.get("PYFFT_C3_CH", "64")), 2 ** 24, 2048, 512
         x = chirps(C, n, 3)
         K = (n - L) // hop + 1
         win = windows("Hanning", nwins=L, verbose=False)
@@ -98,7 +98,7 @@ def main():
 
     # ---- c4: 16 channels x 2^25, Hilbert envelope / analytic signal; ccf 0 vs 1..15 ------------ #
     if not only or "c4" in only:
-        C, n = 16, 2 ** 25
+        C, n = int(os.environ.get("PYFFT_C4_CH", "16")), 2 ** 25
         g = torch.Generator(device=dev).manual_seed(4)
         t = torch.arange(n, device=dev, dtype=torch.float32) / 1.0e6
         u = torch.empty((C, n), dtype=torch.float32, device=dev)
@@ -127,7 +127,7 @@ def main():
             hold["o"] = engine.xcorr(u[0], u[1:], "fp32", normalise=1)
 
         ms = timed(run_ccf, reps=3, warm=2)
-        emit("c4 ccf 0 vs 1..15 (K3b)", ms, C * n * 4 + 15 * (2 * n - 1) * 4, C * n, C=C, N=n, fft_len=2 ** 26)
+        emit("c4 ccf 0 vs 1..%d (K3b)" % (C - 1), ms, C * n * 4 + (C - 1) * (2 * n - 1) * 4, C * n, C=C, N=n, fft_len=2 ** 26)
         hold.clear()
         del u
         torch.cuda.empty_cache()
