@@ -62,7 +62,7 @@ template <int LOG2R> struct BigGeom {
 };
 
 template <typename T, int LOG2R>
-constexpr size_t big_smem_bytes() { return (size_t)2 * BigGeom<LOG2R>::TB * BigGeom<LOG2R>::E * sizeof(cpx<T>); }
+constexpr size_t big_smem_bytes() { return (size_t)BigGeom<LOG2R>::TB * BigGeom<LOG2R>::E * sizeof(cpx<T>); }
 
 // v[s] *= base * step^s
 template <typename T>
@@ -104,9 +104,11 @@ __global__ void __launch_bounds__(256) bigfft_pass_kernel(const BigPass<T> p) {
     const int64_t base_addr = a * R * p.B + b;
 
     const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(sm);
-    Exchange<T, false> ex;
+    // one exchange buffer per transform (a second one would only save a barrier in the 512-point pass):
+    // the passes are bound by the latency of their strided loads, so resident CTAs matter more
+    Exchange<T, true> ex;
     ex.cur = sbase + (uint32_t)(slot * E * sizeof(cpx<T>));
-    ex.other = sbase + (uint32_t)((TB + slot) * E * sizeof(cpx<T>));
+    ex.other = ex.cur;
     const Twiddles<T> tws = load_twiddles<T, LOG2R, INV>(p.tw, t);
 
     cpx<T> v[16];
@@ -134,13 +136,14 @@ __global__ void __launch_bounds__(256) bigfft_pass_kernel(const BigPass<T> p) {
         ws = big_twiddle<T>(p, (int64_t)TPS * b, INV);
     }
     if (p.tw_mode == TW_PRE) twiddle_column<T>(v, wb, ws);
-    fft_block<T, LOG2R, INV, false>(v, ex, tws, t);
+    fft_block<T, LOG2R, INV, true>(v, ex, tws, t);
     if (p.tw_mode == TW_POST) twiddle_column<T>(v, wb, ws);
 
     const T sc = (T)p.scale;
     if (p.out_mode == OUT_NATURAL) {
         // transpose through shared memory: [slot][idx] -> thread (slot' fastest) stores k1-contiguous
         const uint32_t e = ex.cur;
+        ex.before_write();
 #pragma unroll
         for (int s = 0; s < 16; ++s) ex.st(e, t + TPS * s, v[s]);
         __syncthreads();
@@ -264,12 +267,14 @@ struct BigPlan {
 static BigPlan plan_bits(int m) {
     BigPlan pl;
     if (m <= 9) { pl.npass = 1; pl.bits[0] = m; pl.bits[1] = pl.bits[2] = 0; }
-    else if (m <= 18) { pl.npass = 2; pl.bits[0] = m - m / 2; pl.bits[1] = m / 2; pl.bits[2] = 0; }
+    // the longest pass goes LAST (innermost digit, contiguous rows): a strided pass of length R
+    // moves runs of 256 / (R / 16) columns, i.e. 128-byte runs for R = 256 but only 64 for R = 512
+    else if (m <= 18) { pl.npass = 2; pl.bits[0] = m / 2; pl.bits[1] = m - m / 2; pl.bits[2] = 0; }
     else {
         pl.npass = 3;
-        pl.bits[0] = (m + 2) / 3;
-        pl.bits[1] = (m - pl.bits[0] + 1) / 2;
-        pl.bits[2] = m - pl.bits[0] - pl.bits[1];
+        pl.bits[2] = (m + 2) / 3;
+        pl.bits[1] = (m - pl.bits[2] + 1) / 2;
+        pl.bits[0] = m - pl.bits[2] - pl.bits[1];
     }
     return pl;
 }
