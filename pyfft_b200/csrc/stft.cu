@@ -53,6 +53,224 @@ __device__ __forceinline__ double slot_sum(double v, double* red, int t) {
     return 0.0;    // caller reads *red after a barrier
 }
 
+
+// Fast path of the real-input STFT (bin_first == 0, nbins <= L/2 + 1: the one-sided spectra every
+// caller on the path asks for).  Same arithmetic as stft_kernel; what differs is the integer work
+// around it: segments outside the mirrored head are read through one base pointer with
+// compile-time offsets, the output rows are written through two row pointers with compile-time
+// offsets, the per-bin scale (with the 1/2 of the Hermitian split folded in) sits in registers,
+// and only the upper half of the packed spectrum is exchanged for the split.
+template <typename T, int LOG2L, bool SINGLE>
+__global__ void __launch_bounds__(StftGeom<LOG2L>::THREADS,
+                                  (sizeof(T) == 4 && StftGeom<LOG2L>::THREADS == 256) ? 2 : 1)
+stft_real_kernel(const StftParams<T> p) {
+    using G = StftGeom<LOG2L>;
+    constexpr int L = G::L, TPS = G::TPS, SLOTS = G::SLOTS, E = G::E;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    cpx<T>* sm = reinterpret_cast<cpx<T>*>(smem_raw);
+    T* swin = reinterpret_cast<T*>(sm + (size_t)(SINGLE ? 1 : 2) * SLOTS * E);
+    double* sred = reinterpret_cast<double*>(swin + L);     // [SLOTS][4]
+    for (int i = threadIdx.x; i < L; i += G::THREADS) swin[i] = p.window[i];
+    if (threadIdx.x < SLOTS * 4) sred[threadIdx.x] = 0.0;
+    __syncthreads();
+
+    const int slot = threadIdx.x / TPS;
+    const int t = threadIdx.x - slot * TPS;
+    const int c = blockIdx.y;
+    const int part = blockIdx.x * SLOTS + slot;
+    const int64_t nfft_total = (p.seg_count + 1) / 2;
+    const int64_t q0 = (int64_t)part * p.chunk;
+    const int64_t q1 = (q0 + p.chunk < nfft_total) ? q0 + p.chunk : nfft_total;
+    const T* __restrict__ src = p.x + (int64_t)c * p.ch_stride;
+    const double ca = p.coef ? p.coef[2 * c] : 0.0, cb = p.coef ? p.coef[2 * c + 1] : 0.0;
+    const bool linear = cb != 0.0;
+    const T cbf = (T)cb;
+    double* red = sred + slot * 4;
+
+    const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(sm);
+    Exchange<T, SINGLE> ex;
+    ex.cur = sbase + (uint32_t)(slot * E * sizeof(cpx<T>));
+    ex.other = SINGLE ? ex.cur : sbase + (uint32_t)((SLOTS + slot) * E * sizeof(cpx<T>));
+    const Twiddles<T> tws = load_twiddles<T, LOG2L, false>(p.tw, t);
+
+    // sc[s]: scale of bin t + TPS*s (s = 8: the Nyquist bin, thread 0 only), 0 for bins not asked for
+    T sc[9];
+    const T half = p.power_out ? T(0.25) : T(0.5);
+#pragma unroll
+    for (int s = 0; s < 9; ++s) {
+        const int f = t + TPS * s;
+        const bool ok = f < p.nbins && (s < 8 || t == 0);
+        sc[s] = ok ? half * (p.bin_scale ? (T)p.bin_scale[f] : T(1)) : T(0);
+    }
+    const bool full = p.nbins >= L / 2;                      // every bin below Nyquist is stored
+    const bool want_nyq = t == 0 && p.nbins > L / 2;
+    const int64_t plain0 = p.map.i0 - p.map.reflect - p.map.src_base + t;
+
+    for (int64_t it = 0; it < p.chunk; ++it) {               // same trip count for every slot (barriers inside)
+        const int64_t q = q0 + it;
+        const bool active = q < q1;
+        const int64_t ka = 2 * q;
+        const bool has_b = active && (ka + 1 < p.seg_count);
+        cpx<T> v[16];
+        T c0 = T(0), c1 = T(0);
+        if (active) {
+            const int64_t j0 = (p.seg_first + ka) * p.hop;
+            c0 = (T)(ca + cb * (double)j0);
+            c1 = (T)(ca + cb * (double)(j0 + p.hop));
+            if (j0 >= p.map.reflect) {
+                const T* __restrict__ sa = src + (j0 + plain0);
+#pragma unroll
+                for (int s = 0; s < 16; ++s) v[s].x = sa[TPS * s];
+                if (has_b) {
+                    const T* __restrict__ sb = sa + p.hop;
+#pragma unroll
+                    for (int s = 0; s < 16; ++s) v[s].y = sb[TPS * s];
+                } else {
+#pragma unroll
+                    for (int s = 0; s < 16; ++s) v[s].y = c1;
+                }
+            } else {
+                // segments touching the mirrored head of the record (fft_analysis.py:196-205)
+#pragma unroll
+                for (int s = 0; s < 16; ++s) {
+                    const int64_t n = j0 + t + TPS * s;
+                    v[s].x = src[src_index(p.map, n)];
+                    v[s].y = has_b ? src[src_index(p.map, n + p.hop)] : c1;
+                }
+            }
+            if (linear) {
+#pragma unroll
+                for (int s = 0; s < 16; ++s) {
+                    const T n = (T)(t + TPS * s);
+                    v[s].x -= c0 + cbf * n;
+                    v[s].y -= c1 + cbf * n;
+                }
+                c0 = T(0);
+                c1 = T(0);
+                if (!has_b) {
+#pragma unroll
+                    for (int s = 0; s < 16; ++s) v[s].y = T(0);
+                }
+            }
+        } else {
+#pragma unroll
+            for (int s = 0; s < 16; ++s) v[s] = mk<T>(T(0), T(0));
+        }
+        // the reductions below contain barriers / full-warp shuffles: every thread of the CTA runs
+        // them (p.per_segment and p.pseg are uniform), inactive slots on zeros
+        if (p.per_segment) {                                 // detrendwin=True (fft_analysis.py:2169-2172)
+            double sx = 0.0, sy = 0.0;
+#pragma unroll
+            for (int s = 0; s < 16; ++s) { sx += (double)(v[s].x - c0); sy += (double)(v[s].y - c1); }
+            sx = slot_sum<TPS>(sx, red + 0, t);
+            sy = slot_sum<TPS>(sy, red + 1, t);
+            if (TPS > 32) {
+                __syncthreads();
+                sx = red[0]; sy = red[1];
+                __syncthreads();
+                if (t == 0) { red[0] = 0.0; red[1] = 0.0; }
+            }
+            c0 += (T)(sx / L);
+            c1 += (T)(sy / L);
+        }
+#pragma unroll
+        for (int s = 0; s < 16; ++s) {
+            const T wv = swin[t + TPS * s];
+            v[s] = mk<T>((v[s].x - c0) * wv, (v[s].y - c1) * wv);
+        }
+        if (p.pseg) {
+            // trapezoid rule core of fft_analysis.py:2174: sum g - (g_0 + g_{L-1})/2
+            double pa = 0.0, pb = 0.0;
+#pragma unroll
+            for (int s = 0; s < 16; ++s) {
+                const bool edge = (s == 0 && t == 0) || (s == 15 && t == TPS - 1);
+                const double wgt = edge ? 0.5 : 1.0;
+                pa += wgt * (double)v[s].x * v[s].x;
+                pb += wgt * (double)v[s].y * v[s].y;
+            }
+            pa = slot_sum<TPS>(pa, red + 2, t);
+            pb = slot_sum<TPS>(pb, red + 3, t);
+            if (TPS > 32) {
+                __syncthreads();
+                pa = red[2]; pb = red[3];
+                __syncthreads();
+                if (t == 0) { red[2] = 0.0; red[3] = 0.0; }
+            }
+            if (t == 0 && active) {
+                p.pseg[(int64_t)c * p.seg_count + ka] = pa;
+                if (has_b) p.pseg[(int64_t)c * p.seg_count + ka + 1] = pb;
+            }
+        }
+        fft_block<T, LOG2L, false, SINGLE>(v, ex, tws, t);
+
+        // the split needs Z[L - f] for the bins f = t + TPS*s, s < 8: partner thread TPS - t, slot
+        // 15 - s (thread 0 pairs with itself, slot 16 - s) -- only the upper half is exchanged, in
+        // the unpadded layout [slot - 8][t] (ascending writes, descending reads: conflict-free)
+        ex.before_write();
+        const uint32_t e = ex.cur;
+        constexpr uint32_t CB = (uint32_t)sizeof(cpx<T>);
+        if (TPS % 16 == 0) {
+            const uint32_t a = e + (uint32_t)t * CB;
+#pragma unroll
+            for (int s = 8; s < 16; ++s) SharedIO<T>::st(a + (uint32_t)((s - 8) * TPS) * CB, v[s]);
+        } else {
+#pragma unroll
+            for (int s = 0; s < 16; ++s) ex.st(e, t + TPS * s, v[s]);
+        }
+        __syncthreads();
+        ex.flip();
+        if (!active) continue;
+        const int64_t row = ((int64_t)c * p.seg_count + ka) * p.nbins + t;
+        const uint32_t pa = e + (uint32_t)(TPS - t) * CB;
+        // 2U = A + conj B (segment ka), 2V = (A - conj B)/i (segment ka + 1); the 1/2 lives in sc[]
+        auto split = [&](int s, cpx<T>& U, cpx<T>& V) {
+            const cpx<T> A = v[s];
+            cpx<T> B;
+            if (TPS % 16 == 0) {
+                B = SharedIO<T>::ld(pa + (uint32_t)((7 - s) * TPS) * CB);
+                if (s == 0 && t == 0) B = A;                 // DC pairs with itself
+            } else {
+                B = ex.ld(e, (L - (t + TPS * s)) & (L - 1));
+            }
+            U = mk<T>(A.x + B.x, A.y - B.y);
+            V = mk<T>(A.y + B.y, B.x - A.x);
+        };
+        if (p.power_out) {
+            T* __restrict__ oa = static_cast<T*>(p.out) + row;
+            T* __restrict__ ob = oa + p.nbins;
+#pragma unroll
+            for (int s = 0; s < 8; ++s) {
+                cpx<T> U, V;
+                split(s, U, V);
+                if (full || t + TPS * s < p.nbins) {
+                    oa[TPS * s] = (U.x * U.x + U.y * U.y) * sc[s];
+                    if (has_b) ob[TPS * s] = (V.x * V.x + V.y * V.y) * sc[s];
+                }
+            }
+            if (want_nyq) {
+                oa[L / 2] = T(4) * v[8].x * v[8].x * sc[8];
+                if (has_b) ob[L / 2] = T(4) * v[8].y * v[8].y * sc[8];
+            }
+        } else {
+            cpx<T>* __restrict__ oa = static_cast<cpx<T>*>(p.out) + row;
+            cpx<T>* __restrict__ ob = oa + p.nbins;
+#pragma unroll
+            for (int s = 0; s < 8; ++s) {
+                cpx<T> U, V;
+                split(s, U, V);
+                if (full || t + TPS * s < p.nbins) {
+                    oa[TPS * s] = mk<T>(U.x * sc[s], U.y * sc[s]);
+                    if (has_b) ob[TPS * s] = mk<T>(V.x * sc[s], V.y * sc[s]);
+                }
+            }
+            if (want_nyq) {
+                oa[L / 2] = mk<T>(T(2) * v[8].x * sc[8], T(0));
+                if (has_b) ob[L / 2] = mk<T>(T(2) * v[8].y * sc[8], T(0));
+            }
+        }
+    }
+}
+
 template <typename T, int LOG2L, bool CPLX, bool SINGLE>
 __global__ void __launch_bounds__(StftGeom<LOG2L>::THREADS) stft_kernel(const StftParams<T> p) {
     using G = StftGeom<LOG2L>;
@@ -247,6 +465,21 @@ __global__ void __launch_bounds__(256) stft_products_kernel(const cpx<T>* __rest
     }
 }
 
+// grid.x per channel so that the CTAs fill the resident slots of the device a whole number of
+// times (a partial last wave costs as much as a full one): best fill among 1..4 waves
+static int64_t stft_parts(int resident, int nch, int64_t maxb) {
+    int64_t best = 1;
+    double best_fill = 0.0;
+    for (int w = 1; w <= 4; ++w) {
+        const int64_t gx = ((int64_t)resident * w) / nch;
+        if (gx < 1) continue;
+        const double fill = (double)(gx * nch) / ((double)resident * w);
+        if (fill > best_fill + 0.02) { best_fill = fill; best = gx; }
+    }
+    if (best > maxb) best = maxb;
+    return best < 1 ? 1 : best;
+}
+
 template <typename T, int LOG2L, bool CPLX>
 static int launch_stft(StftParams<T> p, int nch, cudaStream_t st) {
     using G = StftGeom<LOG2L>;
@@ -258,8 +491,21 @@ static int launch_stft(StftParams<T> p, int nch, cudaStream_t st) {
     const int64_t nfft_total = (p.seg_count + (CPLX ? 0 : 1)) / (CPLX ? 1 : 2);
     int sms = device_sm_count();
     if (sms <= 0) sms = 148;
-    int64_t gx = ((int64_t)4 * sms + nch - 1) / nch;
     const int64_t maxb = (nfft_total + G::SLOTS - 1) / G::SLOTS;
+    const bool fast = !CPLX && p.bin_first == 0 && p.nbins <= G::L / 2 + 1;
+    if (fast) {
+        auto kern = stft_real_kernel<T, LOG2L, SINGLE>;
+        PYFFT_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        int per_sm = 0;
+        PYFFT_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, G::THREADS, smem));
+        if (per_sm < 1) per_sm = 1;
+        const int64_t gx = stft_parts(per_sm * sms, nch, maxb);
+        p.chunk = (nfft_total + gx * G::SLOTS - 1) / (gx * G::SLOTS);
+        kern<<<dim3((unsigned)gx, (unsigned)nch), G::THREADS, smem, st>>>(p);
+        PYFFT_LAUNCH_OK("stft_real_kernel");
+        return PYFFT_OK;
+    }
+    int64_t gx = ((int64_t)4 * sms + nch - 1) / nch;
     if (gx > maxb) gx = maxb;
     if (gx < 1) gx = 1;
     p.chunk = (nfft_total + gx * G::SLOTS - 1) / (gx * G::SLOTS);
