@@ -10,6 +10,8 @@
 // accumulator.  A CTA owns FB consecutive bins and all nch rows; thread (i, fb) keeps row i of
 // G[f0+fb] (nch complex sums) in registers and streams the segments of the chunk through
 // shared memory.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace pyfft {
@@ -66,6 +68,185 @@ csm_product_kernel(const cpx<T>* __restrict__ X, int64_t K, int nb, int ksplit, 
     }
 }
 
+// Register-tiled product for fp32 spectra and nch = 16 / 32 / 64: a thread owns an 8 x 8 block
+// (rows 8a.., columns 8b.., b >= a: G is Hermitian, the lower triangle is mirrored when the sums
+// are flushed) of one bin's matrix = 128 fp32 accumulators and 256 FFMA per segment for 8
+// 16-byte shared-memory loads.  A CTA owns FB consecutive bins (25 for 32 channels: 8 warps, one
+// 200-byte run per channel and segment) and a range of segments; the spectra X[c][k][f] are transposed on the fly into
+// [k][bin][c] by 8-byte cp.async copies, in a ring of 3 stages of 4 segments.  Inside a row
+// channel 8a + 2h + p sits at byte h*(NB*16) + a*16 + p*8 and rows are ROW = C*8 + 64 bytes apart,
+// so the 16-byte loads of a quarter warp (one h, all row blocks a of at most two bins) fall into
+// distinct banks.
+template <int C> struct CsmTile {
+    static constexpr int NB = C / 8, NT = NB * (NB + 1) / 2, KB = 4;
+    static constexpr int FB = 256 / NT > 32 ? 32 : 256 / NT;     // bins per CTA: 32 / 25 / 7
+    static constexpr int THREADS = (FB * NT + 31) / 32 * 32;     // 96 / 256 / 256 (the last lanes idle)
+    static constexpr int MINB = THREADS >= 256 ? 1 : 2;          // 8 x 8 tiles want ~250 registers
+    static constexpr int ROW = C * 8 + 64;               // bytes per (segment, bin) row; ROW mod 128 == 64
+    static constexpr int STAGE = KB * FB * ROW;
+    static constexpr int NSTAGE = 3;
+    static constexpr int SMEM = NSTAGE * STAGE;
+};
+
+template <int C>
+__global__ void __launch_bounds__(CsmTile<C>::THREADS, CsmTile<C>::MINB)
+csm_tile_kernel(const cpx<float>* __restrict__ X, int64_t K, int nb, int ksplit, double* __restrict__ G) {
+    using Tl = CsmTile<C>;
+    constexpr int NB = Tl::NB, NT = Tl::NT, FB = Tl::FB, KB = Tl::KB, THREADS = Tl::THREADS, ROW = Tl::ROW;
+    extern __shared__ __align__(16) unsigned char csm_smem[];
+    const int tid = threadIdx.x;
+    const bool lane_on = tid < FB * NT;
+    const int fb = lane_on ? tid / NT : 0;
+    int tile = lane_on ? tid - fb * NT : 0, a = 0;
+    while (tile >= NB - a) { tile -= NB - a; ++a; }
+    const int b = a + tile;
+    const int f0 = blockIdx.x * FB;
+    const int64_t kper = (K + ksplit - 1) / ksplit;
+    const int64_t k0 = (int64_t)blockIdx.y * kper;
+    const int64_t k1 = k0 + kper < K ? k0 + kper : K;
+    if (k0 >= k1) return;
+    const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(csm_smem);
+
+    float ar[8][8], ai[8][8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { ar[i][j] = 0.f; ai[i][j] = 0.f; }
+
+    // staging: thread-invariant (channel, bin) slots, NSLOT per thread and segment; only the
+    // segment index changes from copy to copy
+    constexpr int NSLOT = (C * FB + THREADS - 1) / THREADS;
+    uint32_t goff[NSLOT], soff[NSLOT];                       // element offset in X (without k), byte offset in a stage
+    uint32_t okmask = 0;
+#pragma unroll
+    for (int i = 0; i < NSLOT; ++i) {
+        const int e = tid + THREADS * i;
+        const int c = e / FB, fbb = e - c * FB;
+        const bool ok = e < C * FB && f0 + fbb < nb;
+        goff[i] = ok ? (uint32_t)((int64_t)c * K * nb + f0 + fbb) : 0u;
+        soff[i] = (uint32_t)(fbb * ROW + ((c >> 1) & 3) * (NB * 16) + (c >> 3) * 16 + (c & 1) * 8);   // [h][block][2 channels]
+        if (e < C * FB) okmask |= (ok ? 1u : 0u) << (2 * i) | 2u << (2 * i);   // bit 2i: copy, bit 2i+1: slot exists
+    }
+    auto issue = [&](int stage, int64_t kb) {
+        const uint32_t dst0 = sbase + (uint32_t)(stage * Tl::STAGE);
+#pragma unroll
+        for (int q = 0; q < KB; ++q) {
+            const int64_t k = kb + q;
+            const bool kok = k < k1;
+            const cpx<float>* srow = X + (kok ? k : k0) * nb;
+#pragma unroll
+            for (int i = 0; i < NSLOT; ++i) {
+                if (okmask >> (2 * i + 1) & 1u) {
+                    const int nbytes = (kok && (okmask >> (2 * i) & 1u)) ? 8 : 0;      // 0: zero fill
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(dst0 + q * (FB * ROW) + soff[i]),
+                                 "l"(srow + goff[i]), "r"(nbytes) : "memory");
+                }
+            }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+
+    // NSTAGE-deep ring: the copies of stage s + NSTAGE - 1 are in flight while stage s is consumed
+    constexpr int NSTAGE = Tl::NSTAGE;
+    int64_t knext = k0;
+#pragma unroll
+    for (int sidx = 0; sidx < NSTAGE - 1; ++sidx) {
+        if (knext < k1) issue(sidx, knext);
+        else asm volatile("cp.async.commit_group;" ::: "memory");
+        knext += KB;
+    }
+    int stage = 0, fill = NSTAGE - 1;
+    for (int64_t kb = k0; kb < k1; kb += KB) {
+        asm volatile("cp.async.wait_group %0;" ::"n"(NSTAGE - 2) : "memory");
+        __syncthreads();                                     // stage `stage` landed; stage `fill` is free again
+        if (knext < k1) issue(fill, knext);
+        else asm volatile("cp.async.commit_group;" ::: "memory");
+        knext += KB;
+        fill = fill + 1 == NSTAGE ? 0 : fill + 1;
+        const unsigned char* row = csm_smem + stage * Tl::STAGE + fb * ROW;
+#pragma unroll
+        for (int q = 0; q < KB; ++q) {
+            const unsigned char* pi = row + q * (FB * ROW) + a * 16;
+            const unsigned char* pj = row + q * (FB * ROW) + b * 16;
+            float4 xi[4], xj[4];
+#pragma unroll
+            for (int h = 0; h < 4; ++h) {
+                xi[h] = *reinterpret_cast<const float4*>(pi + h * (NB * 16));
+                xj[h] = *reinterpret_cast<const float4*>(pj + h * (NB * 16));
+            }
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const float ir = (i & 1) ? xi[i >> 1].z : xi[i >> 1].x;
+                const float ii = (i & 1) ? xi[i >> 1].w : xi[i >> 1].y;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const float jr = (j & 1) ? xj[j >> 1].z : xj[j >> 1].x;
+                    const float ji = (j & 1) ? xj[j >> 1].w : xj[j >> 1].y;
+                    // X_j conj(X_i)
+                    ar[i][j] = fmaf(jr, ir, ar[i][j]);
+                    ar[i][j] = fmaf(ji, ii, ar[i][j]);
+                    ai[i][j] = fmaf(ji, ir, ai[i][j]);
+                    ai[i][j] = fmaf(-jr, ii, ai[i][j]);
+                }
+            }
+        }
+        stage = stage + 1 == NSTAGE ? 0 : stage + 1;
+    }
+    const int f = f0 + fb;
+    if (f >= nb || !lane_on) return;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int gi = 8 * a + i, gj = 8 * b + j;
+            double* g = G + (((int64_t)f * C + gi) * C + gj) * 2;
+            atomicAdd(g, (double)ar[i][j]);
+            atomicAdd(g + 1, (double)ai[i][j]);
+            if (a != b) {
+                double* gt = G + (((int64_t)f * C + gj) * C + gi) * 2;
+                atomicAdd(gt, (double)ar[i][j]);
+                atomicAdd(gt + 1, -(double)ai[i][j]);
+            }
+        }
+    }
+}
+
+template <int C>
+static int launch_csm_tile(const cpx<float>* X, int64_t cnt, int nb, double* G, int sms, cudaStream_t st) {
+    using Tl = CsmTile<C>;
+    auto kern = csm_tile_kernel<C>;
+    PYFFT_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Tl::SMEM));
+    int per_sm = 0;
+    PYFFT_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, Tl::THREADS, Tl::SMEM));
+    if (per_sm < 1) per_sm = 1;
+    const int gx = (nb + Tl::FB - 1) / Tl::FB;
+    // about six waves of resident CTAs, at least 16 segments per CTA
+    int64_t ksplit = ((int64_t)6 * per_sm * sms + gx - 1) / gx;
+    if (ksplit > cnt / 16) ksplit = cnt / 16;
+    if (ksplit < 1) ksplit = 1;
+    kern<<<dim3(gx, (unsigned)ksplit), Tl::THREADS, Tl::SMEM, st>>>(X, cnt, nb, (int)ksplit, G);
+    PYFFT_LAUNCH_OK("csm_tile_kernel");
+    return PYFFT_OK;
+}
+
+template <typename T>
+static int csm_tile_dispatch(const cpx<T>*, int64_t, int, int, double*, int, cudaStream_t, bool* done) {
+    *done = false;
+    return PYFFT_OK;
+}
+template <>
+int csm_tile_dispatch<float>(const cpx<float>* X, int64_t cnt, int nb, int nch, double* G, int sms, cudaStream_t st,
+                             bool* done) {
+    *done = true;
+    switch (nch) {
+        case 16: return launch_csm_tile<16>(X, cnt, nb, G, sms, st);
+        case 32: return launch_csm_tile<32>(X, cnt, nb, G, sms, st);
+        case 64: return launch_csm_tile<64>(X, cnt, nb, G, sms, st);
+    }
+    *done = false;
+    return PYFFT_OK;
+}
+
 // generic channel count (any nch <= 64): one thread per (i, j, fb) would be wasteful; instead
 // thread (i, fb) loops j with accumulators in local memory only for small nch -- used for
 // channel counts without a specialised instance
@@ -92,8 +273,14 @@ csm_product_generic_kernel(const cpx<T>* __restrict__ X, int64_t K, int nb, int 
 }
 
 static int64_t csm_chunk(int64_t seg_count, int nch, int nb, int64_t esz) {
-    // ~512 MB of spectra per chunk, an even number of segments (K2 packs segment pairs)
-    int64_t kc = (int64_t(512) << 20) / ((int64_t)nch * nb * esz);
+    // up to 16 GB of spectra per chunk (180 GB of HBM: config 5's per-GPU share is one chunk, so
+    // the accumulators are flushed once), an even number of segments (K2 packs segment pairs)
+    int64_t cap = int64_t(16) << 30;
+    if (const char* e = getenv("PYFFT_CSM_CHUNK_BYTES")) {     // tests: force several chunks on small records
+        const long long v = atoll(e);
+        if (v > 0) cap = v;
+    }
+    int64_t kc = cap / ((int64_t)nch * nb * esz);
     kc &= ~int64_t(1);
     if (kc < 2) kc = 2;
     if (kc > seg_count) kc = seg_count;
@@ -119,6 +306,10 @@ static int csm_impl(int dtype, const void* x, int64_t ch_stride, int nch, const 
                             nullptr, st);
         if (rc) return rc;
         const cpx<T>* X = static_cast<const cpx<T>*>(ws);
+        bool done = false;
+        rc = csm_tile_dispatch<T>(X, cnt, nb, nch, G, sms, st, &done);
+        if (rc) return rc;
+        if (done) continue;
         const int gx = (nb + CSM_FB - 1) / CSM_FB;
         int ksplit = (4 * sms + gx - 1) / gx;
         if (ksplit < 1) ksplit = 1;

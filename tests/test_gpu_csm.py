@@ -11,6 +11,7 @@ pytestmark = pytest.mark.gpu
 
 @pytest.mark.parametrize("nch,n,navr,precision", [(4, 2 ** 15, 31, "fp64"), (3, 2 ** 15, 31, "fp64"),
                                                   (8, 2 ** 16, 63, "fp32"), (32, 2 ** 17, 31, "fp32"),
+                                                  (16, 2 ** 16, 31, "fp32"), (64, 2 ** 15, 15, "fp32"),
                                                   (32, 2 ** 16, 15, "fp64")])
 def test_csm_matches_oracle(nch, n, navr, precision, cuda_device):
     from oracle import restatement as R
@@ -57,3 +58,16 @@ def test_csm_config5_cut(cuda_device):
     f, G = cross_spectral_matrix(t, torch.from_numpy(sig), Navr=navr, windowoverlap=0.5, precision="fp32")
     assert G.shape == (4096, 32, 32)
     assert relerr(G, Gr) <= 1e-5
+
+
+def test_csm_several_chunks(cuda_device, monkeypatch):
+    """The spectra workspace is processed in chunks of segments; a small cap forces several chunks
+    (odd tail included) and the sums must not change."""
+    from oracle import signals
+    from pyfft_b200 import cross_spectral_matrix
+    t, sig = signals.c5_mixture(n=2 ** 17, nch=32)
+    sig = sig.astype(np.float32)
+    f, G1 = cross_spectral_matrix(t, sig, Navr=63, windowoverlap=0.5, precision="fp32")
+    monkeypatch.setenv("PYFFT_CSM_CHUNK_BYTES", str(10 * 32 * 2049 * 8))       # 10 segments per chunk
+    f, G2 = cross_spectral_matrix(t, sig, Navr=63, windowoverlap=0.5, precision="fp32")
+    assert relerr(G2, G1) <= 2e-6
