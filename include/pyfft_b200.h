@@ -295,7 +295,11 @@ int pyfft_stft_products(int dtype, const void* X, const void* Y, int32_t nch, in
  *   reuse one reference channel); out is real of `dtype`, [pairs][2n-1].
  *   workspace: pyfft_bigfft_workspace_bytes(dtype, L, pairs + (x_stride ? pairs : 1)) with
  *   L = the power of two >= 2n-1 (at least 16).
- * pyfft_hilbert needs pyfft_bigfft_workspace_bytes(dtype, n, batch) only when analytic is NULL.
+ * pyfft_hilbert: with a workspace of pyfft_bigfft_workspace_bytes(dtype, n, (batch + 1) / 2) bytes
+ *   and batch >= 2, two records share one complex transform (half the work; the Hilbert
+ *   transform is linear).  Without it the records are transformed one by one, in place in
+ *   `analytic`; pyfft_bigfft_workspace_bytes(dtype, n, batch) is then needed only when analytic
+ *   is NULL.  pyfft_xcorr pairs the records of y the same way when x_stride = 0.
  * ------------------------------------------------------------------------- */
 int64_t pyfft_bigfft_workspace_bytes(int dtype, int64_t nfft, int32_t batch);
 

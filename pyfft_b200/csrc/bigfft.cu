@@ -6,6 +6,13 @@
 //                                         X conj(Y) -> inverse -> lag reorder + 1/(n std std)
 //   pyfft_fft_c2c  (fft_analysis.py:2096-2116) numpy.fft.fft / ifft contract, natural order
 //
+// Two real records per complex transform.  Both callers are LINEAR in the record, so records
+// a and b ride one transform as z = a + i b and no spectral un-mixing is needed:
+//   Hilbert:  A(z) = A(a) + i A(b) with A(u) = u + i H(u), hence H(a) = Im A(z) - b and
+//             H(b) = a - Re A(z); the last pass re-reads a and b and writes both analytic signals;
+//   ccf with a shared first record x:  ifft(X conj(Z)) = c(x, a) - i c(x, b).
+// Half the transforms, half the HBM traffic of one transform per record.
+//
 // Decomposition N = N1*N2*N3 (decimation in frequency): pass i transforms digit i
 // (length N_i, element stride B_i = prod_{j>i} N_j) for every other index and multiplies the
 // result by W_{N_i B_i}^{k_i b}.  The spectrum is left in digit-transposed order
@@ -18,8 +25,9 @@
 
 namespace pyfft {
 
-enum { IN_CPLX = 0, IN_REAL = 1 };
-enum { OUT_CPLX = 0, OUT_MASK = 1, OUT_MULCONJ = 2, OUT_NATURAL = 3, OUT_HILBERT = 4, OUT_XCORR = 5 };
+enum { IN_CPLX = 0, IN_REAL = 1, IN_REAL2 = 2 };
+enum { OUT_CPLX = 0, OUT_MASK = 1, OUT_MULCONJ = 2, OUT_NATURAL = 3, OUT_HILBERT = 4, OUT_XCORR = 5,
+       OUT_HILBERT2 = 6, OUT_XCORR2 = 7 };
 enum { TW_NONE = 0, TW_POST = 1, TW_PRE = 2 };
 
 template <typename T> struct BigPass {
@@ -42,6 +50,7 @@ template <typename T> struct BigPass {
     double scale;
     const double* bscale;                     // OUT_XCORR: per-batch factor (or null)
     int64_t nsig;                             // OUT_XCORR: record length n (output has 2n-1 lags)
+    int nreal;                                // IN_REAL2 / OUT_*2: number of real records (two per transform)
 };
 
 template <typename T>
@@ -121,6 +130,18 @@ __global__ void __launch_bounds__(256) bigfft_pass_kernel(const BigPass<T> p) {
                 const int64_t i = base_addr + (int64_t)(t + TPS * s) * p.B;
                 v[s] = mk<T>(i < p.n_valid ? src[i] - m : T(0), T(0));
             }
+        } else if (p.in_mode == IN_REAL2) {
+            const T* sa = static_cast<const T*>(p.in) + 2 * bat * p.in_bs;
+            const bool hb = 2 * bat + 1 < p.nreal;
+            const T* sb = hb ? sa + p.in_bs : sa;
+            const T ma = p.mean ? (T)p.mean[2 * bat] : T(0);
+            const T mb = (p.mean && hb) ? (T)p.mean[2 * bat + 1] : T(0);
+#pragma unroll
+            for (int s = 0; s < 16; ++s) {
+                const int64_t i = base_addr + (int64_t)(t + TPS * s) * p.B;
+                const bool ok = i < p.n_valid;
+                v[s] = mk<T>(ok ? sa[i] - ma : T(0), (ok && hb) ? sb[i] - mb : T(0));
+            }
         } else {
             const cpx<T>* src = static_cast<const cpx<T>*>(p.in) + bat * p.in_bs;
 #pragma unroll
@@ -195,6 +216,43 @@ __global__ void __launch_bounds__(256) bigfft_pass_kernel(const BigPass<T> p) {
             const T re = v[s].x * sc, im = v[s].y * sc;
             if (za) za[i] = mk<T>(re, im);
             if (env) env[i] = sqrt(re * re + im * im);
+        }
+    } else if (p.out_mode == OUT_HILBERT2) {
+        // v = A(a + i b): H(a) = Im v - b, H(b) = a - Re v; records 2 bat and 2 bat + 1
+        const bool hb = 2 * bat + 1 < p.nreal;
+        const T* ua = static_cast<const T*>(p.in2) + 2 * bat * p.in2_bs;
+        const T* ub = hb ? ua + p.in2_bs : ua;
+        cpx<T>* za = p.out ? static_cast<cpx<T>*>(p.out) + 2 * bat * p.out_bs : nullptr;
+        T* env = p.out2 ? static_cast<T*>(p.out2) + 2 * bat * p.out2_bs : nullptr;
+#pragma unroll
+        for (int s = 0; s < 16; ++s) {
+            const int64_t i = base_addr + (int64_t)(t + TPS * s) * p.B;
+            const T a = ua[i], b = hb ? ub[i] : T(0);
+            const T ha = v[s].y * sc - b, hbv = a - v[s].x * sc;
+            if (za) za[i] = mk<T>(a, ha);
+            if (env) env[i] = sqrt(a * a + ha * ha);
+            if (hb) {
+                if (za) za[p.out_bs + i] = mk<T>(b, hbv);
+                if (env) env[p.out2_bs + i] = sqrt(b * b + hbv * hbv);
+            }
+        }
+    } else if (p.out_mode == OUT_XCORR2) {
+        // v = c(x, a) - i c(x, b): records 2 bat and 2 bat + 1 of the second operand
+        const bool hb = 2 * bat + 1 < p.nreal;
+        T* da = static_cast<T*>(p.out) + 2 * bat * p.out_bs;
+        const T fa = (T)(p.scale * (p.bscale ? p.bscale[2 * bat] : 1.0));
+        const T fb = hb ? -(T)(p.scale * (p.bscale ? p.bscale[2 * bat + 1] : 1.0)) : T(0);
+        const int64_t n = p.nsig, tail = p.N - (n - 1);
+#pragma unroll
+        for (int s = 0; s < 16; ++s) {
+            const int64_t i = base_addr + (int64_t)(t + TPS * s) * p.B;
+            int64_t o = -1;
+            if (i < n) o = i + n - 1;
+            else if (i >= tail) o = i - tail;
+            if (o >= 0) {
+                da[o] = v[s].x * fa;
+                if (hb) da[p.out_bs + o] = v[s].y * fb;
+            }
         }
     } else if (p.out_mode == OUT_XCORR) {
         // numpy.correlate(..., 'full') order: lags -(n-1) .. n-1  (ccf.py:69-74)
@@ -331,7 +389,7 @@ template <typename T> static BigPass<T> blank_pass(int64_t N) {
     p.A = 1; p.B = 1; p.N = N; p.N1 = 1; p.N2 = 1;
     p.tw_mode = TW_NONE; p.tw_lo = p.tw_hi = nullptr; p.lo_bits = 0; p.tw = nullptr;
     p.in_mode = IN_CPLX; p.n_valid = N; p.mean = nullptr;
-    p.out_mode = OUT_CPLX; p.scale = 1.0; p.bscale = nullptr; p.nsig = 0;
+    p.out_mode = OUT_CPLX; p.scale = 1.0; p.bscale = nullptr; p.nsig = 0; p.nreal = 0;
     return p;
 }
 
@@ -355,7 +413,7 @@ static int run_dif(int m, bool inv, const BigPass<T>& first, const BigPass<T>& l
         p.in = buf; p.in_bs = N; p.out = buf; p.out_bs = N;
         if (i == 0) {
             p.in = first.in; p.in_bs = first.in_bs; p.in_mode = first.in_mode;
-            p.n_valid = first.n_valid; p.mean = first.mean;
+            p.n_valid = first.n_valid; p.mean = first.mean; p.nreal = first.nreal;
         }
         if (i == pl.npass - 1) {
             p.out_mode = last.out_mode; p.scale = last.scale;
@@ -389,6 +447,7 @@ static int run_dit_inverse(int m, const BigPass<T>& last, void* buf, int batch, 
             p.out_mode = last.out_mode; p.out = last.out; p.out_bs = last.out_bs;
             p.out2 = last.out2; p.out2_bs = last.out2_bs; p.scale = last.scale;
             p.bscale = last.bscale; p.nsig = last.nsig;
+            p.in2 = last.in2; p.in2_bs = last.in2_bs; p.nreal = last.nreal;
         }
         int rc = launch_pass<T>(pl.bits[i], true, p, batch, st);
         if (rc) return rc;
@@ -413,6 +472,19 @@ static int hilbert_impl(const void* in, int64_t n, int batch, void* analytic, vo
     int m = 0;
     int rc = check_pow2(n, 4, 27, &m);
     if (rc) return rc;
+    const int npair = (batch + 1) / 2;
+    if (batch >= 2 && ws && wsb >= (int64_t)npair * n * (int64_t)sizeof(cpx<T>)) {
+        // two records per transform (see the top of the file); the work buffer is the workspace
+        BigPass<T> first = blank_pass<T>(n), last = blank_pass<T>(n);
+        first.in = in; first.in_bs = n; first.in_mode = IN_REAL2; first.n_valid = n; first.nreal = batch;
+        last.out_mode = OUT_MASK;
+        if ((rc = run_dif<T>(m, false, first, last, ws, npair, st))) return rc;
+        BigPass<T> fin = blank_pass<T>(n);
+        fin.out_mode = OUT_HILBERT2; fin.out = analytic; fin.out_bs = n; fin.out2 = envelope; fin.out2_bs = n;
+        fin.in2 = in; fin.in2_bs = n; fin.nreal = batch;
+        fin.scale = 1.0 / (double)n;
+        return run_dit_inverse<T>(m, fin, ws, npair, st);
+    }
     void* buf = analytic;                        // the analytic output doubles as the work buffer
     if (!buf) {
         if (!ws || wsb < (int64_t)batch * n * (int64_t)sizeof(cpx<T>))
@@ -473,6 +545,18 @@ static int xcorr_impl(const void* x, int64_t xs, const void* y, int64_t ys, int6
     first.in = x; first.in_bs = xs; first.in_mode = IN_REAL; first.n_valid = n; first.mean = normalise ? mean_x : nullptr;
     int rc;
     if ((rc = run_dif<T>(m, false, first, last, bufx, nx, st))) return rc;
+    if (xs == 0 && pairs >= 2) {
+        // shared first record: two second records per transform (see the top of the file)
+        const int npair = (pairs + 1) / 2;
+        first.in = y; first.in_bs = ys; first.in_mode = IN_REAL2; first.nreal = pairs;
+        first.mean = normalise ? mean_y : nullptr;
+        last.out_mode = OUT_MULCONJ; last.in2 = bufx; last.in2_bs = 0;
+        if ((rc = run_dif<T>(m, false, first, last, bufy, npair, st))) return rc;
+        BigPass<T> fin2 = blank_pass<T>(N);
+        fin2.out_mode = OUT_XCORR2; fin2.out = out; fin2.out_bs = 2 * n - 1; fin2.scale = 1.0 / (double)N;
+        fin2.bscale = normalise == 1 ? norm : nullptr; fin2.nsig = n; fin2.nreal = pairs;
+        return run_dit_inverse<T>(m, fin2, bufy, npair, st);
+    }
     first.in = y; first.in_bs = ys; first.mean = normalise ? mean_y : nullptr;
     last.out_mode = OUT_MULCONJ; last.in2 = bufx; last.in2_bs = xs == 0 ? 0 : N;
     if ((rc = run_dif<T>(m, false, first, last, bufy, pairs, st))) return rc;

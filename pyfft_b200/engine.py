@@ -381,9 +381,11 @@ def hilbert(u, precision, want_analytic=True, want_envelope=False):
     u = u.contiguous()
     z = torch.empty((batch, n), dtype=_TORCH_CPLX[precision], device=dev) if want_analytic else None
     env = torch.empty((batch, n), dtype=_TORCH_REAL[precision], device=dev) if want_envelope else None
+    # two records ride one complex transform (bigfft.cu): the work buffer is a workspace of
+    # ceil(batch / 2) transforms; a single record works in place in the analytic output
     ws, wsb = None, 0
-    if z is None:
-        wsb = check(lib.pyfft_bigfft_workspace_bytes(_CODE[precision], n, batch))
+    if batch >= 2 or z is None:
+        wsb = check(lib.pyfft_bigfft_workspace_bytes(_CODE[precision], n, (batch + 1) // 2))
         ws = torch.empty(wsb, dtype=torch.uint8, device=dev)
     check(lib.pyfft_hilbert(_CODE[precision], _ptr(u), n, batch, _ptr(z), _ptr(env), _ptr(ws), wsb,
                             _stream()))

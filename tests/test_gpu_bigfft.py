@@ -126,3 +126,48 @@ def test_fft_c2c_matches_numpy(precision, log2n, cuda_device):
     assert relerr(out, ref) <= tol
     back = engine.fft_c2c(torch.from_numpy(ref.astype(z.dtype)).to(cuda_device), precision, inverse=True)
     assert relerr(back.cpu().numpy(), z) <= tol
+
+
+@pytest.mark.parametrize("nrec,log2n", [(2, 10), (5, 14), (3, 19)])
+def test_hilbert_two_records_per_transform(nrec, log2n, cuda_device):
+    """Batches ride one complex transform per two records (odd tail included): every record must
+    equal its own single-record result and the oracle; envelope = |analytic|."""
+    from oracle import restatement as R
+    from pyfft_b200 import hilbert
+    n = 1 << log2n
+    rng = np.random.default_rng(60 + log2n)
+    t = np.arange(n) / 1.0e6
+    u = np.stack([(1 + 0.3 * c) * np.sin(2 * np.pi * (5e3 + 1e3 * c) * t) + 0.1 * rng.standard_normal(n) + c
+                  for c in range(nrec)])
+    z = hilbert(u)
+    assert z.shape == (nrec, n)
+    for c in range(nrec):
+        assert relerr(z[c], R.hilbert(u[c])) <= 1e-12
+        assert relerr(z[c], hilbert(u[c])) <= 1e-12
+    u32 = u.astype(np.float32)
+    z32 = hilbert(u32)
+    env = hilbert(u32, envelope=True)
+    for c in range(nrec):
+        ref = R.hilbert(u32[c].astype(np.float64))
+        assert relerr(z32[c], ref) <= 1e-5
+        assert relerr(env[c], np.abs(ref)) <= 1e-5
+
+
+def test_ccf_two_records_per_transform(cuda_device):
+    """One reference record against 4 and 5 records (pairs share a transform): each row equals the
+    single-pair call."""
+    from pyfft_b200 import ccf
+    rng = np.random.default_rng(61)
+    n = 3000
+    x0 = rng.standard_normal(n) + 2.0
+    for nrec in (4, 5):
+        y = rng.standard_normal((nrec, n)) + np.arange(nrec)[:, None]
+        y[1, 17:] += 0.8 * x0[:-17]
+        for prec, tol in (("fp64", 1e-12), ("fp32", 3e-6)):
+            xs = x0 if prec == "fp64" else x0.astype(np.float32)
+            ys = y if prec == "fp64" else y.astype(np.float32)
+            _, cm = ccf(xs, ys, 1.0e5, precision=prec)
+            assert cm.shape == (nrec, 2 * n - 1)
+            for c in range(nrec):
+                _, c1 = ccf(xs, ys[c], 1.0e5, precision=prec)
+                assert np.max(np.abs(cm[c] - c1)) <= tol
