@@ -23,6 +23,10 @@
 // natural-order spectrum, transposes -- inside its last pass, through shared memory.
 #include "common.cuh"
 
+#ifndef PYFFT_BIG_STRIDED_THREADS
+#define PYFFT_BIG_STRIDED_THREADS 256
+#endif
+
 namespace pyfft {
 
 enum { IN_CPLX = 0, IN_REAL = 1, IN_REAL2 = 2 };
@@ -62,16 +66,24 @@ __device__ __forceinline__ cpx<T> big_twiddle(const BigPass<T>& p, int64_t j, bo
     return w;
 }
 
-template <int LOG2R> struct BigGeom {
+// strided passes move runs of TB neighbouring columns: 512 threads double the run (256 bytes for
+// the 256-point passes of a 2^25 transform), which HBM rewards; contiguous passes keep 256 threads
+template <int LOG2R, bool WIDE = false> struct BigGeom {
     static constexpr int R = 1 << LOG2R;
     static constexpr int TPS = R / 16;
-    static constexpr int THREADS = 256;
+    static constexpr int THREADS = WIDE ? PYFFT_BIG_STRIDED_THREADS : 256;
     static constexpr int TB = THREADS / TPS;       // transforms per CTA
     static constexpr int E = smem_elems(R);
 };
 
-template <typename T, int LOG2R>
-constexpr size_t big_smem_bytes() { return (size_t)BigGeom<LOG2R>::TB * BigGeom<LOG2R>::E * sizeof(cpx<T>); }
+// wide CTAs for strided fp32 passes only (fp64 runs are 256 bytes already)
+template <typename T, bool STRIDED> struct BigWide { static constexpr bool value = STRIDED && sizeof(T) == 4; };
+
+template <typename T, int LOG2R, bool STRIDED>
+constexpr size_t big_smem_bytes() {
+    using G = BigGeom<LOG2R, BigWide<T, STRIDED>::value>;
+    return (size_t)G::TB * G::E * sizeof(cpx<T>);
+}
 
 // v[s] *= base * step^s
 template <typename T>
@@ -82,8 +94,9 @@ __device__ __forceinline__ void twiddle_column(cpx<T> (&v)[16], cpx<T> base, cpx
 }
 
 template <typename T, int LOG2R, bool INV, bool STRIDED>
-__global__ void __launch_bounds__(256) bigfft_pass_kernel(const BigPass<T> p) {
-    using G = BigGeom<LOG2R>;
+__global__ void __launch_bounds__(BigGeom<LOG2R, BigWide<T, STRIDED>::value>::THREADS)
+bigfft_pass_kernel(const BigPass<T> p) {
+    using G = BigGeom<LOG2R, BigWide<T, STRIDED>::value>;
     constexpr int R = G::R, TPS = G::TPS, TB = G::TB, E = G::E;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     cpx<T>* sm = reinterpret_cast<cpx<T>*>(smem_raw);
@@ -339,10 +352,10 @@ static BigPlan plan_bits(int m) {
 
 template <typename T, int LOG2R, bool INV, bool STRIDED>
 static int launch_pass_t(const BigPass<T>& p, int64_t tiles, int batch, cudaStream_t st) {
-    constexpr size_t smem = big_smem_bytes<T, LOG2R>();
+    constexpr size_t smem = big_smem_bytes<T, LOG2R, STRIDED>();
     auto kern = bigfft_pass_kernel<T, LOG2R, INV, STRIDED>;
     PYFFT_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<dim3((unsigned)tiles, (unsigned)batch), 256, smem, st>>>(p);
+    kern<<<dim3((unsigned)tiles, (unsigned)batch), BigGeom<LOG2R, BigWide<T, STRIDED>::value>::THREADS, smem, st>>>(p);
     PYFFT_LAUNCH_OK("bigfft_pass_kernel");
     return PYFFT_OK;
 }
@@ -364,11 +377,11 @@ static int launch_pass(int log2r, bool inv, BigPass<T> p, int batch, cudaStream_
             twiddle_table_ex(dt, M, int64_t(1) << p.lo_bits, M >> p.lo_bits, &status));
         if (!p.tw_hi) return status;
     }
-    const int TB = 256 / (R / 16);
+    const bool strided = p.B > 1;
+    const int TB = ((strided && sizeof(T) == 4) ? PYFFT_BIG_STRIDED_THREADS : 256) / (R / 16);
     int64_t tiles;
     if (p.out_mode == OUT_NATURAL) tiles = p.N2 * ((p.N1 + TB - 1) / TB);
     else tiles = (p.A * p.B + TB - 1) / TB;
-    const bool strided = p.B > 1;
 #define PYFFT_CASE(N)                                                                             \
     case N:                                                                                       \
         if (inv) return strided ? launch_pass_t<T, N, true, true>(p, tiles, batch, st)            \

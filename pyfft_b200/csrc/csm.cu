@@ -74,15 +74,19 @@ csm_product_kernel(const cpx<T>* __restrict__ X, int64_t K, int nb, int ksplit, 
 // 16-byte shared-memory loads.  A CTA owns FB consecutive bins (25 for 32 channels: 8 warps, one
 // 200-byte run per channel and segment) and a range of segments; the spectra X[c][k][f] are transposed on the fly into
 // [k][bin][c] by 8-byte cp.async copies, in a ring of 3 stages of 4 segments.  Inside a row
-// channel 8a + 2h + p sits at byte h*(NB*16) + a*16 + p*8 and rows are ROW = C*8 + 64 bytes apart,
-// so the 16-byte loads of a quarter warp (one h, all row blocks a of at most two bins) fall into
-// distinct banks.
+// channel 8a + 2h + p sits in 16-byte slot (h*NB + a) ^ csm_swz(bin), half p.
+// XOR applied to the 16-byte slot index (h*NB + block) of a row: neighbouring bins land in
+// opposite 64-byte halves, bins 2 apart in different slots -- the 16-byte loads of a quarter warp
+// (one h, the row blocks of at most two bins) and the 8-byte cp.async writes of consecutive bins
+// both spread over the banks
+__host__ __device__ constexpr int csm_swz(int fb) { return ((fb & 1) << 2) | ((fb >> 1) & 3); }
+
 template <int C> struct CsmTile {
     static constexpr int NB = C / 8, NT = NB * (NB + 1) / 2, KB = 4;
     static constexpr int FB = 256 / NT > 32 ? 32 : 256 / NT;     // bins per CTA: 32 / 25 / 7
     static constexpr int THREADS = (FB * NT + 31) / 32 * 32;     // 96 / 256 / 256 (the last lanes idle)
     static constexpr int MINB = THREADS >= 256 ? 1 : 2;          // 8 x 8 tiles want ~250 registers
-    static constexpr int ROW = C * 8 + 64;               // bytes per (segment, bin) row; ROW mod 128 == 64
+    static constexpr int ROW = C * 8;                    // bytes per (segment, bin) row, 16-byte slots XOR-swizzled by the bin
     static constexpr int STAGE = KB * FB * ROW;
     static constexpr int NSTAGE = 3;
     static constexpr int SMEM = NSTAGE * STAGE;
@@ -106,6 +110,8 @@ csm_tile_kernel(const cpx<float>* __restrict__ X, int64_t K, int nb, int ksplit,
     const int64_t k1 = k0 + kper < K ? k0 + kper : K;
     if (k0 >= k1) return;
     const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(csm_smem);
+    const int swz = csm_swz(fb);
+    const int shi = swz & ~(NB - 1) & (4 * NB - 1), alo = a ^ (swz & (NB - 1)), blo = b ^ (swz & (NB - 1));
 
     float ar[8][8], ai[8][8];
 #pragma unroll
@@ -124,7 +130,7 @@ csm_tile_kernel(const cpx<float>* __restrict__ X, int64_t K, int nb, int ksplit,
         const int c = e / FB, fbb = e - c * FB;
         const bool ok = e < C * FB && f0 + fbb < nb;
         goff[i] = ok ? (uint32_t)((int64_t)c * K * nb + f0 + fbb) : 0u;
-        soff[i] = (uint32_t)(fbb * ROW + ((c >> 1) & 3) * (NB * 16) + (c >> 3) * 16 + (c & 1) * 8);   // [h][block][2 channels]
+        soff[i] = (uint32_t)(fbb * ROW + 16 * ((((c >> 1) & 3) * NB + (c >> 3)) ^ csm_swz(fbb)) + (c & 1) * 8);
         if (e < C * FB) okmask |= (ok ? 1u : 0u) << (2 * i) | 2u << (2 * i);   // bit 2i: copy, bit 2i+1: slot exists
     }
     auto issue = [&](int stage, int64_t kb) {
@@ -166,13 +172,12 @@ csm_tile_kernel(const cpx<float>* __restrict__ X, int64_t K, int nb, int ksplit,
         const unsigned char* row = csm_smem + stage * Tl::STAGE + fb * ROW;
 #pragma unroll
         for (int q = 0; q < KB; ++q) {
-            const unsigned char* pi = row + q * (FB * ROW) + a * 16;
-            const unsigned char* pj = row + q * (FB * ROW) + b * 16;
+            const unsigned char* pq = row + q * (FB * ROW);
             float4 xi[4], xj[4];
 #pragma unroll
             for (int h = 0; h < 4; ++h) {
-                xi[h] = *reinterpret_cast<const float4*>(pi + h * (NB * 16));
-                xj[h] = *reinterpret_cast<const float4*>(pj + h * (NB * 16));
+                xi[h] = *reinterpret_cast<const float4*>(pq + (((h * NB) ^ shi) | alo) * 16);
+                xj[h] = *reinterpret_cast<const float4*>(pq + (((h * NB) ^ shi) | blo) * 16);
             }
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
