@@ -13,6 +13,6 @@ from .fft_analysis import (fft_pwelch, fftanal, cross_spectral_matrix, fftinfosc
 
 from .spectrogram import stft, specgram  # noqa: F401,E402
 from .hilbert import hilbert, hilbert_1d  # noqa: F401,E402
-from .ccf import ccf, ccf_sh, fftcorr, cross_correlation_fft  # noqa: F401,E402
+from .ccf import ccf, ccf_sh, fftcorr, fftconv, convolve_fft, cross_correlation_fft  # noqa: F401,E402
 
 __version__ = "0.1.0"

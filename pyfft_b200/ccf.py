@@ -81,6 +81,35 @@ def fftcorr(x, y, precision=None, device=None):
     return r[0].cpu().numpy().astype(np.complex128)
 
 
+def fftconv(x, y, precision=None, device=None):
+    """Circular FFT convolution 'x*y <==> XY' of two equal power-of-two length sequences
+    (ccf.py:227-235): ifft(fft(x) * fft(y))."""
+    dev = engine.require_cuda(device)
+    x = np.asarray(x)
+    y = np.asarray(y)
+    prec = engine.resolve_precision(precision, x, y)
+    if x.shape != y.shape or x.ndim != 1:
+        raise ValueError("fftconv expects two 1-D sequences of equal length")
+    ct = np.complex128 if prec == "fp64" else np.complex64
+    zx = engine.to_device(x.astype(ct), prec, dev, True)
+    zy = engine.to_device(y.astype(ct), prec, dev, True)
+    X = engine.fft_c2c(zx[None, :], prec)
+    Y = engine.fft_c2c(zy[None, :], prec)
+    r = engine.fft_c2c(X * Y, prec, inverse=True)
+    return r[0].cpu().numpy().astype(np.complex128)
+
+
+def convolve_fft(a, b, mode="valid", precision=None, device=None):
+    """numpy.convolve(a, b, mode) through the FFT -- what ccf.py:267-283 intends (its padding
+    helper divides by a float, ccf.py:264, and cannot run).  Equal-length real inputs; the
+    convolution is the correlation with the second operand reversed (ccf.py:303 states the same
+    identity the other way round)."""
+    b = np.asarray(b)
+    if b.ndim != 1:
+        raise ValueError("Can only vectorize vectors")                  # ccf.py:258-259
+    return cross_correlation_fft(a, b[::-1].copy(), mode=mode, precision=precision, device=device)
+
+
 def cross_correlation_fft(a, b, mode="valid", precision=None, device=None):
     """numpy.correlate(a, b, mode) through the FFT -- what ccf.py:285-303 intends ("similar to
     numpy.correlate, but faster"; the reference's own padding helper divides by a float,

@@ -106,6 +106,10 @@ def test_fftcorr_and_cross_correlation_fft(cuda_device):
     assert relerr(fftcorr(x, y), ref) <= 1e-12
     for mode in ("full", "same", "valid"):
         assert relerr(cross_correlation_fft(x, y, mode=mode), np.correlate(x, y, mode)) <= 1e-12
+    from pyfft_b200 import convolve_fft, fftconv
+    assert relerr(fftconv(x, y), np.fft.ifft(np.fft.fft(x) * np.fft.fft(y))) <= 1e-12      # ccf.py:227-235
+    for mode in ("full", "same", "valid"):
+        assert relerr(convolve_fft(x, y, mode=mode), np.convolve(x, y, mode)) <= 1e-12
 
 
 @pytest.mark.parametrize("precision", ["fp64", "fp32"])
