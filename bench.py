@@ -347,7 +347,12 @@ def run_ours(args):
                         "whole_step_frac": alg_bytes / (ms_step / 1e3) / 1e9 / peak,
                         "two_pass_step_ms": ms_two, "cuda_core_kernel_ms": ms_k1_cuda,
                         "vs_two_pass_cuda_core_max_rel": dev_fused, "vs_two_pass_cuda_core_coherence_abs": dev_coh},
-           "cpu_baseline": cpu, "e2e": e2e, "clocks": clk, "gpu_launches": (6 if world == 1 else 7) * args.steps}
+           "cpu_baseline": cpu, "e2e": e2e, "clocks": clk,
+           # kernels of this library per step; sharded: + rereference + the NVLink peer reduction (csrc/peer.cu)
+           "gpu_launches": (6 if world == 1 else (8 if wp._peer else 7)) * args.steps}
+    if world > 1:
+        out["config"]["collective"] = ("one kernel over NVLink peer memory (pyfft_peer_allreduce), 131 KB"
+                                       if wp._peer else "one NCCL all-reduce, 131 KB")
     print(json.dumps(out), flush=True)
     if group is not None:
         dist.destroy_process_group()

@@ -332,6 +332,24 @@ int pyfft_csm_accumulate(int dtype, const void* x, int64_t ch_stride, int32_t nc
                          const void* window, const double* coef, double* G,
                          void* workspace, int64_t workspace_bytes, void* stream);
 
+/* ------------------------------------------------------------------------- *
+ * The exchange step of the sharded path over NVLink peer memory
+ * replaces: the single all-reduce of the packed partial sums acc | lin | stats
+ * (the sum over shards of the segment sums of fft_analysis.py:444-446).
+ * Every rank owns a buffer of pyfft_peer_buffer_bytes(n, world) bytes, zero-filled
+ * once, with the SAME layout on every GPU (double staging[2][n] | uint32 flags[world])
+ * and peer-mapped by the caller; peer_base is a DEVICE array of `world` 64-bit
+ * addresses: where rank r's buffer is mapped in THIS process.  One call per step on
+ * every rank with the same epoch = 1, 2, 3, ...: state[0..n) becomes the sum over
+ * ranks, formed in rank order (bit-identical on all ranks).  ticket: one zeroed
+ * uint32 in device memory; status_flag: device int, set to 1 if a peer did not show
+ * up within the (bounded) wait -- the result is then undefined and the caller must
+ * fall back to another collective.
+ * ------------------------------------------------------------------------- */
+int64_t pyfft_peer_buffer_bytes(int64_t n, int32_t world);
+int pyfft_peer_allreduce(double* state, int64_t n, const int64_t* peer_base, int32_t rank, int32_t world,
+                         uint32_t epoch, uint32_t* ticket, int32_t* status_flag, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

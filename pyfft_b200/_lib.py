@@ -71,6 +71,8 @@ _PROTOS = {
     "pyfft_csm_workspace_bytes": (_i64, [C.c_int, _pseg, _i32]),
     "pyfft_csm_accumulate": (C.c_int, [C.c_int, _vp, _i64, _i32, _pmap, _pseg, _vp, _vp, _vp, _vp,
                                        _i64, _vp]),
+    "pyfft_peer_buffer_bytes": (_i64, [_i64, _i32]),
+    "pyfft_peer_allreduce": (C.c_int, [_vp, _i64, _vp, _i32, _i32, C.c_uint32, _vp, _vp, _vp]),
 }
 
 EXPORTS = tuple(_PROTOS)

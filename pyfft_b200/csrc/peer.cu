@@ -1,0 +1,120 @@
+// The one exchange step of the sharded Welch / cross-spectral-matrix path:
+// the sum over GPUs of the packed partial sums acc | lin | stats (131 KB for config 2), done by ONE
+// kernel over NVLink peer memory instead of a library collective.
+//
+// Reference lines replaced: none one-to-one -- the reference is single-process; this is the sum of
+// the per-shard segment sums of fft_analysis.py:444-446 (mean over segments).
+//
+// Every rank owns a symmetric buffer (same layout on every GPU, peer-mapped by the host:
+// torch.distributed._symmetric_memory):  double staging[2][n] | uint32 flags[world].
+// One call = one epoch:
+//   1. every CTA copies its slice of the local state into staging[epoch & 1];
+//   2. the last CTA to finish (ticket) publishes: st.release.sys of the epoch into flags[rank] of
+//      EVERY peer;
+//   3. every CTA waits until its own flags[] hold the epoch for all ranks (ld.acquire.sys), then
+//      sums its slice over the peers' staging buffers in rank order 0..world-1 -- the same order
+//      on every GPU, so all ranks end with bit-identical sums -- and writes the local state.
+// Two staging buffers are enough: a rank can be at most one epoch ahead of a peer (to publish
+// epoch e+1 it must have seen the peer's flag of epoch e, which the peer sets after it finished
+// reading epoch e-1), so the buffer a slow peer still reads is never the one being written.
+// All CTAs spin, so the grid is kept far below the SM count (co-residency); waits are bounded and
+// raise *status instead of hanging the GPU.
+#include "common.cuh"
+
+namespace pyfft {
+
+constexpr int PEER_CTAS = 96;      // all CTAs spin on the peers' flags: keep the grid co-resident (148 SMs)
+constexpr int PEER_THREADS = 256;
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ double ld_relaxed_sys(const double* p) {
+    double v;
+    asm volatile("ld.relaxed.sys.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
+    return v;
+}
+
+__global__ void __launch_bounds__(PEER_THREADS)
+peer_allreduce_kernel(double* __restrict__ state, int64_t n, const int64_t* __restrict__ peer_base, int rank, int world,
+                      uint32_t epoch, unsigned int* __restrict__ ticket, int* __restrict__ status) {
+    __shared__ int s_last, s_ok;
+    const int64_t per = (n + gridDim.x - 1) / gridDim.x;
+    const int64_t i0 = (int64_t)blockIdx.x * per;
+    const int64_t i1 = i0 + per < n ? i0 + per : n;
+    const int64_t stage = (int64_t)(epoch & 1u) * n;
+    double* mine = reinterpret_cast<double*>(peer_base[rank]) + stage;
+    for (int64_t i = i0 + threadIdx.x; i < i1; i += PEER_THREADS) mine[i] = state[i];
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        s_ok = 1;
+        const unsigned int t = atomicAdd(ticket, 1u);
+        s_last = (t == gridDim.x - 1) ? 1 : 0;
+        if (s_last) *ticket = 0u;                       // every CTA has taken its ticket
+    }
+    __syncthreads();
+    if (s_last && threadIdx.x < world) {
+        __threadfence_system();
+        uint32_t* f = reinterpret_cast<uint32_t*>(reinterpret_cast<double*>(peer_base[threadIdx.x]) + 2 * n);
+        st_release_sys(f + rank, epoch);
+    }
+    if (threadIdx.x < world) {
+        const uint32_t* f = reinterpret_cast<const uint32_t*>(reinterpret_cast<const double*>(peer_base[rank]) + 2 * n);
+        bool ok = false;
+        for (uint32_t it = 0; it < (1u << 24); ++it) {
+            if ((int32_t)(ld_acquire_sys(f + threadIdx.x) - epoch) >= 0) { ok = true; break; }
+            __nanosleep(40);
+        }
+        if (!ok) { s_ok = 0; atomicExch(status, 1); }
+    }
+    __syncthreads();
+    if (!s_ok) return;
+    for (int64_t i = i0 + threadIdx.x; i < i1; i += PEER_THREADS) {
+        double s = 0.0;
+        for (int r0 = 0; r0 < world; r0 += 8) {         // eight NVLink loads in flight, summed in rank order
+            double v[8];
+#pragma unroll
+            for (int q = 0; q < 8; ++q)
+                v[q] = r0 + q < world ? ld_relaxed_sys(reinterpret_cast<const double*>(peer_base[r0 + q]) + stage + i) : 0.0;
+#pragma unroll
+            for (int q = 0; q < 8; ++q)
+                if (r0 + q < world) s += v[q];
+        }
+        state[i] = s;
+    }
+}
+
+}  // namespace pyfft
+
+using namespace pyfft;
+
+extern "C" {
+
+int64_t pyfft_peer_buffer_bytes(int64_t n, int32_t world) {
+    if (n <= 0 || world <= 0) return fail(PYFFT_EINVAL, "peer_buffer_bytes: bad arguments");
+    return 2 * n * (int64_t)sizeof(double) + 4 * (int64_t)world + 64;
+}
+
+int pyfft_peer_allreduce(double* state, int64_t n, const int64_t* peer_base, int32_t rank, int32_t world,
+                         uint32_t epoch, uint32_t* ticket, int32_t* status_flag, void* stream) {
+    if (!state || !peer_base || !ticket || !status_flag || n <= 0)
+        return fail(PYFFT_EINVAL, "peer_allreduce: NULL pointer or n <= 0");
+    if (world < 1 || world > PEER_THREADS || rank < 0 || rank >= world)
+        return fail(PYFFT_EINVAL, "peer_allreduce: bad rank/world %d/%d", rank, world);
+    if (epoch == 0) return fail(PYFFT_EINVAL, "peer_allreduce: epochs start at 1 (flags are zero-initialised)");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    int ctas = (int)((n + PEER_THREADS - 1) / PEER_THREADS);
+    if (ctas > PEER_CTAS) ctas = PEER_CTAS;
+    peer_allreduce_kernel<<<ctas, PEER_THREADS, 0, st>>>(state, n, peer_base, rank, world, epoch, ticket,
+                                                         reinterpret_cast<int*>(status_flag));
+    PYFFT_LAUNCH_OK("peer_allreduce_kernel");
+    return PYFFT_OK;
+}
+
+}  // extern "C"

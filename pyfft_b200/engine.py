@@ -6,6 +6,7 @@ current torch CUDA stream; nothing here synchronises except explicit ``.cpu()``
 conversions done by the callers.
 """
 import ctypes as C
+import os
 
 import numpy as np
 import torch
@@ -79,6 +80,68 @@ def channels_first(y, n):
     return y.contiguous()
 
 
+class PeerReducer:
+    """Sum over the ranks of a process group of one packed double buffer, by ONE kernel over
+    NVLink peer memory (csrc/peer.cu) instead of a library collective.  The symmetric buffer
+    (two staging copies + flags) comes from torch.distributed._symmetric_memory, which peer-maps
+    it into every rank of the group; PYFFT_PEER_REDUCE=0 disables it."""
+
+    _cache = {}
+
+    def __init__(self, n, device, group):
+        import torch.distributed._symmetric_memory as symm
+        dist = torch.distributed
+        group = dist.group.WORLD if group is None else group
+        self.n = int(n)
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        nbytes = check(lib.pyfft_peer_buffer_bytes(self.n, self.world))
+        self.buf = symm.empty((nbytes + 7) // 8, dtype=torch.float64, device=device)
+        self.buf.zero_()
+        self.hdl = symm.rendezvous(self.buf, group.group_name)
+        self.peer_base = torch.tensor([int(p) for p in self.hdl.buffer_ptrs], dtype=torch.int64, device=device)
+        self.ticket = torch.zeros(1, dtype=torch.int32, device=device)
+        self.status = torch.zeros(1, dtype=torch.int32, device=device)
+        self.epoch = 0
+        torch.cuda.synchronize(device)
+        dist.barrier(group=group)                      # every rank's buffer is zeroed before the first epoch
+
+    @classmethod
+    def create(cls, n, device, group):
+        """-> PeerReducer, or False when peer memory is not available (single process, CPU group,
+        no peer access): the caller keeps using NCCL."""
+        if os.environ.get("PYFFT_PEER_REDUCE", "1") == "0":
+            return False
+        dist = torch.distributed
+        if not (dist.is_available() and dist.is_initialized()):
+            return False
+        g = dist.group.WORLD if group is None else group
+        if dist.get_world_size(g) < 2 or dist.get_backend(g) != "nccl":
+            return False
+        key = (int(n), str(device), g.group_name)
+        if key not in cls._cache:
+            try:
+                ok = cls(n, device, g)
+            except Exception as exc:                   # no peer mapping on this machine
+                import warnings
+                warnings.warn("pyfft_b200: NVLink peer reduction unavailable (%s); using NCCL" % (exc,))
+                ok = False
+            # all ranks must take the same route
+            flag = torch.tensor([1 if ok else 0], dtype=torch.int32, device=device)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=g)
+            cls._cache[key] = ok if int(flag.item()) == 1 else False
+        return cls._cache[key]
+
+    def all_reduce(self, state):
+        self.epoch += 1
+        check(lib.pyfft_peer_allreduce(_ptr(state), self.n, _ptr(self.peer_base), self.rank, self.world,
+                                       self.epoch & 0xFFFFFFFF or 1, _ptr(self.ticket), _ptr(self.status), _stream()))
+
+    def check_status(self):
+        """Synchronising check of the bounded waits (tests / debugging)."""
+        if int(self.status.item()) != 0:
+            raise RuntimeError("pyfft_b200: a peer did not reach the NVLink reduction in time")
+
+
 class WelchPlan(object):
     """Streaming Welch accumulator for one x channel against nch y channels.
 
@@ -100,6 +163,7 @@ class WelchPlan(object):
         # acc | lin | stats share one buffer: one fill resets them, one all-reduce adds shards
         self.nlin = self.nfft // 16
         n_acc, n_lin, n_st = self.nch * 4 * self.nbin, self.nch * 4 * self.nlin, 2 * (self.nch + 1)
+        self._peer = None                              # PeerReducer, False (unavailable) or None (not tried)
         self.state = torch.zeros(n_acc + n_lin + n_st, dtype=torch.float64, device=self.device)
         self.acc = self.state[:n_acc].view(self.nch, 4, self.nbin)
         self.lin = self.state[n_acc:n_acc + n_lin].view(self.nch, 4, self.nlin)
@@ -226,8 +290,15 @@ class WelchPlan(object):
         self.est = self._zero_est
 
     def all_reduce_state(self, group=None):
-        """The one collective of the sharded fused-mean route: acc | lin | stats in one buffer."""
-        torch.distributed.all_reduce(self.state, group=group)
+        """The one collective of the sharded fused-mean route: acc | lin | stats in one buffer.
+        Over NVLink peer memory (PeerReducer) when the group's GPUs can map each other's memory,
+        else NCCL."""
+        if self._peer is None:
+            self._peer = PeerReducer.create(self.state.numel(), self.device, group)
+        if self._peer:
+            self._peer.all_reduce(self.state)
+        else:
+            torch.distributed.all_reduce(self.state, group=group)
 
     # -- accumulate --------------------------------------------------------- #
     def accumulate(self, x, y, rmap, seg_first, seg_count):

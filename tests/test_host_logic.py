@@ -133,3 +133,11 @@ def test_fftinfosc_container():
     assert "Pxx" in d and not any(k.startswith("_") for k in d)
     s = FA.Struct(info)
     assert np.array_equal(s.Pxx, np.ones(3))
+
+
+def test_peer_reducer_needs_an_nccl_group():
+    """The NVLink peer reduction is only taken inside an initialised NCCL group of >= 2 ranks;
+    everywhere else create() answers False and the caller keeps its library collective."""
+    import torch
+    from pyfft_b200 import engine
+    assert engine.PeerReducer.create(1024, torch.device("cpu"), None) is False
