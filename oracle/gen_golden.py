@@ -157,5 +157,32 @@ def main():
     print("golden fixtures in", OUT)
 
 
+def gen_fft_deriv():
+    """fft_analysis.fft_deriv (fft_analysis.py:1453-1588) on the recipes of its own self-test
+    (test_fft_deriv, :1591-1650: smooth profiles on a uniform grid), default arguments and the
+    unmodified-wavenumber / windowed variants.  Own RNG: does not disturb the other fixtures."""
+    m = ref_shim.load_reference()
+    fa = m["fft_analysis"]
+    rng = np.random.default_rng(1453)
+    d = {}
+    for n in (256, 4096):
+        xx = np.linspace(-1.0, 1.3, n)
+        sig = np.exp(-0.5 * (xx / 0.3) ** 2) + 0.2 * np.sin(2 * np.pi * 3 * xx) + 0.01 * rng.standard_normal(n)
+        d["x_%d" % n] = xx
+        d["s_%d" % n] = sig
+        for tag, kw in (("def", {}), ("naive", dict(modified=False)), ("ham", dict(window=np.hamming)),
+                        ("mean", dict(detrend=fa.detrend_mean))):
+            ds, xo = fa.fft_deriv(sig.copy(), xx.copy(), **kw)
+            d["d_%s_%d" % (tag, n)] = ds
+            d["xo_%s_%d" % (tag, n)] = xo
+    ds, xo = fa.fft_deriv(d["s_256"].copy())                       # xx = None: index grid
+    d["d_noxx_256"], d["xo_noxx_256"] = ds, xo
+    np.savez_compressed(os.path.join(OUT, "fft_deriv.npz"), **d)
+    print("wrote fft_deriv")
+
+
 if __name__ == "__main__":
-    main()
+    if len(sys.argv) > 1 and sys.argv[1] == "fft_deriv":
+        gen_fft_deriv()
+    else:
+        main()

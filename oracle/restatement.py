@@ -539,3 +539,53 @@ def cross_spectral_matrix(tvec, sig, Navr, windowoverlap=0.5,
     wgt = _one_sided_weights(nw, nnyq)
     G *= (wgt / (S1 ** 2) / ENBW / K)[:, None, None]
     return np.fft.fftfreq(nw, 1.0 / fs)[:nnyq], G
+
+
+# --------------------------------------------------------------------------- #
+# fft_analysis.py:1419-1588 (rescale / unscale / fft_deriv), SURVEY 8(f) rank 3
+# --------------------------------------------------------------------------- #
+
+def fft_deriv(sig, xx=None, lowpass=True, Fs_new=None, modified=True, detrend=None, window=None):
+    """Spectral derivative dsig/dxx on a uniform grid: ifft(wavenumber * fft(sig)) with the
+    modified wavenumber i sin(k dx)/dx (fft_analysis.py:1453-1588).  The pre-filter branch
+    (:1493-1511) only acts when Fs_new < Fs, i.e. never with the defaults (lowpass = Nyquist,
+    Fs_new = min(5 lowpass, Fs) = Fs); it belongs to filters.py (out of scope) and is refused."""
+    sig = np.asarray(sig, float)
+    if xx is None:
+        xx = 1.0 * np.arange(len(sig))                                    # :1484-1487
+    xx = np.asarray(xx, float)
+    if lowpass:                                                           # :1493-1511
+        dxo = xx[1] - xx[0]
+        lp = 0.5 / dxo if lowpass is True else float(lowpass)
+        Fs = 1.0 / dxo
+        fsn = min(5.0 * lp, Fs) if Fs_new is None else Fs_new
+        if fsn < Fs:
+            raise NotImplementedError("fft_deriv: the down-sampling pre-filter is filters.py territory")
+    # rescale (:1419-1437): y to [0, 1], x by its span with the fixed offset -1e-4
+    slope = np.nanmax(sig) - np.nanmin(sig)
+    offset = np.nanmin(sig)
+    if slope == 0:
+        slope = 1.0
+    s = (sig - offset) / slope
+    xslope = np.nanmax(xx) - np.nanmin(xx)
+    xoffset = -1e-4
+    if xslope == 0:
+        xslope = 1.0
+    x = (xx - xoffset) / xslope
+    if detrend is not None:
+        s = detrend(s)                                                    # :1519
+    N = len(x)
+    dx = x[1] - x[0]
+    L = N * dx
+    k = 2.0 * np.pi * np.fft.fftfreq(N, d=dx / L)                         # :1529-1530
+    wavenumber = (1.0j * np.sin(k * dx) / dx if modified else 1.0j * k) / L   # :1531-1540
+    win = np.ones_like(s) if window is None else window(N)                # :1543-1547
+    s = win * s
+    ds0 = (s[1] - s[0]) / (x[1] - x[0])                                   # :1551-1552
+    ds1 = (s[-1] - s[-2]) / (x[-1] - x[-2])
+    d = np.real(np.fft.ifft(wavenumber * np.fft.fft(s, n=N), n=N))        # :1553
+    d = d / win                                                           # :1556
+    d[0] = ds0                                                            # :1559-1560
+    d[-1] = ds1
+    # unscale (:1439-1451)
+    return d * slope / xslope, x * xslope + xoffset

@@ -70,7 +70,7 @@ csm_product_kernel(const cpx<T>* __restrict__ X, int64_t K, int nb, int ksplit, 
 
 // Register-tiled product for fp32 spectra and nch = 16 / 32 / 64: a thread owns an 8 x 8 block
 // (rows 8a.., columns 8b.., b >= a: G is Hermitian, the lower triangle is mirrored when the sums
-// are flushed) of one bin's matrix = 128 fp32 accumulators and 256 FFMA per segment for 8
+// are flushed -- also inside the diagonal blocks, so G is Hermitian bit for bit with a real diagonal) of one bin's matrix = 128 fp32 accumulators and 256 FFMA per segment for 8
 // 16-byte shared-memory loads.  A CTA owns FB consecutive bins (25 for 32 channels: 8 warps, one
 // 200-byte run per channel and segment) and a range of segments; the spectra X[c][k][f] are transposed on the fly into
 // [k][bin][c] by 8-byte cp.async copies, in a ring of 3 stages of 4 segments.  Inside a row
@@ -204,10 +204,12 @@ csm_tile_kernel(const cpx<float>* __restrict__ X, int64_t K, int nb, int ksplit,
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             const int gi = 8 * a + i, gj = 8 * b + j;
+            if (gj < gi) continue;                      // diagonal blocks: upper triangle only, mirrored below
             double* g = G + (((int64_t)f * C + gi) * C + gj) * 2;
             atomicAdd(g, (double)ar[i][j]);
+            if (gi == gj) continue;                     // G_ii is real: |X_i|^2
             atomicAdd(g + 1, (double)ai[i][j]);
-            if (a != b) {
+            {
                 double* gt = G + (((int64_t)f * C + gj) * C + gi) * 2;
                 atomicAdd(gt, (double)ar[i][j]);
                 atomicAdd(gt + 1, -(double)ai[i][j]);

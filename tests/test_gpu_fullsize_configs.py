@@ -77,7 +77,7 @@ def test_config4_full_size_hilbert_and_ccf(cuda_device):
     zb, _ = engine.hilbert(torch.stack([base, base]), "fp32", want_analytic=True, want_envelope=False)
     inner = slice(n // 64, n - n // 64)
     assert float((zb[0].abs()[inner] - amp[inner]).abs().max()) <= 2e-3
-    assert torch.equal(zb[0], zb[1])                            # both halves of a pair get the same answer
+    assert float((zb[0] - zb[1]).abs().max()) <= 2e-5           # both halves of a pair: H(a) = Im A - b, H(b) = a - Re A
     del zb, amp, base
     # no power at negative frequencies: independent FFT of one analytic record
     Z = torch.fft.fft(z[3].to(torch.complex128))

@@ -140,3 +140,18 @@ def test_cross_spectral_matrix_rows_are_fft_pwelch_calls():
         o = R.fft_pwelch(t, s[:, i], s, Navr=15, windowoverlap=0.5, windowfunction="Hanning")
         assert relerr(G[:, i, :], o["Pxy"]) < 1e-12
     assert np.allclose(G, np.conj(np.transpose(G, (0, 2, 1))))     # Hermitian in (i, j)
+
+
+def test_fft_deriv_restatement_matches_reference():
+    """the spectral derivative (fft_analysis.py:1453-1588) against the
+    reference's own outputs (oracle/gen_golden.py fft_deriv)."""
+    g = load_golden("fft_deriv")
+    for n in (256, 4096):
+        x, s = g["x_%d" % n], g["s_%d" % n]
+        for tag, kw in (("def", {}), ("naive", dict(modified=False)), ("ham", dict(window=np.hamming)),
+                        ("mean", dict(detrend=lambda v: v - v.mean()))):
+            d, xo = R.fft_deriv(s, x, **kw)
+            assert relerr(d, g["d_%s_%d" % (tag, n)]) <= 1e-12, (tag, n)
+            assert relerr(xo, g["xo_%s_%d" % (tag, n)]) <= 1e-14
+    d, xo = R.fft_deriv(g["s_256"])
+    assert relerr(d, g["d_noxx_256"]) <= 1e-12 and relerr(xo, g["xo_noxx_256"]) <= 1e-14
