@@ -311,6 +311,14 @@ int pyfft_xcorr(int dtype, const void* x, int64_t x_stride, const void* y, int64
                 int64_t n, int32_t pairs, int32_t normalise, void* out,
                 void* workspace, int64_t workspace_bytes, void* stream);
 
+/* Spectral derivative of `batch` real records on one uniform grid
+ * replaces: sig = real(ifft(wavenumber * fft(sig))), fft_analysis.py:1528-1553 (fft_deriv), with
+ * wavenumber = i sin(k dx)/dx / L (modified != 0) or i k / L, k = 2 pi fftfreq(n, d = dx/L), L = n dx.
+ * n a power of two (2^4 .. 2^27); in/out real [batch][n] of `dtype`; two records share one complex
+ * transform; workspace: pyfft_bigfft_workspace_bytes(dtype, n, (batch + 1) / 2). */
+int pyfft_spectral_derivative(int dtype, const void* in, int64_t n, int32_t batch, int32_t modified, double dx,
+                              void* out, void* workspace, int64_t workspace_bytes, void* stream);
+
 /* Batched complex FFT of power-of-two length 2^4 .. 2^27 (forward: e^{-2 pi i nk/N}
  * unnormalised; inverse: 1/N), the numpy.fft.fft/ifft contract used at every
  * reference call site (fft_analysis.py:2096-2116).  in/out complex of `dtype`,

@@ -68,6 +68,7 @@ _PROTOS = {
     "pyfft_hilbert": (C.c_int, [C.c_int, _vp, _i64, _i32, _vp, _vp, _vp, _i64, _vp]),
     "pyfft_xcorr": (C.c_int, [C.c_int, _vp, _i64, _vp, _i64, _i64, _i32, _i32, _vp, _vp, _i64, _vp]),
     "pyfft_fft_c2c": (C.c_int, [C.c_int, _vp, _vp, _i64, _i32, _i32, _vp, _i64, _vp]),
+    "pyfft_spectral_derivative": (C.c_int, [C.c_int, _vp, _i64, _i32, _i32, _dbl, _vp, _vp, _i64, _vp]),
     "pyfft_csm_workspace_bytes": (_i64, [C.c_int, _pseg, _i32]),
     "pyfft_csm_accumulate": (C.c_int, [C.c_int, _vp, _i64, _i32, _pmap, _pseg, _vp, _vp, _vp, _vp,
                                        _i64, _vp]),

@@ -31,7 +31,7 @@ namespace pyfft {
 
 enum { IN_CPLX = 0, IN_REAL = 1, IN_REAL2 = 2 };
 enum { OUT_CPLX = 0, OUT_MASK = 1, OUT_MULCONJ = 2, OUT_NATURAL = 3, OUT_HILBERT = 4, OUT_XCORR = 5,
-       OUT_HILBERT2 = 6, OUT_XCORR2 = 7 };
+       OUT_HILBERT2 = 6, OUT_XCORR2 = 7, OUT_DERIV = 8, OUT_REAL2 = 9 };
 enum { TW_NONE = 0, TW_POST = 1, TW_PRE = 2 };
 
 template <typename T> struct BigPass {
@@ -55,6 +55,8 @@ template <typename T> struct BigPass {
     const double* bscale;                     // OUT_XCORR: per-batch factor (or null)
     int64_t nsig;                             // OUT_XCORR: record length n (output has 2n-1 lags)
     int nreal;                                // IN_REAL2 / OUT_*2: number of real records (two per transform)
+    double d_dx;                              // OUT_DERIV: grid step (the record spans N * d_dx)
+    int d_modified;                           // OUT_DERIV: modified wavenumber i sin(k dx)/dx instead of i k
 };
 
 template <typename T>
@@ -211,6 +213,32 @@ bigfft_pass_kernel(const BigPass<T> p) {
             const int64_t k = klow + p.N1 * p.N2 * (int64_t)(t + TPS * s);
             const T wgt = (k == 0 || k == nyq) ? T(1) : (k < nyq ? T(2) : T(0));
             dst[base_addr + (int64_t)(t + TPS * s) * p.B] = mk<T>(v[s].x * wgt, v[s].y * wgt);
+        }
+    } else if (p.out_mode == OUT_DERIV) {
+        // fft_analysis.py:1528-1540: k = 2 pi fftfreq(N, d = dx/L) = 2 pi m (m the signed bin index, L = N dx),
+        // wavenumber = i sin(k dx)/dx / L (modified) or i k / L; (re + i im) * (i w) = (-im w, re w)
+        cpx<T>* dst = static_cast<cpx<T>*>(p.out) + bat * p.out_bs;
+        const int64_t klow = (a / p.N2) + p.N1 * (a % p.N2);
+        const double len = (double)p.N * p.d_dx;
+#pragma unroll
+        for (int s = 0; s < 16; ++s) {
+            const int64_t k = klow + p.N1 * p.N2 * (int64_t)(t + TPS * s);
+            const double m = (double)(k < (p.N + 1) / 2 ? k : k - p.N);
+            const double wd = p.d_modified ? sinpi(2.0 * m * p.d_dx) / p.d_dx : 6.283185307179586476925286766559 * m;
+            // the Nyquist bin of a real record is real, so i w X[N/2] only feeds the imaginary part that
+            // the reference drops (:1553 real()): zero it, which also keeps two packed records apart
+            const T w = 2 * k == p.N ? T(0) : (T)(wd / len);
+            dst[base_addr + (int64_t)(t + TPS * s) * p.B] = mk<T>(-v[s].y * w, v[s].x * w);
+        }
+    } else if (p.out_mode == OUT_REAL2) {
+        // real results of two records that shared the transform: Re -> record 2 bat, Im -> 2 bat + 1
+        const bool hb = 2 * bat + 1 < p.nreal;
+        T* da = static_cast<T*>(p.out) + 2 * bat * p.out_bs;
+#pragma unroll
+        for (int s = 0; s < 16; ++s) {
+            const int64_t i = base_addr + (int64_t)(t + TPS * s) * p.B;
+            da[i] = v[s].x * sc;
+            if (hb) da[p.out_bs + i] = v[s].y * sc;
         }
     } else if (p.out_mode == OUT_MULCONJ) {
         cpx<T>* dst = static_cast<cpx<T>*>(p.out) + bat * p.out_bs;
@@ -403,6 +431,7 @@ template <typename T> static BigPass<T> blank_pass(int64_t N) {
     p.tw_mode = TW_NONE; p.tw_lo = p.tw_hi = nullptr; p.lo_bits = 0; p.tw = nullptr;
     p.in_mode = IN_CPLX; p.n_valid = N; p.mean = nullptr;
     p.out_mode = OUT_CPLX; p.scale = 1.0; p.bscale = nullptr; p.nsig = 0; p.nreal = 0;
+    p.d_dx = 1.0; p.d_modified = 0;
     return p;
 }
 
@@ -430,6 +459,7 @@ static int run_dif(int m, bool inv, const BigPass<T>& first, const BigPass<T>& l
         }
         if (i == pl.npass - 1) {
             p.out_mode = last.out_mode; p.scale = last.scale;
+            p.d_dx = last.d_dx; p.d_modified = last.d_modified;
             p.in2 = last.in2; p.in2_bs = last.in2_bs;
             if (last.out) { p.out = last.out; p.out_bs = last.out_bs; }
         }
@@ -513,6 +543,27 @@ static int hilbert_impl(const void* in, int64_t n, int batch, void* analytic, vo
     fin.out_mode = OUT_HILBERT; fin.out = analytic; fin.out_bs = n; fin.out2 = envelope; fin.out2_bs = n;
     fin.scale = 1.0 / (double)n;
     return run_dit_inverse<T>(m, fin, buf, batch, st);
+}
+
+// fft_analysis.py:1553: real(ifft(wavenumber * fft(sig))) for `batch` real records on one grid
+template <typename T>
+static int deriv_impl(const void* in, int64_t n, int batch, int modified, double dx, void* out, void* ws,
+                      int64_t wsb, cudaStream_t st) {
+    int m = 0;
+    int rc = check_pow2(n, 4, 27, &m);
+    if (rc) return rc;
+    const int npair = (batch + 1) / 2;
+    if (!ws || wsb < (int64_t)npair * n * (int64_t)sizeof(cpx<T>))
+        return fail(PYFFT_EINVAL, "spectral_derivative: workspace of %lld bytes needed",
+                    (long long)((int64_t)npair * n * sizeof(cpx<T>)));
+    BigPass<T> first = blank_pass<T>(n), last = blank_pass<T>(n);
+    first.in = in; first.in_bs = n; first.in_mode = IN_REAL2; first.n_valid = n; first.nreal = batch;
+    last.out_mode = OUT_DERIV; last.d_dx = dx; last.d_modified = modified;
+    if ((rc = run_dif<T>(m, false, first, last, ws, npair, st))) return rc;
+    BigPass<T> fin = blank_pass<T>(n);
+    fin.out_mode = OUT_REAL2; fin.out = out; fin.out_bs = n; fin.nreal = batch;
+    fin.scale = 1.0 / (double)n;
+    return run_dit_inverse<T>(m, fin, ws, npair, st);
 }
 
 template <typename T>
@@ -633,6 +684,16 @@ int pyfft_xcorr(int dtype, const void* x, int64_t x_stride, const void* y, int64
         return xcorr_impl<float>(x, x_stride, y, y_stride, n, pairs, normalise, out, workspace, workspace_bytes, st);
     if (dtype == PYFFT_F64)
         return xcorr_impl<double>(x, x_stride, y, y_stride, n, pairs, normalise, out, workspace, workspace_bytes, st);
+    return fail(PYFFT_EINVAL, "unknown dtype %d", dtype);
+}
+
+int pyfft_spectral_derivative(int dtype, const void* in, int64_t n, int32_t batch, int32_t modified, double dx,
+                              void* out, void* workspace, int64_t workspace_bytes, void* stream) {
+    if (!in || !out || batch <= 0) return fail(PYFFT_EINVAL, "spectral_derivative: NULL pointer or batch <= 0");
+    if (!(dx > 0.0)) return fail(PYFFT_EINVAL, "spectral_derivative: the grid step must be positive");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (dtype == PYFFT_F32) return deriv_impl<float>(in, n, batch, modified, dx, out, workspace, workspace_bytes, st);
+    if (dtype == PYFFT_F64) return deriv_impl<double>(in, n, batch, modified, dx, out, workspace, workspace_bytes, st);
     return fail(PYFFT_EINVAL, "unknown dtype %d", dtype);
 }
 

@@ -484,6 +484,19 @@ def xcorr(x, y, precision, normalise=1):
     return out
 
 
+def spectral_derivative(u, dx, precision, modified=True):
+    """u: (batch, n) real device tensor on a uniform grid of step dx, n a power of two ->
+    real(ifft(wavenumber * fft(u))) per record (fft_analysis.py:1528-1553)."""
+    batch, n = u.shape
+    u = u.contiguous()
+    out = torch.empty_like(u)
+    wsb = check(lib.pyfft_bigfft_workspace_bytes(_CODE[precision], n, (batch + 1) // 2))
+    ws = torch.empty(wsb, dtype=torch.uint8, device=u.device)
+    check(lib.pyfft_spectral_derivative(_CODE[precision], _ptr(u), n, batch, 1 if modified else 0, float(dx),
+                                        _ptr(out), _ptr(ws), wsb, _stream()))
+    return out
+
+
 def fft_c2c(z, precision, inverse=False):
     """(batch, n) complex device tensor, n a power of two -> numpy.fft.fft / ifft along the last axis."""
     batch, n = z.shape

@@ -410,6 +410,61 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
     return freq, Pxy, Pxx, Pyy, Cxy, phi_xy, fftinfo
 
 
+def fft_deriv(sig, xx=None, lowpass=True, Fs_new=None, modified=True, detrend=detrend_none, window=None,
+              precision=None, device=None):
+    """Spectral derivative of a profile on a uniform grid (fft_analysis.py:1453-1588): same
+    arguments and return values ``(dsdx, xx)``.  The grid rescaling, the ``detrend`` and ``window``
+    callables and the end-point fix-up run on the host exactly as in the reference
+    (:1513-1519, :1543-1563); its numpy.fft line ``real(ifft(wavenumber * fft(sig)))`` (:1553) is
+    one call into the long-transform kernels (pyfft_spectral_derivative).  The reference's
+    pre-filter (:1493-1511, filters.downsample_efficient) only acts when ``Fs_new < Fs`` -- never
+    with the defaults -- and is refused (NotImplementedError); the length must be a power of
+    two >= 16 (no CPU fallback)."""
+    dev = _eng.require_cuda(device)
+    sig = np.asarray(sig)
+    precision = _eng.resolve_precision(precision, sig)
+    sig = sig.astype(np.float64)
+    if xx is None:
+        xx = 1.0 * np.asarray(range(0, len(sig)))                             # :1484-1487
+    xx = np.asarray(xx, dtype=np.float64)
+    if lowpass:                                                               # :1493-1511
+        dxo = xx[1] - xx[0]
+        lp = 0.5 * 1.0 / dxo if lowpass is True else lowpass
+        Fs = 1.0 / dxo
+        fsn = min(5.0 * lp, Fs) if Fs_new is None else Fs_new
+        if fsn < Fs:
+            raise NotImplementedError("fft_deriv: down-sampling before the derivative (Fs_new < Fs) is "
+                                      "filters.py territory, outside the GPU path")
+    # rescale (:1419-1437)
+    slope = np.nanmax(sig) - np.nanmin(sig)
+    offset = np.nanmin(sig)
+    if slope == 0:
+        slope = 1.0
+    s = (sig.copy() - offset) / slope
+    xslope = np.nanmax(xx) - np.nanmin(xx)
+    xoffset = -1e-4
+    if xslope == 0:
+        xslope = 1.0
+    x = (xx.copy() - xoffset) / xslope
+    s = detrend(s)                                                            # :1519
+    N = len(x)
+    if N < 16 or N & (N - 1):
+        raise NotImplementedError("fft_deriv: %d points -- the GPU path needs a power of two >= 16" % N)
+    dx = x[1] - x[0]
+    win = np.ones_like(s) if window is None else window(N)                    # :1543-1547
+    s = win * s
+    ds0 = (s[1] - s[0]) / (x[1] - x[0])                                       # :1551-1552
+    ds1 = (s[-1] - s[-2]) / (x[-1] - x[-2])
+    with torch.cuda.device(dev):
+        u = _eng.to_device(s[None, :], precision, dev)
+        d = _eng.spectral_derivative(u, dx, precision, modified=bool(modified))[0]
+        d = d.cpu().numpy().astype(np.float64)
+    d /= win                                                                  # :1556
+    d[0] = ds0                                                                # :1559-1560
+    d[-1] = ds1
+    return d * slope / xslope, x * xslope + xoffset                           # unscale, :1439-1451
+
+
 def cross_spectral_matrix(tvec, sig, tbounds=None, Navr=None, windowoverlap=None, windowfunction=None,
                           detrend_style=None, **kwargs):
     """All-pairs cross-power spectral density of a multi-channel record in ONE pass.

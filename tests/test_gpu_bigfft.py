@@ -175,3 +175,45 @@ def test_ccf_two_records_per_transform(cuda_device):
             for c in range(nrec):
                 _, c1 = ccf(xs, ys[c], 1.0e5, precision=prec)
                 assert np.max(np.abs(cm[c] - c1)) <= tol
+
+
+def test_fft_deriv_matches_reference_golden(cuda_device):
+    """fft_deriv (fft_analysis.py:1453-1588) against the reference's own outputs
+    -- default (modified wavenumber), naive wavenumber, Hamming window, mean detrend, index grid."""
+    from pyfft_b200 import detrend_mean, fft_deriv
+    g = load_golden("fft_deriv")
+    for n in (256, 4096):
+        x, s = g["x_%d" % n], g["s_%d" % n]
+        for tag, kw in (("def", {}), ("naive", dict(modified=False)), ("ham", dict(window=np.hamming)),
+                        ("mean", dict(detrend=detrend_mean))):
+            d, xo = fft_deriv(s, x, **kw)
+            assert d.dtype == np.float64 and d.shape == (n,)
+            assert relerr(d, g["d_%s_%d" % (tag, n)]) <= 1e-11, (tag, n)
+            assert relerr(xo, g["xo_%s_%d" % (tag, n)]) <= 1e-14
+        d32, _ = fft_deriv(s.astype(np.float32), x)
+        assert relerr(d32, g["d_def_%d" % n]) <= 5e-3, relerr(d32, g["d_def_%d" % n])
+    d, xo = fft_deriv(g["s_256"])
+    assert relerr(d, g["d_noxx_256"]) <= 1e-11 and relerr(xo, g["xo_noxx_256"]) <= 1e-14
+    with pytest.raises(NotImplementedError):
+        fft_deriv(g["s_256"][:200], g["x_256"][:200])              # not a power of two: no CPU fallback
+    with pytest.raises(NotImplementedError):
+        fft_deriv(g["s_256"], g["x_256"], lowpass=0.01 / (g["x_256"][1] - g["x_256"][0]))   # would down-sample
+
+
+@pytest.mark.parametrize("log2n,batch", [(6, 1), (12, 3), (19, 2), (21, 1)])
+def test_spectral_derivative_kernel_against_numpy(log2n, batch, cuda_device):
+    """pyfft_spectral_derivative (1-, 2- and 3-pass transforms, odd batches: two records per
+    transform) against the numpy line it replaces, fft_analysis.py:1528-1553."""
+    import torch
+    from pyfft_b200 import engine
+    n = 1 << log2n
+    rng = np.random.default_rng(70 + log2n)
+    u = rng.standard_normal((batch, n)).cumsum(axis=1) / np.sqrt(n)
+    dx = 1.0 / n * 0.9
+    L = n * dx
+    k = 2.0 * np.pi * np.fft.fftfreq(n, d=dx / L)
+    for modified in (True, False):
+        wn = (1j * np.sin(k * dx) / dx if modified else 1j * k) / L
+        ref = np.real(np.fft.ifft(wn * np.fft.fft(u, axis=1), axis=1))
+        got = engine.spectral_derivative(torch.from_numpy(u).to(cuda_device), dx, "fp64", modified=modified)
+        assert relerr(got.cpu().numpy(), ref) <= 1e-11, (modified, relerr(got.cpu().numpy(), ref))
