@@ -131,6 +131,21 @@ __device__ __forceinline__ bool mbar_wait_abortable(uint32_t mbar, uint32_t pari
     return false;
 }
 
+// The same for a wait that sits on the critical ring of the pipeline (the MMA-issuing threads and
+// the epilogue's wait for the stage-2 commit): the abort flag is looked at once per 32 polls, so a
+// poll is try_wait + branch and the thread reacts to the phase flip as fast as it can be issued.
+__device__ __forceinline__ bool mbar_wait_hot(uint32_t mbar, uint32_t parity, volatile int* abort_flag) {
+#pragma unroll 1
+    for (uint32_t i = 0; i < (1u << 17); ++i) {
+#pragma unroll 1
+        for (int j = 0; j < 32; ++j)
+            if (mbar_try_wait_nohint(mbar, parity)) return true;
+        if (*abort_flag) return false;
+    }
+    *abort_flag = 1;
+    return false;
+}
+
 // Warp-collective form: lane 0 polls, the result is broadcast (the shuffle also orders the lanes'
 // memory accesses after the acquire).  One poller per warp keeps the barrier unit responsive for
 // the thread that issues the MMAs -- with 32 pollers per warp its own waits took ~300 cycles each.

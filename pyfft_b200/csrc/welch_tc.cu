@@ -219,7 +219,7 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
 #pragma unroll 1                                             // keeps the loop body small for the instruction cache
             for (int sg = 0; sg < SEGS; ++sg) {
                 if (sg == 0) {
-                    if (!mbar_wait_abortable(bar0 + 8 * S2_DONE, (uint32_t)b & 1u, abort_flag)) { live = false; break; }
+                    if (!mbar_wait_hot(bar0 + 8 * S2_DONE, (uint32_t)b & 1u, abort_flag)) { live = false; break; }
                     tc_fence_after();
                     PYFFT_TC_TRACE(10, b)
                 }
@@ -482,9 +482,9 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
             for (int si = 0; si < nseg; ++si) {
                 const int g = si & 1, b = si >> 1, d = si % 3;                // A1 slot, batch, D1 slot
                 if (g == 0) { PYFFT_TC_TRACE(12, b) }
-                bool live = mbar_wait_abortable(bar0 + 8 * (A1_FULL + g), (uint32_t)b & 1u, abort_flag);
+                bool live = mbar_wait_hot(bar0 + 8 * (A1_FULL + g), (uint32_t)b & 1u, abort_flag);
                 if (si >= 3)
-                    live = live && mbar_wait_abortable(bar0 + 8 * (D1_FREE + d), ((uint32_t)(si / 3) & 1u) ^ 1u, abort_flag);
+                    live = live && mbar_wait_hot(bar0 + 8 * (D1_FREE + d), ((uint32_t)(si / 3) & 1u) ^ 1u, abort_flag);
                 if (!live) break;
                 tc_fence_after();
                 if (g == 0) { PYFFT_TC_TRACE(13, b) }
@@ -508,8 +508,8 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
                 PYFFT_TC_TRACE(14, bb)
                 const uint32_t b2 = sw128_desc_lo(sm_addr + OFF_B2 + s * B2_BYTES);
                 // the operand is ready long before the epilogue has drained the single D2 slot
-                bool live = mbar_wait_abortable(bar0 + 8 * (B2_FULL + s), (uint32_t)(bb >> 1) & 1u, abort_flag);
-                if (bb >= 1) live = live && mbar_wait_abortable(bar0 + 8 * D2_FREE, (uint32_t)(bb - 1) & 1u, abort_flag);
+                bool live = mbar_wait_hot(bar0 + 8 * (B2_FULL + s), (uint32_t)(bb >> 1) & 1u, abort_flag);
+                if (bb >= 1) live = live && mbar_wait_hot(bar0 + 8 * D2_FREE, (uint32_t)(bb - 1) & 1u, abort_flag);
                 if (!live) break;
                 tc_fence_after();
                 PYFFT_TC_TRACE(15, bb)
