@@ -319,11 +319,11 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
             const int s0 = 2 * b, s1 = 2 * b + 1;                            // segment indices; D1 slot = index % 3
             const int d0 = s0 % 3, d1 = s1 % 3;
             // the stage-2 MMAs of batch b-2 have finished reading this B2 slot
-            if (b >= 2 && !mbar_wait_abortable(bar0 + 8 * (B2_FREE + s), ((uint32_t)(b >> 1) & 1u) ^ 1u, abort_flag)) break;
+            if (b >= 2 && !mbar_wait_hot(bar0 + 8 * (B2_FREE + s), ((uint32_t)(b >> 1) & 1u) ^ 1u, abort_flag)) break;
             // stage 1 of the batch's second segment done implies the first one (same issuing thread,
             // the tensor pipe completes in order)
             PYFFT_TC_TRACE(7, b)
-            if (!mbar_wait_abortable(bar0 + 8 * (S1_DONE + d1), (uint32_t)(s1 / 3) & 1u, abort_flag)) break;
+            if (!mbar_wait_hot(bar0 + 8 * (S1_DONE + d1), (uint32_t)(s1 / 3) & 1u, abort_flag)) break;
             tc_fence_after();
             PYFFT_TC_TRACE(8, b)
             const uint32_t ca = tl + d0 * 64, cb = tl + d1 * 64;
