@@ -263,6 +263,15 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
     else:
         sy = np.shape(sigy)
         ny = sy[1] if (len(sy) == 2 and sy[1] == ntv) else sy[0]
+    # host records: start the (asynchronous, when pinned) host->device copies first, so that the
+    # segmentation, window and norm arithmetic below runs on the host while PCIe is busy
+    x_dev = y_dev = None
+    if not is_cplx:
+        precision = _eng.resolve_precision(precision, sigx, sigy)
+        device = _eng.require_cuda(device)
+        with torch.cuda.device(device):
+            x_dev = _eng.to_device(sigx, precision, device)
+            y_dev = _eng.to_device(sigy, precision, device)
     plan = _Plan(tvec, nx, ny, tbounds, Navr, windowoverlap, windowfunction, kwargs)
     nwins, nfft, K = plan.nwins, plan.nfft, plan.Navr
     if verbose:
@@ -284,11 +293,10 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
         raise NotImplementedError("nwins = %d: the GPU path needs a power-of-two window of 16..8192 "
                                   "samples (choose Navr/tper accordingly)" % nfft)
 
-    precision = _eng.resolve_precision(precision, sigx, sigy)
-    dev = _eng.require_cuda(device)
+    dev = device
     with torch.cuda.device(dev):
-        x = _eng.to_device(sigx, precision, dev)
-        y = _eng.channels_first(_eng.to_device(sigy, precision, dev), ntv)
+        x = x_dev
+        y = _eng.channels_first(y_dev, ntv)
         nch = y.shape[0]
         if x.dim() != 1:
             x = x.reshape(-1)
