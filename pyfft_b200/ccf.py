@@ -6,6 +6,7 @@ normalisation fused into the last pass.
 import numpy as np
 import torch
 
+from . import dist as _dist
 from . import engine
 
 
@@ -16,9 +17,12 @@ def _dev1(x, prec, dev):
     return t
 
 
-def ccf(x1, x2, fs, precision=None, device=None, return_device=False):
+def ccf(x1, x2, fs, precision=None, device=None, return_device=False, group=None, gather=False):
     """(tau, co): normalised cross-covariance at all 2N-1 lags (ccf.py:66-77).
-    x2 may be (pairs, N): every row is correlated against x1 (one shared forward FFT)."""
+    x2 may be (pairs, N): every row is correlated against x1 (one shared forward FFT).
+    ``group``: the rows of x2 are sharded over the ranks of a torch.distributed group in
+    contiguous blocks (no collective); each rank gets its rows, or all of them with
+    ``gather=True`` (one all_gather)."""
     dev = engine.require_cuda(device)
     if not isinstance(x1, torch.Tensor):
         x1 = np.asarray(x1)
@@ -33,7 +37,15 @@ def ccf(x1, x2, fs, precision=None, device=None, return_device=False):
     npts = a.shape[0]
     if b.shape[1] != npts:
         raise ValueError("operands could not be broadcast together: %d vs %d samples" % (npts, b.shape[1]))
-    co = engine.xcorr(a, b, prec, normalise=1)
+    npairs = b.shape[0]
+    if group is not None and not single:
+        b = _dist.shard_channels(b, group)
+    if b.shape[0] == 0:
+        co = torch.empty((0, 2 * npts - 1), dtype=engine._TORCH_REAL[prec], device=b.device)
+    else:
+        co = engine.xcorr(a, b, prec, normalise=1)
+    if group is not None and not single and gather:
+        co = _dist.gather_channels(co, npairs, group)
     lags = np.arange(-npts + 1, npts)
     tau = -lags / float(fs)                                      # ccf.py:70
     if single:

@@ -57,3 +57,50 @@ def local_plan(K, hop, nfft, nana, i0, reflect, rank, world):
     hi = max(a_hi, s_hi) if a_hi > a_lo else s_hi
     g_lo, g_hi = source_span(lo, hi, i0, reflect)
     return dict(k0=k0, k1=k1, seg_span=(a_lo, a_hi), stats_span=(s_lo, s_hi), src=(g_lo, g_hi))
+
+
+# --------------------------------------------------------------------------- #
+# channel sharding: spectrogram / STFT, Hilbert and ccf: independent
+# channels (or pairs), contiguous channel blocks per rank, no data-path collective; an
+# all-gather only when the caller asks for the assembled array
+# --------------------------------------------------------------------------- #
+
+def channel_range(C, rank, world):
+    """Channels [c0, c1) handled by `rank` of `world` (contiguous, balanced to +-1)."""
+    return C * rank // world, C * (rank + 1) // world
+
+
+def group_rank_world(group):
+    """(rank, world) of a torch.distributed group, (0, 1) without one."""
+    if group is None:
+        return 0, 1
+    import torch.distributed as dist
+    return dist.get_rank(group), dist.get_world_size(group)
+
+
+def shard_channels(x, group, axis=0):
+    """This rank's contiguous channel block of x along `axis` (a view)."""
+    rank, world = group_rank_world(group)
+    c0, c1 = channel_range(x.shape[axis], rank, world)
+    return x.narrow(axis, c0, c1 - c0) if hasattr(x, "narrow") else x.take(range(c0, c1), axis=axis)
+
+
+def gather_channels(local, C, group):
+    """Assembles the (C, ...) array from the per-rank blocks [c0, c1) along axis 0: one
+    all_gather of blocks padded to the largest one (the only collective of the channel-sharded
+    paths, and only on request)."""
+    import torch
+    import torch.distributed as dist
+    rank, world = group_rank_world(group)
+    if world == 1:
+        return local
+    width = max(channel_range(C, r, world)[1] - channel_range(C, r, world)[0] for r in range(world))
+    pad = torch.zeros((width,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
+    pad[:local.shape[0]] = local
+    parts = [torch.empty_like(pad) for _ in range(world)]
+    dist.all_gather(parts, pad, group=group)
+    out = []
+    for r in range(world):
+        c0, c1 = channel_range(C, r, world)
+        out.append(parts[r][:c1 - c0])
+    return torch.cat(out, dim=0)

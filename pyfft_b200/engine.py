@@ -418,6 +418,25 @@ def stft(x, rmap, nfft, hop, seg_first, seg_count, window, precision, coef=None,
     return out, pseg
 
 
+def stft_sharded(x, group, rmap, nfft, hop, seg_first, seg_count, window, precision, gather=False, **kw):
+    """Channel-sharded stft: rank r of `group` transforms its contiguous
+    block of the rows of x and keeps the result (no collective); gather=True assembles
+    [C][K][nbins] on every rank with one all_gather."""
+    from . import dist as _dist
+    xl = _dist.shard_channels(x, group)
+    if xl.shape[0] == 0:
+        nb = int(kw.get("nbins") or nfft)
+        odt = _TORCH_REAL[precision] if kw.get("power_out") else _TORCH_CPLX[precision]
+        out, pseg = torch.empty((0, int(seg_count), nb), dtype=odt, device=x.device), None
+    else:
+        out, pseg = stft(xl, rmap, nfft, hop, seg_first, seg_count, window, precision, **kw)
+    if gather:
+        out = _dist.gather_channels(out, x.shape[0], group)
+        if pseg is not None:
+            pseg = _dist.gather_channels(pseg, x.shape[0], group)
+    return out, pseg
+
+
 def stft_products(X, Y, conj_x, precision):
     """X [K][nb], Y [nch][K][nb] (or None) complex device tensors -> double sums
     (sxx [nb], syy [nch][nb], sxy [nch][nb] complex128) over the K segments."""

@@ -8,6 +8,7 @@ behaviour.  Lengths that are not powers of two raise NotImplementedError (no CPU
 import numpy as np
 import torch
 
+from . import dist as _dist
 from . import engine
 
 
@@ -38,12 +39,25 @@ def _prepare(uin, nfft, axes, precision, device):
     return u2, prec, (u.dim() == 2 and ax == 0), u.dim()
 
 
-def hilbert(uin, nfft=None, axes=-1, precision=None, device=None, return_device=False, envelope=False):
+def hilbert(uin, nfft=None, axes=-1, precision=None, device=None, return_device=False, envelope=False,
+            group=None, gather=False):
     """Analytic signal u + j H[u] (hilbert.py:22-67).  ``envelope=True`` returns |z| instead
-    (fused into the last pass; the complex signal is never written)."""
+    (fused into the last pass; the complex signal is never written).  ``group``: a
+    torch.distributed process group -- the records of a 2-D input are sharded over its ranks in
+    contiguous blocks (no collective); each rank gets its block back, or the assembled array
+    with ``gather=True`` (one all_gather)."""
     u2, prec, transposed, ndim = _prepare(uin, nfft, axes, precision, device)
-    z, env = engine.hilbert(u2, prec, want_analytic=not envelope, want_envelope=envelope)
+    nrec = u2.shape[0]
+    if group is not None and ndim == 2:
+        u2 = _dist.shard_channels(u2, group)
+    if u2.shape[0] == 0:
+        z = torch.empty((0, u2.shape[1]), dtype=engine._TORCH_CPLX[prec], device=u2.device)
+        env = torch.empty((0, u2.shape[1]), dtype=engine._TORCH_REAL[prec], device=u2.device)
+    else:
+        z, env = engine.hilbert(u2, prec, want_analytic=not envelope, want_envelope=envelope)
     out = env if envelope else z
+    if group is not None and ndim == 2 and gather:
+        out = _dist.gather_channels(out, nrec, group)
     if transposed:
         out = out.t()
     if ndim == 1:

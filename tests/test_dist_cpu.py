@@ -96,3 +96,45 @@ def test_local_plan_covers_everything():
             assert segs == K
             assert cover[0][0] == 0 and cover[-1][1] == nana
             assert all(cover[i][1] == cover[i + 1][0] for i in range(world - 1))
+
+
+def _channel_worker(rank, world, port, C, q):
+    sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from pyfft_b200.dist import channel_range, gather_channels, shard_channels
+    full = torch.arange(C * 6, dtype=torch.float64).reshape(C, 2, 3)       # same on each rank
+    mine = shard_channels(full, dist.group.WORLD)
+    c0, c1 = channel_range(C, rank, world)
+    ok = mine.shape[0] == c1 - c0 and torch.equal(mine, full[c0:c1])
+    back = gather_channels(mine * 1.0, C, dist.group.WORLD)                # the one optional collective
+    ok = ok and torch.equal(back, full)
+    q.put((rank, bool(ok), (c0, c1)))
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("C", [64, 5, 1])
+def test_channel_sharding_two_ranks(C):
+    """STFT / Hilbert / ccf shard by channel: contiguous blocks that cover every
+    channel once, unequal blocks and empty ranks included; gather restores the array."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29600 + C
+    procs = [ctx.Process(target=_channel_worker, args=(r, 2, port, C, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+    assert all(r[1] for r in res), res
+    assert res[0][2][0] == 0 and res[0][2][1] == res[1][2][0] and res[1][2][1] == C
+
+
+def test_channel_range_partitions():
+    from pyfft_b200.dist import channel_range
+    for C in (1, 7, 16, 64):
+        for world in (1, 2, 4, 8):
+            spans = [channel_range(C, r, world) for r in range(world)]
+            assert spans[0][0] == 0 and spans[-1][1] == C
+            assert all(spans[i][1] == spans[i + 1][0] for i in range(world - 1))
+            assert max(b - a for a, b in spans) - min(b - a for a, b in spans) <= 1
