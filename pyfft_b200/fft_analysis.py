@@ -25,6 +25,8 @@ Deliberate differences from the reference (documented in DESIGN.md):
   * the per-segment fields of fftinfo (Pxx_seg, Xfft_seg, ...) are computed lazily
     on first access instead of being materialised on every call.
 """
+import threading
+
 import numpy as np
 import torch
 
@@ -191,6 +193,45 @@ def _host(t):
     return t.cpu().numpy()
 
 
+def _host_many(tensors):
+    """Several small device results in ONE device->host transfer (each .cpu() is a synchronising
+    round trip of ~25 us): complex tensors travel as (re, im) float64 pairs."""
+    flat = [torch.view_as_real(t).reshape(-1) if t.is_complex() else t.reshape(-1).to(torch.float64)
+            for t in tensors]
+    host = torch.cat(flat).cpu().numpy()
+    out, pos = [], 0
+    for t, f in zip(tensors, flat):
+        a = host[pos:pos + f.numel()]
+        pos += f.numel()
+        if t.is_complex():
+            a = a.view(np.complex128)
+        out.append(a.reshape(tuple(t.shape)).copy())
+    return out
+
+
+_plans = threading.local()
+
+
+def _welch_plan(nfft, hop, nch, precision, win, dev):
+    """engine.WelchPlan of this thread for these parameters, reset (device buffers, the uploaded
+    window and its transform are reused from call to call: ~0.2 ms of a 0.4 ms computation)."""
+    cache = getattr(_plans, "cache", None)
+    if cache is None:
+        cache = _plans.cache = {}
+    key = (int(nfft), int(hop), int(nch), precision, str(dev))
+    hit = cache.get(key)
+    if hit is not None and np.array_equal(hit[0], win):
+        wp = hit[1]
+        wp.reset()
+        wp.coef = None
+        return wp
+    wp = _eng.WelchPlan(nfft, hop, nch, precision, win, dev)
+    if len(cache) >= 8:
+        cache.clear()
+    cache[key] = (np.array(win, dtype=np.float64, copy=True), wp)
+    return wp
+
+
 def _make_segment_loader(sigx, sigy, ntv, plan, win, mode, precision, dev, onesided, scale):
     """Per-segment fields of fftinfo (fft_analysis.py:461-481) are produced on first access by
     the STFT kernel instead of on every call: Xfft_seg (Navr, nfft), Yfft_seg (nch, Navr, nfft)
@@ -310,7 +351,7 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
             # the reference dies here with a broadcasting ValueError (fft_analysis.py:375)
             raise ValueError("operands could not be broadcast together: segment %d runs past the "
                              "analysed record (%d samples, nwins=%d, hop=%d)" % (K - 1, plan.nana, nwins, hop))
-        wp = _eng.WelchPlan(nfft, hop, nch, precision, win, dev)
+        wp = _welch_plan(nfft, hop, nch, precision, win, dev)
         mode = _lib.DETREND_MEAN if detrend_style > 0 else (_lib.DETREND_LINEAR if detrend_style < 0
                                                             else _lib.DETREND_NONE)
         rank, world = 0, 1
@@ -362,8 +403,16 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
 
     freq = np.fft.fftfreq(nfft, 1.0 / plan.Fs)                     # :396
     freq = freq[:plan.Nnyquist] if onesided else np.fft.fftshift(freq)
-    Pxx, Pyy, Pxy = _host(res["Pxx"]), _host(res["Pyy"]), _host(res["Pxy"])
-    Cxy, Cxy2, phi_xy = _host(res["Cxy"]), _host(res["Cxy2"]), _host(res["phi_xy"])
+    tc_flag = wp._tc_status if getattr(fftinfo, "tensor_cores", False) else None
+    hosted = _host_many([res["Pxx"], res["Pyy"], res["Pxy"], res["Cxy"], res["Cxy2"], res["phi_xy"],
+                         corr["Rxx"], corr["Ryy"], corr["Rxy"], corr["iCxy"]] +
+                        ([tc_flag] if tc_flag is not None else []))
+    (Pxx, Pyy, Pxy, Cxy, Cxy2, phi_xy, h_rxx, h_ryy, h_rxy, h_icxy) = hosted[:10]
+    if tc_flag is not None and hosted[10][0] != 0:
+        # a hand-shake of the tensor-core kernel timed out (bounded waits): the sums are not valid
+        tc_flag.zero_()
+        raise RuntimeError("pyfft_b200: the tensor-core Welch kernel aborted (barrier time-out); "
+                           "call again with tensor_cores=False")
 
     # ---- O(nfreq) bookkeeping on the averaged spectra, as in the reference (:496-540) ---- #
     with np.errstate(all="ignore"):
@@ -380,8 +429,8 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
                 if nfft % 2:
                     amp[-1] = np.sqrt(2) * amp[-1]
             setattr(fftinfo, nm, amp)
-        fftinfo.Rxx, fftinfo.Ryy = _host(corr["Rxx"]), _host(corr["Ryy"])
-        fftinfo.Rxy, fftinfo.iCxy = _host(corr["Rxy"]), _host(corr["iCxy"])
+        fftinfo.Rxx, fftinfo.Ryy = h_rxx, h_ryy
+        fftinfo.Rxy, fftinfo.iCxy = h_rxy, h_icxy
         # zero-lag values sit at index nfft//2 after the fftshift (:585-596)
         fftinfo.Ex = fftinfo.Rxx[nfft // 2, ...].copy()
         fftinfo.Ey = fftinfo.Ryy[nfft // 2, ...].copy()
