@@ -69,6 +69,53 @@ def to_device(a, precision, device, complex_ok=False):
     return t.to(device=device, dtype=want, non_blocking=True)
 
 
+_upload_streams = {}
+
+
+def staged_upload(sigx, sigy, precision, device, nchunks=4, min_samples=1 << 22):
+    """Host -> device copy of two long pinned records in `nchunks` pieces on a side stream, with an
+    event after each piece, so that the caller can start on the segments of a piece while the next
+    one is still crossing PCIe.  -> (x, y, events, bounds) with bounds[i] = samples per channel that
+    are on the device once events[i] has fired; None when the inputs do not qualify (not pinned host
+    tensors of the compute dtype, short, or time-major 2-D) -- the caller then uses to_device."""
+    if not (isinstance(sigx, torch.Tensor) and isinstance(sigy, torch.Tensor)):
+        return None
+    want = _TORCH_REAL[precision]
+    if sigx.is_cuda or sigy.is_cuda or sigx.dtype != want or sigy.dtype != want:
+        return None
+    if not (sigx.is_pinned() and sigy.is_pinned()) or sigx.dim() != 1:
+        return None
+    n = sigx.shape[0]
+    if n < min_samples or sigy.dim() not in (1, 2) or sigy.shape[-1] != n or not sigy.is_contiguous() \
+            or not sigx.is_contiguous():
+        return None
+    cur = torch.cuda.current_stream(device)
+    key = str(device)
+    side = _upload_streams.get(key)
+    if side is None:
+        side = _upload_streams[key] = torch.cuda.Stream(device=device)
+    x = torch.empty(n, dtype=want, device=device)
+    y = torch.empty(tuple(sigy.shape), dtype=want, device=device)
+    side.wait_stream(cur)
+    events, bounds = [], []
+    step = (n + nchunks - 1) // nchunks
+    step = (step + 1023) // 1024 * 1024
+    with torch.cuda.stream(side):
+        a = 0
+        while a < n:
+            b = min(n, a + step)
+            x[a:b].copy_(sigx[a:b], non_blocking=True)
+            y[..., a:b].copy_(sigy[..., a:b], non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(side)
+            events.append(ev)
+            bounds.append(b)
+            a = b
+    x.record_stream(side)
+    y.record_stream(side)
+    return x, y, events, bounds
+
+
 def channels_first(y, n):
     """(n,), (n, C) or (C, n) device tensor -> contiguous (C, n).  Mirrors the reference's
     orientation rule: a 2-D sigy whose second axis has the record length is transposed

@@ -306,13 +306,17 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
         ny = sy[1] if (len(sy) == 2 and sy[1] == ntv) else sy[0]
     # host records: start the (asynchronous, when pinned) host->device copies first, so that the
     # segmentation, window and norm arithmetic below runs on the host while PCIe is busy
-    x_dev = y_dev = None
+    x_dev = y_dev = staged = None
     if not is_cplx:
         precision = _eng.resolve_precision(precision, sigx, sigy)
         device = _eng.require_cuda(device)
         with torch.cuda.device(device):
-            x_dev = _eng.to_device(sigx, precision, device)
-            y_dev = _eng.to_device(sigy, precision, device)
+            staged = _eng.staged_upload(sigx, sigy, precision, device) if group is None else None
+            if staged is not None:
+                x_dev, y_dev = staged[0], staged[1]
+            else:
+                x_dev = _eng.to_device(sigx, precision, device)
+                y_dev = _eng.to_device(sigy, precision, device)
     plan = _Plan(tvec, nx, ny, tbounds, Navr, windowoverlap, windowfunction, kwargs)
     nwins, nfft, K = plan.nwins, plan.nfft, plan.Navr
     if verbose:
@@ -360,8 +364,12 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
         lp = _dist.local_plan(K, hop, nwins, plan.nana, plan.i0, refl, rank, world)
         nseg = lp["k1"] - lp["k0"]
         fix_nana = None
-        if mode == _lib.DETREND_MEAN and wp.can_fuse_mean and nseg > 0 and hop <= nwins \
-                and not two_pass:
+        fused = mode == _lib.DETREND_MEAN and wp.can_fuse_mean and nseg > 0 and hop <= nwins and not two_pass
+        if staged is not None and not fused:
+            # only the fused single pass consumes the records piece by piece: wait for all of them
+            torch.cuda.current_stream(dev).wait_event(staged[2][-1])
+            staged = None
+        if fused:
             # global mean (:356-357) fused into the single pass over the data: provisional mean
             # from the head of the shard, exact correction by linearity afterwards
             s_lo, s_hi = lp["stats_span"]
@@ -370,12 +378,25 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
             # (2^-12 relative, zero mean) averages out as 1/sqrt(K) -- used when enough segments
             # are averaged for the 1e-5-of-peak contract to hold with margin
             use_tc = wp.can_use_tc and (nseg >= 16384 if tensor_cores is None else bool(tensor_cores))
-            if use_tc:
-                wp.prepare_tc(x, y, rmap, c_lo, c_hi)
-                wp.accumulate_tc(x, y, rmap, lp["k0"], nseg)
+            accumulate = wp.accumulate_tc if use_tc else wp.accumulate_mean
+            if staged is None:
+                (wp.prepare_tc if use_tc else wp.estimate_mean)(x, y, rmap, c_lo, c_hi)
+                accumulate(x, y, rmap, lp["k0"], nseg)
             else:
-                wp.estimate_mean(x, y, rmap, c_lo, c_hi)
-                wp.accumulate_mean(x, y, rmap, lp["k0"], nseg)
+                # the records are still arriving in pieces (engine.staged_upload): the segments that are
+                # complete behind each piece are accumulated while the next piece crosses PCIe
+                cur = torch.cuda.current_stream(dev)
+                events, bounds = staged[2], staged[3]
+                cur.wait_event(events[0])
+                (wp.prepare_tc if use_tc else wp.estimate_mean)(x, y, rmap, c_lo, c_hi)
+                kdone = lp["k0"]
+                for i, (ev, b_i) in enumerate(zip(events, bounds)):
+                    cur.wait_event(ev)
+                    kend = lp["k1"] if i == len(events) - 1 else \
+                        max(kdone, min(lp["k1"], (b_i - nwins + refl - plan.i0) // hop + 1))
+                    if kend > kdone:
+                        accumulate(x, y, rmap, kdone, kend - kdone)
+                        kdone = kend
             fftinfo.tensor_cores = bool(use_tc)
             if s_lo < c_lo:
                 wp.detrend_stats(x, y, rmap, s_lo, c_lo)

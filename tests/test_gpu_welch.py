@@ -156,3 +156,30 @@ def test_fused_mean_route_equals_two_pass_and_oracle(precision, window, cuda_dev
     b = fft_pwelch(t, x, y, plotit=False, precision=precision, two_pass_detrend=True, **kw)
     _check(a, ref, precision)
     _check(b, ref, precision)
+
+
+@pytest.mark.parametrize("tensor_cores,navr", [(True, 2047), (False, 2047), (None, 1023)])
+def test_pinned_host_records_are_uploaded_in_pieces(tensor_cores, navr, cuda_device):
+    """Long pinned host records take the staged upload (copy in pieces on a side stream, the complete
+    segments of each piece accumulated behind it): same spectra as with device-resident inputs, for
+    the tensor-core kernel, the CUDA-core kernel and a two-pass case that has to wait for all pieces."""
+    import torch
+    from oracle import signals
+    from pyfft_b200 import fft_pwelch
+    n = 2 ** 22
+    t, x, y = signals.c2_cross(n=n, dc=(7.0, 2.5))
+    xs, ys = torch.from_numpy(x.astype(np.float32)).pin_memory(), torch.from_numpy(y.astype(np.float32)).pin_memory()
+    kw = dict(Navr=navr, windowoverlap=0.5, windowfunction="Hanning", detrend_style=1, plotit=False,
+              precision="fp32")
+    if tensor_cores is None:
+        kw["two_pass_detrend"] = True
+    else:
+        kw["tensor_cores"] = tensor_cores
+    a = fft_pwelch(t, xs, ys, **kw)
+    b = fft_pwelch(t, xs.to(cuda_device), ys.to(cuda_device), **kw)
+    for i in (1, 2, 3, 4):
+        assert relerr(a[i], b[i]) <= 2e-6, i
+    assert relerr(a[6].Rxy, b[6].Rxy) <= 2e-6
+    # a (1, n) second record goes the same way
+    c = fft_pwelch(t, xs, ys.view(1, n), **kw)
+    assert relerr(c[1], a[1]) <= 1e-12
