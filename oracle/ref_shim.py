@@ -14,9 +14,11 @@ that are absent here:
 ``ccf.py`` / ``dft.py`` cannot be loaded on Python 3 (dft.py:200 is a py2 print
 statement), so they are not offered here.
 
-Only usable where ``/root/reference`` exists (the build container).  The GPU box
-has no such directory: nothing in ``-m gpu`` tests, ``smoke()`` or ``bench.py``
-may call :func:`load_reference`.
+``/root/reference`` exists in the build container only.  ``__graft_entry__.build()`` places
+unmodified copies of the four modules under ``baseline/_ref/`` (git-ignored, it travels to the
+GPU box like the built ``.so``); ``bench.py --impl reference`` and the ``cpu_baseline`` leg
+load them from there (``load_reference(ref_dir)``) to time the stock CPU path.  Nothing in
+``-m gpu`` tests or ``smoke()`` reads either directory.
 """
 import importlib.util
 import os
@@ -28,8 +30,12 @@ import numpy as np
 REFERENCE_DIR = os.environ.get("PYFFT_REFERENCE_DIR", "/root/reference")
 
 
-def available():
-    return os.path.isfile(os.path.join(REFERENCE_DIR, "fft_analysis.py"))
+MODULES = ("windows", "fft_analysis", "spectrogram", "hilbert")
+
+
+def available(ref_dir=None):
+    d = REFERENCE_DIR if ref_dir is None else ref_dir
+    return all(os.path.isfile(os.path.join(d, m + ".py")) for m in MODULES)
 
 
 class _Struct(object):
@@ -72,12 +78,13 @@ def _detrend_linear(y, axis=None):
 _loaded = {}
 
 
-def load_reference():
-    """Return a dict of the reference modules {name: module}."""
+def load_reference(ref_dir=None):
+    """Return a dict of the reference modules {name: module} (first call decides the directory)."""
     if _loaded:
         return _loaded
-    if not available():
-        raise RuntimeError("reference tree not present at %s" % REFERENCE_DIR)
+    ref_dir = REFERENCE_DIR if ref_dir is None else ref_dir
+    if not available(ref_dir):
+        raise RuntimeError("reference tree not present at %s" % ref_dir)
     if not hasattr(np, "deprecate"):
         np.deprecate = lambda *a, **k: (lambda f: f)
     saved = {}
@@ -97,11 +104,11 @@ def load_reference():
     sys.modules.update({"pybaseutils": pb, "pybaseutils.Struct": st,
                         "pybaseutils.utils": ut})
     pkg = types.ModuleType("FFT")
-    pkg.__path__ = [REFERENCE_DIR]
+    pkg.__path__ = [ref_dir]
     sys.modules["FFT"] = pkg
-    for name in ("windows", "fft_analysis", "spectrogram", "hilbert"):
+    for name in MODULES:
         spec = importlib.util.spec_from_file_location(
-            "FFT." + name, os.path.join(REFERENCE_DIR, name + ".py"))
+            "FFT." + name, os.path.join(ref_dir, name + ".py"))
         mod = importlib.util.module_from_spec(spec)
         sys.modules["FFT." + name] = mod
         spec.loader.exec_module(mod)
