@@ -167,7 +167,7 @@ int pyfft_welch_rereference(double* acc, double* lin, int32_t nfft, int32_t nch,
 
 /* ------------------------------------------------------------------------- *
  * K1-TC, the same accumulation on the tcgen05 tensor cores (float32 input,
- * nfft = 4096, hop a multiple of 512)
+ * nfft = 4096, hop 512, 1024, 2048 or 4096)
  * replaces: the same reference lines as pyfft_welch_accumulate_mean.
  * Every segment's 4096-point DFT is computed as two real DFT-matrix GEMMs
  * (64 x 64 decomposition, fp16 operands split hi + lo for the matrices, fp32
@@ -182,10 +182,13 @@ int pyfft_welch_rereference(double* acc, double* lin, int32_t nfft, int32_t nch,
  *   pyfft_welch_tc_prepare: est (pairs, as above; the mean is rounded to float so
  *     that the kernel's subtraction is the one the correction assumes) and
  *     prescale = double[nch+1], powers of two bringing the rms of each channel to
- *     [1/8, 1/4), from the samples of analysed indices [j_begin, j_end).
- *   status_flag (device int32, zeroed by the caller) is set to 1 if a tensor-core
- *     completion barrier timed out; the result is then invalid and the host falls
- *     back to pyfft_welch_accumulate_mean.
+ *     [1/8, 1/4), from 64 runs of 1024 samples spread evenly over the analysed
+ *     indices [j_begin, j_end).
+ *   status_flag (device int32, zeroed by the caller): bit 0 is set if a tensor-core
+ *     completion barrier timed out, bit 1 if a partial sum is not finite (an fp16
+ *     operand overflowed: the record is far louder somewhere than the sampled
+ *     statistics said); the result is then invalid and the host reruns on
+ *     pyfft_welch_accumulate_mean.
  * ------------------------------------------------------------------------- */
 int64_t pyfft_welch_tc_workspace_bytes(const pyfft_segmentation* seg, int32_t nch);
 
@@ -226,6 +229,16 @@ int pyfft_welch_finalize_mean(const double* acc, const double* lin, int32_t nfft
                               const double* wlow, double scale, int32_t onesided,
                               double* Pxx, double* Pyy, double* Pxy, double* Cxy, double* Cxy2,
                               double* phi, void* stream);
+
+/* Dynamic range of the averaged auto-spectra, the host's data-aware check of the tensor-core path
+ * (no reference line: the reference computes in float64 throughout).  The fp16 operands of
+ * pyfft_welch_accumulate_tc leave a white error floor of ~1e-7 of the MEAN bin power in every bin; the
+ * coherence (fft_analysis.py:1662-1680) of a bin whose own power is not far above that floor cannot meet
+ * the 1e-4 contract.  out[2c] = min over bins, out[2c+1] = mean over bins of Re Pxx (c = 0) / Re Pyy[:, c-1]
+ * (c = 1..nch), F = nfreq bins as written by pyfft_welch_finalize; the caller reruns on the CUDA-core
+ * kernel when min < threshold * mean (pyfft_b200.fft_analysis.TC_DYNAMIC_RANGE / Navr). */
+int pyfft_welch_dynamic_range(const double* Pxx, const double* Pyy, int32_t nfreq, int32_t nch,
+                              int32_t onesided, double* out, void* stream);
 
 /* ------------------------------------------------------------------------- *
  * K3a  correlation epilogue

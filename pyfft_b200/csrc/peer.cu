@@ -17,8 +17,9 @@
 // Two staging buffers are enough: a rank can be at most one epoch ahead of a peer (to publish
 // epoch e+1 it must have seen the peer's flag of epoch e, which the peer sets after it finished
 // reading epoch e-1), so the buffer a slow peer still reads is never the one being written.
-// All CTAs spin, so the grid is kept far below the SM count (co-residency); waits are bounded and
-// raise *status instead of hanging the GPU.
+// All CTAs spin, so the grid is kept far below the SM count (co-residency); waits are bounded (tens of
+// seconds) and on a time-out raise *status AND overwrite the local state with NaN instead of hanging the
+// GPU or returning a partial sum.
 #include "common.cuh"
 
 namespace pyfft {
@@ -74,7 +75,12 @@ peer_allreduce_kernel(double* __restrict__ state, int64_t n, const int64_t* __re
         if (!ok) { s_ok = 0; atomicExch(status, 1); }
     }
     __syncthreads();
-    if (!s_ok) return;
+    if (!s_ok) {
+        // a peer never published this epoch: fail loudly -- every consumer of the state sees NaN, the host
+        // wrappers also read *status and raise
+        for (int64_t i = i0 + threadIdx.x; i < i1; i += PEER_THREADS) state[i] = __longlong_as_double(0x7ff8000000000000ll);
+        return;
+    }
     for (int64_t i = i0 + threadIdx.x; i < i1; i += PEER_THREADS) {
         double s = 0.0;
         for (int r0 = 0; r0 < world; r0 += 8) {         // eight NVLink loads in flight, summed in rank order

@@ -599,6 +599,36 @@ static int dispatch_welch(int log2l, const void* x, const void* y, int64_t y_str
     return fail(PYFFT_EUNSUPPORTED, "nfft = 2^%d not supported", log2l);
 }
 
+// min and mean over the bins of the averaged auto-spectra (one block per channel: 0 = x from Pxx, 1.. = y
+// from Pyy[F][nch]); one-sided spectra: the un-doubled end bins are counted twice so that all bins are alike
+__global__ void __launch_bounds__(256) welch_dynamic_range_kernel(const double* __restrict__ Pxx, const double* __restrict__ Pyy,
+                                                                  int F, int nch, int onesided, double* __restrict__ out) {
+    const int c = blockIdx.x;
+    double mn = 1e300, sum = 0.0;
+    for (int f = threadIdx.x; f < F; f += 256) {
+        double v = c == 0 ? Pxx[2 * f] : Pyy[2 * ((size_t)f * nch + (c - 1))];
+        if (onesided && (f == 0 || f == F - 1)) v *= 2.0;
+        if (!(v >= 0.0)) v = 0.0;                     // NaN counts as an empty bin
+        mn = v < mn ? v : mn;
+        sum += v;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const double a = __shfl_xor_sync(0xffffffffu, mn, o);
+        mn = a < mn ? a : mn;
+        sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    }
+    __shared__ double sh[2][8];
+    if ((threadIdx.x & 31) == 0) { sh[0][threadIdx.x >> 5] = mn; sh[1][threadIdx.x >> 5] = sum; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        mn = sh[0][0]; sum = sh[1][0];
+        for (int w = 1; w < 8; ++w) { mn = sh[0][w] < mn ? sh[0][w] : mn; sum += sh[1][w]; }
+        out[2 * c] = mn;
+        out[2 * c + 1] = sum / (double)F;
+    }
+}
+
 int welch_reduce_launch_f32(const float* partial, int nparts, int per_pair, int nch, double* acc, cudaStream_t st) {
     welch_reduce_kernel<float><<<dim3((per_pair + 31) / 32, nch), 256, 0, st>>>(partial, nparts, per_pair, acc);
     PYFFT_LAUNCH_OK("welch_reduce_kernel");
@@ -778,6 +808,14 @@ int pyfft_welch_finalize_mean(const double* acc, const double* lin, int32_t nfft
     welch_finalize_kernel<<<(total + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
         acc, fix, nfft, nch, scale / (double)K, onesided, F, Pxx, Pyy, Pxy, Cxy, Cxy2, phi);
     PYFFT_LAUNCH_OK("welch_finalize_kernel");
+    return PYFFT_OK;
+}
+
+int pyfft_welch_dynamic_range(const double* Pxx, const double* Pyy, int32_t nfreq, int32_t nch, int32_t onesided,
+                              double* out, void* stream) {
+    if (!Pxx || !Pyy || !out || nfreq <= 0 || nch <= 0) return fail(PYFFT_EINVAL, "welch_dynamic_range: bad arguments");
+    welch_dynamic_range_kernel<<<nch + 1, 256, 0, static_cast<cudaStream_t>(stream)>>>(Pxx, Pyy, nfreq, nch, onesided, out);
+    PYFFT_LAUNCH_OK("welch_dynamic_range_kernel");
     return PYFFT_OK;
 }
 

@@ -11,27 +11,40 @@
 //             j <= 32: Re A1[k1 = j],  j >= 33: Im A1[k1 = j - 32]
 //   twiddle   B[k1, n2] = A1[k1, n2] * W_4096^(n2 k1)                     CUDA cores, out of TMEM
 //   stage 2   X[k1 + 64 k2] = sum_n2 B[k1, n2] W_64^(n2 k2)
-//             D2[(k2, re|im), (seg, ch, k1)] = F2[(k2, c'), (n2, c)] * B2[(seg, ch, k1), (n2, c)]
-//                                                                         M = 128, N = 144, K = 128
-// Lane (k2, c) of D2 holds one component of X and Y of 33 bins for both segments of a batch,
-// so the cross-spectral sums are thread-local (one shuffle for the mixed Im term) and every
-// lane owns distinct bins: 132 accumulator registers, no redundancy.  Rows k1 = 33..63 of
-// stage 1 are never computed: bins with f mod 64 > 32 come from lanes k2 >= 32 by Hermitian
-// symmetry X[4096 - f] = conj X[f].
+//             D2[(k2, re|im), (ch, k1)] = F2[(k2, c'), (n2, c)] * B2[(ch, k1), (n2, c)]
+//                                                                         M = 128, N = 80, K = 128
+// Lane (k2, c) of D2 holds one component of X and Y of 33 bins of a segment, so the cross-spectral
+// sums are thread-local (one shuffle for the mixed Im term) and every lane owns distinct bins:
+// 132 accumulator registers, no redundancy.  Rows k1 = 33..63 of stage 1 are never computed: bins
+// with f mod 64 > 32 come from lanes k2 >= 32 by Hermitian symmetry X[4096 - f] = conj X[f].
 // Precision: operands are fp16 with fp32 accumulation.  The DFT matrices are split in two fp16
 // terms (hi + lo, 22 significant bits, two MMAs per product); the data is scaled by a power of
 // two to unit-ish rms and rounded ONCE to fp16 at each stage -- a zero-mean relative error of
-// 2^-12 per element that averages out over the segments (use for Navr >~ 10^4).
+// 2^-12 per element that averages out over the segments when the record carries broadband noise
+// (the host checks the dynamic range of the result, see pyfft_welch_dynamic_range).
 //
-// Execution: one persistent CTA per SM, warp-specialised, all hand-shakes through mbarriers:
-//   warpgroup 0  epilogue   D2 (TMEM) -> register accumulators                 (128 threads)
-//   warpgroup 1  twiddle    D1 (TMEM) -> twiddle -> fp16 -> B2 operand (smem)   (128 threads)
-//   warpgroup 2-5 loaders   global -> detrend -> window -> fp16 -> A1 operand; set g (8 warps)
-//                           takes the segments of parity g and owns A1 slot g   (2 x 256 threads)
-//   warps 24, 25 MMA issue  one thread each for stage 1 and stage 2 (independent instruction
-//                           streams; the stages meet only through the mbarriers)
-// A1: 2 slots (segment parity); D1: 3 slots (segment index % 3); B2, D2: 2 slots (batch parity).  Registers
-// are moved from the twiddle and MMA warpgroups to the epilogue group with setmaxnreg.
+// Data path (round 2): BOTH operands that stream are kept out of the shared-memory read port.
+//   * the raw samples arrive by TMA (cp.async.bulk, one copy of hop samples per channel and segment: a
+//     bulk copy costs its issuing thread ~170 clocks whatever its size, tools/bulk_rate.cu) in a ring of
+//     16 K samples per channel; with 50 % overlap every sample crosses L2 -> SM once and is converted
+//     from shared memory by both segments that contain it;
+//   * the stage-1 data operand A1op lives in TENSOR memory (tcgen05.st by the converter warps, thread =
+//     row (ch, n2), 32 columns of packed half2), so stage 1 reads only the 8 KB matrix tile from shared
+//     memory and runs at the tensor pipe's N/2 = 32 clocks per MMA instead of the 48 clocks that the
+//     operand fetch of a 128 x 16 shared-memory A tile costs (tools/mma_rate.cu);
+//   * stage 2 as before: the matrix F2 (hi, lo) in tensor memory, the twiddled data from shared memory.
+// Everything is per segment and double-buffered (A1, D1, B2, D2 x 2): no role waits for a slot that its
+// consumer is still draining.  One MMA-issuing thread sustains one tcgen05.mma per ~51 clocks whatever
+// its shape (tools/mma_rate.cu), so three threads issue: stage 1, stage 2 of even and of odd segments.
+//
+// Execution: one persistent CTA of 20 warps per SM, warp-specialised, all hand-shakes through mbarriers:
+//   warps 0-3    epilogue    D2 (TMEM) -> register accumulators, packed f32x2 FMAs         (176 regs)
+//   warps 4-7    twiddle     D1 (TMEM) -> twiddle (factors in registers) -> fp16 -> B2     (120 regs)
+//   warps 8-15   converters  ring (smem) -> (x - mean) * window * scale -> fp16 -> A1 (TMEM); warp
+//                            (q, h): TMEM lane quarter q = rows (ch, n2), n1 half h; the 32 window
+//                            values a thread needs stay in registers                         (72 regs)
+//   warp 16      TMA producer (one thread)      warp 17      stage-1 MMA issue
+//   warps 18, 19 stage-2 MMA issue for even / odd segments                                   (40 regs)
 #include <cuda_fp16.h>
 
 #include <map>
@@ -45,37 +58,42 @@ namespace pyfft {
 
 namespace tcw {
 constexpr int L = 4096, NBIN = L / 2 + 1;
-constexpr int SEGS = 2;                      // segments per batch (one B2 slot, one twiddle pass)
+constexpr int UNIT = 512;                    // samples per unit: a converter thread reads 8 samples (n1) of a unit
+constexpr int NU = 32;                       // ring depth in units; the ring is filled in BLOCKS of one hop (m units, m | 8)
+constexpr int RING_CH_FLOATS = NU * (UNIT + 4);   // one channel's ring: NU / m blocks of m * 512 + 4 floats (worst case m = 1);
+                                             // + 16 bytes per block: the copy starts at the 16-byte boundary below the block
+constexpr int RING_BYTES = 2 * RING_CH_FLOATS * 4;   // x then y: 132096
 constexpr int YOFF = 36;                     // D2 columns of a segment: X at +0 (33 bins), Y at +36 (33 bins); rows of B2 alike
-constexpr int COLS_PER_SEG = 72;             // D2 columns / B2 rows per segment
-constexpr int N2 = SEGS * COLS_PER_SEG;      // stage-2 MMA N = 144 (a multiple of 16)
+constexpr int NCOL = 80;                     // stage-2 MMA N (a multiple of 16 >= 69), D2 columns / B2 rows per segment
 constexpr int NLIN = 8;                      // bins with linear sums (mean correction)
-constexpr int NTHREADS = 896;
+constexpr int NTHREADS = 640;
 constexpr int HEAD = 3 * L;                  // samples per channel of the materialised reflect zone
-// constant block in global memory: [shared part][F2 hi, plain rows][F2 lo, plain rows]
-// shared part (copied to shared memory), byte offsets
+constexpr int HEADP = HEAD + 4;              // pitch of a channel in that buffer (+ the alignment shift)
+// constant block in global memory: [G hi][G lo][twiddles][F2 hi, plain rows][F2 lo, plain rows]
 constexpr int OFF_GHI = 0, OFF_GLO = 8192, OFF_TW = 16384;
-constexpr int CONST_SMEM_BYTES = 16384 + 33 * 64 * 8;        // 33280
-// stage-2 matrix F2[(k2, c')][(n2, c)] as 128 rows of 64 packed half2, loaded into tensor memory
+constexpr int CONST_SMEM_BYTES = 16384 + 33 * 64 * 8;        // 33280 (offset of the F2 rows)
 constexpr int OFF_F2T_HI = CONST_SMEM_BYTES, OFF_F2T_LO = OFF_F2T_HI + 128 * 64 * 4;
 constexpr int CONST_BYTES = OFF_F2T_LO + 128 * 64 * 4;       // 98816
-constexpr int WIN_LD = 68;                                   // window stored [n2][n1], padded: conflict-free LDS.128
-constexpr int OFF_WIN = CONST_SMEM_BYTES;                    // float[64][WIN_LD] = 17408 bytes
-constexpr int OFF_A1 = 51200;                                // 1024-aligned; 2 slots of 128 rows x 64 halves
-constexpr int A1_BYTES = 16384;
-constexpr int OFF_B2 = OFF_A1 + 2 * A1_BYTES;                // 2 slots of N2 rows x 128 halves (2 K atoms)
-constexpr int B2_BYTES = N2 * 128 * 2;                       // 36864
-constexpr int B2_SEG_BYTES = COLS_PER_SEG * 128;             // row offset of segment 1 inside a K atom
-constexpr int SMEM_BYTES = OFF_B2 + 2 * B2_BYTES + 1024;     // + alignment slack = 158720
-static_assert(OFF_WIN + 64 * WIN_LD * 4 <= OFF_A1, "window table overlaps the operand slots");
+// shared memory (1024-aligned): G hi | G lo | B2 x 2 | ring
+constexpr int OFF_B2 = 16384;
+constexpr int B2_ATOM = NCOL * 128;                          // bytes of one K atom (64 halves) of all rows: 10240
+constexpr int B2_BYTES = 2 * B2_ATOM;                        // K = 128: 20480
+constexpr int OFF_RING = OFF_B2 + 2 * B2_BYTES;              // 57344
+constexpr int SMEM_BYTES = OFF_RING + RING_BYTES + 1024;     // + alignment slack = 190464
+static_assert(B2_ATOM % 1024 == 0 && OFF_RING % 16 == 0 && (RING_CH_FLOATS * 4) % 16 == 0, "operand alignment");
 // tensor memory columns (480 of 512)
 constexpr int TM_F2HI = 0, TM_F2LO = 64;                     // stage-2 A operand: 128 lanes x 64 columns of half2
-constexpr int TM_D1 = 128;                                   // 3 slots x 64 columns (segment index % 3)
-constexpr int TM_D2 = 320;                                   // 1 slot of N2 columns
+constexpr int TM_A1 = 128;                                   // 2 slots x 32 columns of half2 (stage-1 A operand)
+constexpr int TM_D1 = 192;                                   // 2 slots x 64 columns
+constexpr int TM_D2 = 320;                                   // 2 slots x NCOL columns
 // mbarriers
-enum { A1_FULL = 0, S1_DONE = 2, D1_FREE = 5, B2_FULL = 8, B2_FREE = 10, S2_DONE = 12, D2_FREE = 14, NBARS = 16 };
-// registers per thread after reallocation (launch: 72; released 512*16 + 128*16 + 128*24 = requested 128*104)
-constexpr int REGS_EPI = 176, REGS_TWD = 56, REGS_LDR = 56, REGS_MMA = 48;
+enum { RAW_FULL = 0, A1_FULL = NU, S1_DONE = NU + 2, D1_FREE = NU + 4, B2_FULL = NU + 6, S2_DONE = NU + 8,
+       D2_FREE = NU + 10, NBARS = NU + 12 };
+// registers per thread after reallocation; the launch allocation is 96 x 640 (ptxas -v must say 96: a
+// smaller launch allocation makes setmaxnreg.inc wait for ever)
+constexpr int REGS_LAUNCH = 96, REGS_EPI = 176, REGS_TWD = 120, REGS_CNV = 72, REGS_MISC = 40;
+static_assert(128 * REGS_EPI + 128 * REGS_TWD + 256 * REGS_CNV + 128 * REGS_MISC <= NTHREADS * REGS_LAUNCH,
+              "register reallocation exceeds the launch allocation");
 }  // namespace tcw
 
 struct TcParams {
@@ -88,14 +106,14 @@ struct TcParams {
     const double* est;        // (mean, -) pairs: x first, then the y channels
     const double* prescale;   // power-of-two scale per channel, same order
     const unsigned char* consts;
-    const float* head;        // [nch+1][HEAD]: analysed samples j < head_len materialised (reflect zone)
-    int64_t head_len;         // segments that start before map.reflect read from head instead of x / y
+    const float* head;        // [nch+1][HEADP]: analysed samples j < head_len at [shift + j] (reflect zone)
+    int64_t head_len;         // blocks that start before head_len are copied from head instead of x / y
     float* partial;           // [nch][nparts][4][NBIN]
     int nparts;
-    float* lin_partial;       // [nch][nparts][4][L/16]  (zeroed by the host; bins < NLIN written)
+    float* lin_partial;       // [nch][nparts][4][L/16]  (bins < NLIN written)
     double* dev_sums;         // [nch+1]
     int* status;
-    long long* trace;         // debug: [batch][16] clock64 stamps of CTA (0, 0), or NULL
+    long long* trace;         // debug: per-CTA start / end stamps and the time line of CTA (0, 0), or NULL
 };
 
 __device__ __forceinline__ uint32_t pack_h2(float a, float b) {
@@ -103,18 +121,32 @@ __device__ __forceinline__ uint32_t pack_h2(float a, float b) {
     return *reinterpret_cast<uint32_t*>(&h);
 }
 
-#define PYFFT_TC_TRACE(EV, B) \
-    if (trace_on) p.trace[(B) * 16 + (EV)] = clock64();
+// float offset (0..3) of the sample at `p` inside its 16-byte line
+__host__ __device__ __forceinline__ int align_shift(const float* p) { return (int)((reinterpret_cast<uintptr_t>(p) & 15) >> 2); }
 
-// one cross-spectral update of a lane's accumulators for bin slot k1
-#define PYFFT_TC_ACC(K1, XX, YY)                                              \
-    {                                                                         \
-        const float xo_ = __shfl_xor_sync(0xffffffffu, (XX), 1);              \
-        acc[K1][0] = fmaf((XX), (XX), acc[K1][0]);                            \
-        acc[K1][1] = fmaf((YY), (YY), acc[K1][1]);                            \
-        acc[K1][2] = fmaf((YY), (XX), acc[K1][2]);                            \
-        acc[K1][3] = fmaf((YY), xo_, acc[K1][3]);                             \
-    }
+// source sample of the analysed index j (outside the reflect zone) of a channel
+__host__ __device__ __forceinline__ const float* direct_ptr(const float* base, const RecMap& m, int64_t j) {
+    return base + (j - m.reflect + m.i0 - m.src_base);
+}
+
+__device__ __forceinline__ void bulk_load(uint32_t dst_smem, const void* src, uint32_t bytes, uint32_t mbar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst_smem), "l"(src), "r"(bytes), "r"(mbar) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t mbar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&v)[16]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+        ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]),
+          "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
+        : "memory");
+}
+
+// debug time line (tools/tc_trace.py): event EV of segment S of CTA (0, 0), stamped by one lane of a role
+#define PYFFT_TC_TRACE(EV, S) \
+    if (trace_on && (S) < 128) p.trace[(S) * 16 + (EV)] = clock64();
 
 __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcParams p) {
     using namespace tcw;
@@ -123,6 +155,7 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
     __shared__ __align__(8) unsigned long long bars[NBARS];
     __shared__ uint32_t tmem_slot;
     __shared__ int abort_store;
+    __shared__ int conv_prog[8];             // segments each converter warp has finished reading
 
     const uint32_t raw = (uint32_t)__cvta_generic_to_shared(smem_raw);
     const uint32_t pad = (1024u - (raw & 1023u)) & 1023u;
@@ -131,10 +164,10 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
     const uint32_t bar0 = (uint32_t)__cvta_generic_to_shared(&bars[0]);
     volatile int* abort_flag = &abort_store;
 
-    const int tid = threadIdx.x, warp = tid >> 5, wg = warp >> 2;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int pair = blockIdx.y;
-    const bool trace_on = p.trace != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && (tid & 31) == 0 &&
-                          ((tid & 127) == 0 || tid == 800);
+    const bool trace_on = p.trace != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && lane == 0 &&
+                          (warp == 0 || warp == 4 || warp == 8 || warp >= 16);
     if (p.trace != nullptr && tid == 0) {
         unsigned long long t_;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));
@@ -142,31 +175,29 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
         p.trace[2048 + 4 * (blockIdx.y * gridDim.x + blockIdx.x) + 2] = clock64();
     }
 
-    // ---- one-time setup: constants, window, barriers, tensor memory ---------------------- //
+    // ---- one-time setup: stage-1 matrix, barriers, tensor memory --------------------------- //
     {
         const uint4* src = reinterpret_cast<const uint4*>(p.consts);
         uint4* dst = reinterpret_cast<uint4*>(sm);
-        for (int i = tid; i < CONST_SMEM_BYTES / 16; i += NTHREADS) dst[i] = src[i];
-        float* sw = reinterpret_cast<float*>(sm + OFF_WIN);
-        for (int n = tid; n < L; n += NTHREADS) sw[(n & 63) * WIN_LD + (n >> 6)] = p.window[n];
+        for (int i = tid; i < 16384 / 16; i += NTHREADS) dst[i] = src[i];
+        uint4* b2 = reinterpret_cast<uint4*>(sm + OFF_B2);                     // rows 33..35, 69..79 stay zero
+        for (int i = tid; i < 2 * B2_BYTES / 16; i += NTHREADS) b2[i] = make_uint4(0, 0, 0, 0);
     }
     if (tid == 0) {
         abort_store = 0;
+        for (int i = 0; i < NU; ++i) mbar_init(bar0 + 8 * (RAW_FULL + i), 1);
 #pragma unroll
         for (int i = 0; i < 2; ++i) {
             mbar_init(bar0 + 8 * (A1_FULL + i), 256);
+            mbar_init(bar0 + 8 * (S1_DONE + i), 1);
+            mbar_init(bar0 + 8 * (D1_FREE + i), 128);
             mbar_init(bar0 + 8 * (B2_FULL + i), 128);
-            mbar_init(bar0 + 8 * (B2_FREE + i), 1);
             mbar_init(bar0 + 8 * (S2_DONE + i), 1);
             mbar_init(bar0 + 8 * (D2_FREE + i), 128);
         }
-#pragma unroll
-        for (int i = 0; i < 3; ++i) {
-            mbar_init(bar0 + 8 * (S1_DONE + i), 1);
-            mbar_init(bar0 + 8 * (D1_FREE + i), 128);
-        }
         fence_mbar_init();
     }
+    if (tid < 8) conv_prog[tid] = 0;
     if (warp == 0) tmem_alloc((uint32_t)__cvta_generic_to_shared(&tmem_slot), 512);
     fence_async_smem();
     tc_fence_before();
@@ -198,69 +229,80 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
 
     const int64_t c0 = (int64_t)blockIdx.x * p.chunk;
     const int64_t c1 = (c0 + p.chunk < p.seg_count) ? c0 + p.chunk : p.seg_count;
-    const int nb = c1 > c0 ? (int)((c1 - c0 + 1) >> 1) : 0;                  // batches of two segments
+    const int nseg = c1 > c0 ? (int)(c1 - c0) : 0;
+    const int m = (int)(p.hop >> 9);                                           // units per hop: 1, 2, 4 or 8
+    const int lm = 31 - __clz(m);
 
-    if (wg == 0) {
+    if (warp < 4) {
         // ================= epilogue: D2 -> cross-spectral sums in registers =================== //
         setmaxnreg_inc<REGS_EPI>();
-        const uint32_t tl = tbase + ((uint32_t)(warp * 32) << 16) + TM_D2;   // this warp's lane quarter
-        float acc[33][4];
-        float linx[NLIN], liny[NLIN];
+        const uint32_t tl = tbase + ((uint32_t)(warp * 32) << 16) + TM_D2;     // this warp's lane quarter
+        // pairs of neighbouring bins k1 = 2i, 2i+1 in one 64-bit register pair: packed FMAs
+        float2 axx[16], ayy[16], ayx[16], ayo[16];
+        float a32[4] = {0.f, 0.f, 0.f, 0.f};
+        float2 linx[NLIN / 2], liny[NLIN / 2];
 #pragma unroll
-        for (int k = 0; k < 33; ++k)
+        for (int i = 0; i < 16; ++i) axx[i] = ayy[i] = ayx[i] = ayo[i] = make_float2(0.f, 0.f);
 #pragma unroll
-            for (int q = 0; q < 4; ++q) acc[k][q] = 0.f;
-#pragma unroll
-        for (int k = 0; k < NLIN; ++k) { linx[k] = 0.f; liny[k] = 0.f; }
+        for (int i = 0; i < NLIN / 2; ++i) linx[i] = liny[i] = make_float2(0.f, 0.f);
 
-        bool live = true;
 #pragma unroll 1
-        for (int b = 0; b < nb && live; ++b) {
-#pragma unroll 1                                             // keeps the loop body small for the instruction cache
-            for (int sg = 0; sg < SEGS; ++sg) {
-                if (sg == 0) {
-                    if (!mbar_wait_hot(bar0 + 8 * S2_DONE, (uint32_t)b & 1u, abort_flag)) { live = false; break; }
-                    tc_fence_after();
-                    PYFFT_TC_TRACE(10, b)
+        for (int s = 0; s < nseg; ++s) {
+            const int slot = s & 1;
+            if (!mbar_wait_hot(bar0 + 8 * (S2_DONE + slot), (uint32_t)(s >> 1) & 1u, abort_flag)) break;
+            tc_fence_after();
+            PYFFT_TC_TRACE(9, s)
+            const uint32_t col = tl + slot * NCOL;
+            float xa[8], ya[8], xb[8], yb[8];
+            tmem_ld8(col, xa);
+            tmem_ld8(col + YOFF, ya);
+            tmem_ld_wait();
+            tmem_ld8(col + 8, xb);
+            tmem_ld8(col + YOFF + 8, yb);
+#define PYFFT_TC_ACC4(BASE, XV, YV)                                                                      \
+    _Pragma("unroll") for (int i = 0; i < 4; ++i) {                                                      \
+        const float2 x2 = make_float2(XV[2 * i], XV[2 * i + 1]), y2 = make_float2(YV[2 * i], YV[2 * i + 1]); \
+        const float2 o2 = make_float2(__shfl_xor_sync(0xffffffffu, XV[2 * i], 1),                        \
+                                      __shfl_xor_sync(0xffffffffu, XV[2 * i + 1], 1));                   \
+        axx[BASE + i] = __ffma2_rn(x2, x2, axx[BASE + i]);                                               \
+        ayy[BASE + i] = __ffma2_rn(y2, y2, ayy[BASE + i]);                                               \
+        ayx[BASE + i] = __ffma2_rn(y2, x2, ayx[BASE + i]);                                               \
+        ayo[BASE + i] = __ffma2_rn(y2, o2, ayo[BASE + i]);                                               \
+    }
+            PYFFT_TC_ACC4(0, xa, ya)
+            if (warp == 0) {                                  // bins f < 8 live in lanes k2 = 0 of warp 0
+#pragma unroll
+                for (int i = 0; i < NLIN / 2; ++i) {
+                    linx[i] = __fadd2_rn(linx[i], make_float2(xa[2 * i], xa[2 * i + 1]));
+                    liny[i] = __fadd2_rn(liny[i], make_float2(ya[2 * i], ya[2 * i + 1]));
                 }
-                const uint32_t col = tl + sg * COLS_PER_SEG;
-                // software pipeline over chunks of 8 bins: the next chunk is in flight during the FMAs
-                float xa[8], ya[8], xb[8], yb[8];
-                tmem_ld8(col, xa);
-                tmem_ld8(col + YOFF, ya);
-                tmem_ld_wait();
-                tmem_ld8(col + 8, xb);
-                tmem_ld8(col + YOFF + 8, yb);
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    PYFFT_TC_ACC(i, xa[i], ya[i]);
-                    if (i < NLIN) { linx[i] += xa[i]; liny[i] += ya[i]; }
-                }
-                tmem_ld_wait();
-                tmem_ld8(col + 16, xa);
-                tmem_ld8(col + YOFF + 16, ya);
-#pragma unroll
-                for (int i = 0; i < 8; ++i) PYFFT_TC_ACC(8 + i, xb[i], yb[i]);
-                tmem_ld_wait();
-                tmem_ld8(col + 24, xb);
-                tmem_ld8(col + YOFF + 24, yb);
-#pragma unroll
-                for (int i = 0; i < 8; ++i) PYFFT_TC_ACC(16 + i, xa[i], ya[i]);
-                tmem_ld_wait();
-                float x32, y32, d0, d1;
-                tmem_ld2(col + 32, x32, d0);
-                tmem_ld2(col + YOFF + 32, y32, d1);
-#pragma unroll
-                for (int i = 0; i < 8; ++i) PYFFT_TC_ACC(24 + i, xb[i], yb[i]);
-                tmem_ld_wait();
-                if (sg == SEGS - 1) {                                        // D2 is in registers now
-                    tc_fence_before();
-                    mbar_arrive(bar0 + 8 * D2_FREE);
-                    PYFFT_TC_TRACE(11, b)
-                }
-                PYFFT_TC_ACC(32, x32, y32);
+            }
+            tmem_ld_wait();
+            tmem_ld8(col + 16, xa);
+            tmem_ld8(col + YOFF + 16, ya);
+            PYFFT_TC_ACC4(4, xb, yb)
+            tmem_ld_wait();
+            tmem_ld8(col + 24, xb);
+            tmem_ld8(col + YOFF + 24, yb);
+            PYFFT_TC_ACC4(8, xa, ya)
+            tmem_ld_wait();
+            float x32, y32, d0, d1;
+            tmem_ld2(col + 32, x32, d0);
+            tmem_ld2(col + YOFF + 32, y32, d1);
+            PYFFT_TC_ACC4(12, xb, yb)
+            tmem_ld_wait();
+            tc_fence_before();                                // D2 is in registers now
+            mbar_arrive(bar0 + 8 * (D2_FREE + slot));
+            PYFFT_TC_TRACE(10, s)
+            {
+                const float xo = __shfl_xor_sync(0xffffffffu, x32, 1);
+                a32[0] = fmaf(x32, x32, a32[0]);
+                a32[1] = fmaf(y32, y32, a32[1]);
+                a32[2] = fmaf(y32, x32, a32[2]);
+                a32[3] = fmaf(y32, xo, a32[3]);
             }
         }
+#undef PYFFT_TC_ACC4
 
         // ---- write the CTA's partial sums ---------------------------------------------------- //
         const float sx = (float)p.prescale[0], sy = (float)p.prescale[1 + pair];
@@ -269,12 +311,16 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
         float* out = p.partial + ((size_t)pair * p.nparts + blockIdx.x) * 4 * NBIN;
 #pragma unroll
         for (int k1 = 0; k1 <= 32; ++k1) {
-            const float t0 = acc[k1][0] + __shfl_xor_sync(0xffffffffu, acc[k1][0], 1);
-            const float t1 = acc[k1][1] + __shfl_xor_sync(0xffffffffu, acc[k1][1], 1);
-            const float t2 = acc[k1][2] + __shfl_xor_sync(0xffffffffu, acc[k1][2], 1);
-            const float o3 = __shfl_xor_sync(0xffffffffu, acc[k1][3], 1);
-            // even lane: acc3 = sum Yr Xi, partner's = sum Yi Xr  ->  Im(Y conj X) = Yi Xr - Yr Xi
-            float t3 = o3 - acc[k1][3];
+            const float v0 = k1 == 32 ? a32[0] : ((k1 & 1) ? axx[k1 >> 1 & 15].y : axx[k1 >> 1 & 15].x);
+            const float v1 = k1 == 32 ? a32[1] : ((k1 & 1) ? ayy[k1 >> 1 & 15].y : ayy[k1 >> 1 & 15].x);
+            const float v2 = k1 == 32 ? a32[2] : ((k1 & 1) ? ayx[k1 >> 1 & 15].y : ayx[k1 >> 1 & 15].x);
+            const float v3 = k1 == 32 ? a32[3] : ((k1 & 1) ? ayo[k1 >> 1 & 15].y : ayo[k1 >> 1 & 15].x);
+            const float t0 = v0 + __shfl_xor_sync(0xffffffffu, v0, 1);
+            const float t1 = v1 + __shfl_xor_sync(0xffffffffu, v1, 1);
+            const float t2 = v2 + __shfl_xor_sync(0xffffffffu, v2, 1);
+            const float o3 = __shfl_xor_sync(0xffffffffu, v3, 1);
+            // even lane: v3 = sum Yr Xi, partner's = sum Yi Xr  ->  Im(Y conj X) = Yi Xr - Yr Xi
+            float t3 = o3 - v3;
             if (c == 0) {
                 int f = k1 + 64 * k2;
                 bool wr = true;
@@ -295,240 +341,252 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
             float* lo = p.lin_partial + ((size_t)pair * p.nparts + blockIdx.x) * 4 * (L / 16);
 #pragma unroll
             for (int k1 = 0; k1 < NLIN; ++k1) {
-                lo[(0 + c) * (L / 16) + k1] = linx[k1] / sx;       // rows 0/1: Re/Im sum U
-                lo[(2 + c) * (L / 16) + k1] = liny[k1] / sy;       // rows 2/3: Re/Im sum V
+                lo[(0 + c) * (L / 16) + k1] = ((k1 & 1) ? linx[k1 >> 1].y : linx[k1 >> 1].x) / sx;   // rows 0/1: Re/Im sum U
+                lo[(2 + c) * (L / 16) + k1] = ((k1 & 1) ? liny[k1 >> 1].y : liny[k1 >> 1].x) / sy;   // rows 2/3: Re/Im sum V
             }
         }
-    } else if (wg == 1) {
+    } else if (warp < 8) {
         // ================= twiddle: D1 -> W_4096^(n2 k1) -> fp16 -> stage-2 operand ========== //
-        // Both segments of a batch in lock-step (each twiddle factor is read once for the two), in
-        // groups of 4 k1 with the next group's TMEM loads in flight during the arithmetic.
-        setmaxnreg_dec<REGS_TWD>();
+        // Thread = TMEM lane = row (ch, n2) of D1; its 33 twiddle factors stay in registers as pairs of
+        // neighbouring k1, so a pair of outputs costs four packed f32x2 operations.
+        setmaxnreg_inc<REGS_TWD>();
         const int ln = tid - 128;                                            // TMEM lane = row (ch, n2) of D1
         const int ch = ln >> 6, n2 = ln & 63;
         const uint32_t tl = tbase + ((uint32_t)((warp & 3) * 32) << 16) + TM_D1;
-        const float2* __restrict__ tw = reinterpret_cast<const float2*>(sm + OFF_TW) + n2;
-        // row r = sg*72 + ch*36 + k1 of the operand; 8-row groups are contiguous, so the row offset
-        // is r*128 and only the 16-byte chunk index is XOR-ed with r & 7 = (k1 + 4 ch) & 7
-        const uint32_t thread_off = (uint32_t)((n2 >> 5) * (N2 * 128) + (n2 & 3) * 4 + ch * YOFF * 128);   // inside a segment block
-        const uint32_t xbase = (uint32_t)((((n2 & 31) >> 2) ^ (4 * ch)) << 4);   // chunk ^ (k1 & 7) = xbase ^ (i << 4)
+        float2 wc[16], ws[16];                                               // (cos, cos), (-sin, -sin) of k1 = 2i, 2i+1
+        float2 w32;
+        {
+            const float2* __restrict__ tw = reinterpret_cast<const float2*>(p.consts + OFF_TW) + n2;
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                const float2 t0 = tw[(2 * i) * 64], t1 = tw[(2 * i + 1) * 64];
+                wc[i] = make_float2(t0.x, t1.x);
+                ws[i] = make_float2(t0.y, t1.y);
+            }
+            w32 = tw[32 * 64];
+        }
+        // row r = ch*36 + k1 of the operand; 8-row groups are contiguous, so the row offset is r*128 and
+        // only the 16-byte chunk index is XOR-ed with r & 7 = (k1 + 4 ch) & 7
+        const uint32_t thread_off = (uint32_t)((n2 >> 5) * B2_ATOM + (n2 & 3) * 4 + ch * YOFF * 128);
+        const uint32_t xbase = (uint32_t)((((n2 & 31) >> 2) ^ (4 * ch)) << 4);   // chunk ^ (k1 & 7) = xbase ^ ((k1 & 7) << 4)
 
 #pragma unroll 1
-        for (int b = 0; b < nb; ++b) {
-            const int s = b & 1;
-            const int s0 = 2 * b, s1 = 2 * b + 1;                            // segment indices; D1 slot = index % 3
-            const int d0 = s0 % 3, d1 = s1 % 3;
-            // the stage-2 MMAs of batch b-2 have finished reading this B2 slot
-            if (b >= 2 && !mbar_wait_hot(bar0 + 8 * (B2_FREE + s), ((uint32_t)(b >> 1) & 1u) ^ 1u, abort_flag)) break;
-            // stage 1 of the batch's second segment done implies the first one (same issuing thread,
-            // the tensor pipe completes in order)
-            PYFFT_TC_TRACE(7, b)
-            if (!mbar_wait_hot(bar0 + 8 * (S1_DONE + d1), (uint32_t)(s1 / 3) & 1u, abort_flag)) break;
+        for (int s = 0; s < nseg; ++s) {
+            const int slot = s & 1;
+            // the stage-2 MMAs of segment s-2 have finished reading this B2 slot
+            if (s >= 2 && !mbar_wait_hot(bar0 + 8 * (S2_DONE + slot), ((uint32_t)(s >> 1) & 1u) ^ 1u, abort_flag)) break;
+            if (!mbar_wait_hot(bar0 + 8 * (S1_DONE + slot), (uint32_t)(s >> 1) & 1u, abort_flag)) break;
             tc_fence_after();
-            PYFFT_TC_TRACE(8, b)
-            const uint32_t ca = tl + d0 * 64, cb = tl + d1 * 64;
-            unsigned char* bp = sm + OFF_B2 + s * B2_BYTES + thread_off;     // segment 1: + B2_SEG_BYTES
-            // group buffers: [0..3] Re seg 0, [4..7] Im seg 0, [8..11] Re seg 1, [12..15] Im seg 1
-            float ga[16], gb[16];
-            tmem_ld4(ca, &ga[0]);
-            tmem_ld4(ca + 32, &ga[4]);                    // first value = Re A1[32]; Im A1[0] = 0
-            tmem_ld4(cb, &ga[8]);
-            tmem_ld4(cb + 32, &ga[12]);
+            PYFFT_TC_TRACE(5, s)
+            const uint32_t ca = tl + slot * 64;
+            unsigned char* bp = sm + OFF_B2 + slot * B2_BYTES + thread_off;
+            float ra[8], ia[8], rb[8], ib[8];
+            tmem_ld8(ca, ra);
+            tmem_ld8(ca + 32, ia);                        // first value = Re A1[32]; Im A1[0] = 0
             tmem_ld_wait();
-            const float re32a = ga[4], re32b = ga[12];
-            ga[4] = 0.f;
-            ga[12] = 0.f;
+            const float re32 = ia[0];
+            ia[0] = 0.f;
+#define PYFFT_TC_TWD(J, RV, IV)                                                                          \
+    _Pragma("unroll") for (int i = 0; i < 4; ++i) {                                                      \
+        const float2 a2 = make_float2(RV[2 * i], RV[2 * i + 1]), b2 = make_float2(IV[2 * i], IV[2 * i + 1]); \
+        const float2 t2 = __fmul2_rn(b2, ws[4 * (J) + i]);                                               \
+        const float2 re = __ffma2_rn(a2, wc[4 * (J) + i], make_float2(-t2.x, -t2.y));                    \
+        const float2 im = __ffma2_rn(a2, ws[4 * (J) + i], __fmul2_rn(b2, wc[4 * (J) + i]));              \
+        const int k1 = 8 * (J) + 2 * i;                                                                  \
+        *reinterpret_cast<uint32_t*>(bp + k1 * 128 + (xbase ^ (uint32_t)((k1 & 7) << 4))) = pack_h2(re.x, im.x);           \
+        *reinterpret_cast<uint32_t*>(bp + (k1 + 1) * 128 + (xbase ^ (uint32_t)(((k1 + 1) & 7) << 4))) = pack_h2(re.y, im.y); \
+    }
+            tmem_ld8(ca + 8, rb);
+            tmem_ld8(ca + 40, ib);
+            PYFFT_TC_TWD(0, ra, ia)
+            tmem_ld_wait();
+            tmem_ld8(ca + 16, ra);
+            tmem_ld8(ca + 48, ia);
+            PYFFT_TC_TWD(1, rb, ib)
+            tmem_ld_wait();
+            tmem_ld8(ca + 24, rb);
+            tmem_ld8(ca + 56, ib);
+            PYFFT_TC_TWD(2, ra, ia)
+            tmem_ld_wait();
+            tc_fence_before();                            // the last D1 columns are in registers: slot free
+            mbar_arrive(bar0 + 8 * (D1_FREE + slot));
+            PYFFT_TC_TWD(3, rb, ib)
+            *reinterpret_cast<uint32_t*>(bp + 32 * 128 + xbase) = pack_h2(re32 * w32.x, re32 * w32.y);
+            fence_async_smem();
+            mbar_arrive(bar0 + 8 * (B2_FULL + slot));
+            PYFFT_TC_TRACE(6, s)
+        }
+#undef PYFFT_TC_TWD
+    } else if (warp < 16) {
+        // ================= converters: ring -> detrend -> window -> fp16 -> stage-1 operand (TMEM) ==== //
+        // Warp (q, h): TMEM lane quarter q (rows (ch, n2): ch = q >> 1, n2 = 32 (q & 1) + lane) and the half
+        // n1 = 32 h .. 32 h + 31 of the row = units 4 h .. 4 h + 3 of the segment = TMEM columns 16 h .. 16 h + 15.
+        setmaxnreg_dec<REGS_CNV>();
+        const int cw = warp - 8, q = cw & 3, h = cw >> 2;
+        const int ch = q >> 1, n2 = 32 * (q & 1) + lane;
+        const float* __restrict__ xsrc = ch ? p.y + (int64_t)pair * p.y_stride : p.x;
+        const int csel = ch ? 1 + pair : 0;
+        const float sc = (float)p.prescale[csel];
+        const float nm = -(float)p.est[2 * csel];
+        const int dsh = align_shift(direct_ptr(xsrc, p.map, 0));             // the same for every block (hops are multiples of 4)
+        float2 w2[16];                                                       // window * scale of n1 = 32 h + 2 i, + 1
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {                 // k1 = 4j .. 4j+3
-                const float* cur = (j & 1) ? gb : ga;
-                float* nxt = (j & 1) ? ga : gb;
-                if (j < 7) {
-                    tmem_ld4(ca + 4 * (j + 1), &nxt[0]);
-                    tmem_ld4(ca + 32 + 4 * (j + 1), &nxt[4]);
-                    tmem_ld4(cb + 4 * (j + 1), &nxt[8]);
-                    tmem_ld4(cb + 32 + 4 * (j + 1), &nxt[12]);
+        for (int i = 0; i < 16; ++i)
+            w2[i] = make_float2(p.window[64 * (32 * h + 2 * i) + n2] * sc, p.window[64 * (32 * h + 2 * i + 1) + n2] * sc);
+        const float2 nm2 = make_float2(nm, nm);
+        const float* ring = reinterpret_cast<const float*>(sm + OFF_RING) + ch * RING_CH_FLOATS + dsh + n2;
+        const uint32_t ta = tbase + ((uint32_t)(q * 32) << 16) + TM_A1 + 16 * h;
+        const int bpitch = m * UNIT + 4;                                     // floats per block of the ring
+        const int nblk = NU >> lm;                                           // blocks in the ring
+        float2 sum2 = make_float2(0.f, 0.f);
+
+#pragma unroll 1
+        for (int s = 0; s < nseg; ++s) {
+            const int slot = s & 1;
+            uint32_t pk[16];
+            bool live = true;
+            PYFFT_TC_TRACE(0, s)
+#pragma unroll
+            for (int a = 0; a < 4; ++a) {
+                const int U = s * m + 4 * h + a;                             // unit index inside the CTA's span
+                const int blk = U >> lm, bs = blk & (nblk - 1);              // its block and the block's ring slot
+                if (!mbar_wait_abortable<32>(bar0 + 8 * (RAW_FULL + bs), (uint32_t)(blk >> (5 - lm)) & 1u, abort_flag)) {
+                    live = false;
+                    break;
                 }
+                const float* up = ring + bs * bpitch + (U & (m - 1)) * UNIT;
+                float v[8];
+#pragma unroll
+                for (int b = 0; b < 8; ++b) v[b] = up[64 * b];
                 float2 t[4];
 #pragma unroll
-                for (int i = 0; i < 4; ++i) t[i] = tw[(4 * j + i) * 64];
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const uint32_t off = (uint32_t)((4 * j + i) * 128) + (xbase ^ (uint32_t)(((4 * j + i) & 7) << 4));
-                    *reinterpret_cast<uint32_t*>(bp + off) =
-                        pack_h2(cur[i] * t[i].x - cur[4 + i] * t[i].y, cur[i] * t[i].y + cur[4 + i] * t[i].x);
-                    *reinterpret_cast<uint32_t*>(bp + B2_SEG_BYTES + off) =
-                        pack_h2(cur[8 + i] * t[i].x - cur[12 + i] * t[i].y, cur[8 + i] * t[i].y + cur[12 + i] * t[i].x);
+                for (int b = 0; b < 4; ++b) t[b] = __fadd2_rn(make_float2(v[2 * b], v[2 * b + 1]), nm2);
+                if (4 * h + a < m) {                                         // the part of the segment inside its hop
+                    sum2 = __fadd2_rn(sum2, __fadd2_rn(__fadd2_rn(t[0], t[1]), __fadd2_rn(t[2], t[3])));
                 }
-                if (j < 7) tmem_ld_wait();
-                if (j == 6) {                             // the last D1 columns are in registers: slots free
-                    tc_fence_before();
-                    mbar_arrive(bar0 + 8 * (D1_FREE + d0));
-                    mbar_arrive(bar0 + 8 * (D1_FREE + d1));
+#pragma unroll
+                for (int b = 0; b < 4; ++b) {
+                    const float2 o = __fmul2_rn(t[b], w2[4 * a + b]);
+                    pk[4 * a + b] = pack_h2(o.x, o.y);
                 }
             }
-            {
-                const float2 t32 = tw[32 * 64];
-                *reinterpret_cast<uint32_t*>(bp + 32 * 128 + xbase) = pack_h2(re32a * t32.x, re32a * t32.y);
-                *reinterpret_cast<uint32_t*>(bp + B2_SEG_BYTES + 32 * 128 + xbase) = pack_h2(re32b * t32.x, re32b * t32.y);
-            }
-            fence_async_smem();
-            mbar_arrive(bar0 + 8 * (B2_FULL + s));
-            PYFFT_TC_TRACE(9, b)
+            if (!live) break;
+            PYFFT_TC_TRACE(1, s)
+            // the stage-1 MMAs of segment s-2 have finished reading this A1 slot
+            if (s >= 2 && !mbar_wait_abortable<32>(bar0 + 8 * (S1_DONE + slot), ((uint32_t)(s >> 1) & 1u) ^ 1u, abort_flag)) break;
+            tc_fence_after();
+            tmem_st16(ta + 32 * slot, pk);
+            tmem_st_wait();
+            tc_fence_before();
+            mbar_arrive(bar0 + 8 * (A1_FULL + slot));
+            PYFFT_TC_TRACE(2, s)
+            __syncwarp();
+            if (lane == 0) *reinterpret_cast<volatile int*>(&conv_prog[cw]) = s + 1;
         }
-    } else if (wg <= 5) {
-        // ================= loaders: gather -> detrend -> window -> fp16 -> stage-1 operand ==== //
-        // Two sets of 8 warps; set g takes the segments of parity g and owns A1 slot g.  Thread
-        // (quarter, n2) converts the 16 samples n = 64 (16 quarter + i) + n2 of BOTH channels, so each
-        // window value is read once for the two.  The loads of the set's next segment are issued
-        // before it waits for the slot: their latency overlaps the stage-1 MMAs of the previous batch
-        // and the other set's conversion.
-        setmaxnreg_dec<REGS_LDR>();
-        const int lt = tid - 256;
-        const int g = lt >> 8;                                               // set = segment parity = A1 slot
-        const int qt = (lt >> 6) & 3, n2 = lt & 63;
-        const float* __restrict__ ysrc = p.y + (int64_t)pair * p.y_stride;
-        const float scx = (float)p.prescale[0], scy = (float)p.prescale[1 + pair];
-        const float nmx = -(float)p.est[0] * scx, nmy = -(float)p.est[2 * (1 + pair)] * scy;   // exact: powers of two
-        const float4* __restrict__ wrow =
-            reinterpret_cast<const float4*>(sm + OFF_WIN + n2 * (WIN_LD * 4) + qt * 64);
-        // rows n2 (x) and 64 + n2 (y) of the slot, 16-byte chunks 2 qt and 2 qt + 1
-        unsigned char* rowx = sm + OFF_A1 + g * A1_BYTES + (n2 >> 3) * 1024 + (n2 & 7) * 128;
-        const uint32_t ck0 = (uint32_t)(((2 * qt) ^ (n2 & 7)) << 4), ck1 = (uint32_t)(((2 * qt + 1) ^ (n2 & 7)) << 4);
-        const int hb = (int)(p.hop >> 9) - 2 * qt;                           // chunks of this quarter inside the hop
-        const float in0 = hb > 0 ? 1.f : 0.f, in1 = hb > 1 ? 1.f : 0.f;
-        // segments that start in the reflect-padded zone read the materialised head of the record
-        const int64_t poff = p.map.i0 - p.map.reflect - p.map.src_base + n2 + 1024 * qt;
-        const float* __restrict__ hx = p.head + n2 + 1024 * qt;
-        const float* __restrict__ hy = hx + (int64_t)(1 + pair) * HEAD;
-        // L2 prefetch two segments of this set ahead: 128 lines of 128 bytes per channel; threads
-        // (qt, n2 < 32) take line qt*32 + n2 of x, threads n2 >= 32 the same line of y
-        const float* pf = (n2 < 32 ? p.x : ysrc) + (p.map.i0 - p.map.reflect - p.map.src_base) + (qt * 32 + (n2 & 31)) * 32;
-        const int64_t first = p.seg_first + c0 + g;
-        float sumx = 0.f, sumy = 0.f;
-
-#pragma unroll 1
-        for (int b = 0; b < nb; ++b) {
-            const bool have = c0 + 2 * b + g < c1;
-            float vx[16], vy[16];
-            if (have) {
-                const int64_t j0 = (first + 2 * b) * p.hop;
-                const bool zone = j0 < p.map.reflect;
-                const float* __restrict__ qx = zone ? hx + j0 : p.x + (j0 + poff);
-                const float* __restrict__ qy = zone ? hy + j0 : ysrc + (j0 + poff);
+        double dsum = (double)sum2.x + (double)sum2.y;
 #pragma unroll
-                for (int i = 0; i < 16; ++i) vx[i] = qx[64 * i];
-#pragma unroll
-                for (int i = 0; i < 16; ++i) vy[i] = qy[64 * i];
-                if (c0 + 2 * b + g + 4 < c1) {
-                    const int64_t jn = (first + 2 * b + 4) * p.hop;
-                    if (jn >= p.map.reflect) asm volatile("prefetch.global.L2 [%0];" ::"l"(pf + jn));
-                }
-            } else {
-#pragma unroll
-                for (int i = 0; i < 16; ++i) { vx[i] = 0.f; vy[i] = 0.f; }
-            }
-            // the stage-1 MMAs of this set's previous segment have finished reading the A1 slot
-            if (b >= 1) {
-                const int sp = 2 * (b - 1) + g;
-                if (!mbar_wait_abortable<200>(bar0 + 8 * (S1_DONE + sp % 3), (uint32_t)(sp / 3) & 1u, abort_flag)) break;
-            }
-            if (qt == 0) { PYFFT_TC_TRACE(2 * g, b) }
-#pragma unroll
-            for (int c = 0; c < 2; ++c) {
-                float* ux = vx + 8 * c;
-                float* uy = vy + 8 * c;
-                const float4 w0 = wrow[2 * c], w1 = wrow[2 * c + 1];
-#pragma unroll
-                for (int i = 0; i < 8; ++i) { ux[i] = fmaf(ux[i], scx, nmx); uy[i] = fmaf(uy[i], scy, nmy); }   // (x - mean) * scale
-                if (have) {
-                    const float in = c ? in1 : in0;
-                    sumx = fmaf(in, ((ux[0] + ux[1]) + (ux[2] + ux[3])) + ((ux[4] + ux[5]) + (ux[6] + ux[7])), sumx);
-                    sumy = fmaf(in, ((uy[0] + uy[1]) + (uy[2] + uy[3])) + ((uy[4] + uy[5]) + (uy[6] + uy[7])), sumy);
-                }
-                uint4 ox, oy;
-                ox.x = pack_h2(ux[0] * w0.x, ux[1] * w0.y); ox.y = pack_h2(ux[2] * w0.z, ux[3] * w0.w);
-                ox.z = pack_h2(ux[4] * w1.x, ux[5] * w1.y); ox.w = pack_h2(ux[6] * w1.z, ux[7] * w1.w);
-                oy.x = pack_h2(uy[0] * w0.x, uy[1] * w0.y); oy.y = pack_h2(uy[2] * w0.z, uy[3] * w0.w);
-                oy.z = pack_h2(uy[4] * w1.x, uy[5] * w1.y); oy.w = pack_h2(uy[6] * w1.z, uy[7] * w1.w);
-                if (!have) { ox = make_uint4(0, 0, 0, 0); oy = ox; }
-                *reinterpret_cast<uint4*>(rowx + (c ? ck1 : ck0)) = ox;
-                *reinterpret_cast<uint4*>(rowx + 8192 + (c ? ck1 : ck0)) = oy;
-            }
-            fence_async_smem();
-            mbar_arrive(bar0 + 8 * (A1_FULL + g));
-            if (qt == 0) { PYFFT_TC_TRACE(2 * g + 1, b) }
-        }
-        double dx = (double)sumx / (double)scx, dy = (double)sumy / (double)scy;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            dx += __shfl_xor_sync(0xffffffffu, dx, o);
-            dy += __shfl_xor_sync(0xffffffffu, dy, o);
-        }
-        if ((tid & 31) == 0) {
-            if (pair == 0) atomicAdd(&p.dev_sums[0], dx);
-            atomicAdd(&p.dev_sums[1 + pair], dy);
-        }
+        for (int o = 16; o > 0; o >>= 1) dsum += __shfl_xor_sync(0xffffffffu, dsum, o);
+        // sum2 = sum of (x - provisional mean), unscaled: the window carries the power-of-two scale
+        if (lane == 0 && (ch == 1 || pair == 0)) atomicAdd(&p.dev_sums[csel], dsum);
     } else {
-        // ================= MMA issue: one thread per GEMM stage ================================ //
-        // Two warps so that the two serial instruction streams (waits, descriptors, issue) run on
-        // different schedulers; the stages only meet through the mbarriers.
-        setmaxnreg_dec<REGS_MMA>();
-        if (tid == 768) {
-            // stage 1: one 128 x 64 x 64 product (hi + lo) per segment
+        setmaxnreg_dec<REGS_MISC>();
+        if (tid == 512) {
+            // ================= TMA producer: one block (hop samples) of both channels per segment ====== //
+            const float* __restrict__ ysrc = p.y + (int64_t)pair * p.y_stride;
+            const int64_t jc = (p.seg_first + c0) * p.hop;                     // first analysed sample of the CTA
+            const int nblocks = nseg > 0 ? nseg - 1 + (8 >> lm) : 0;           // one block = one hop = m units
+            const int nblk = NU >> lm;                                         // blocks in the ring
+            const uint32_t bbytes = (uint32_t)(m * UNIT + 4) * 4;              // bytes of a block per channel
+            const int shx = align_shift(direct_ptr(p.x, p.map, 0));
+            const int shy = align_shift(direct_ptr(ysrc, p.map, 0));
+            const float* hx = p.head;
+            const float* hy = p.head + (int64_t)(1 + pair) * HEADP;
+            int done_seg = 0;                                                  // segments all converter warps have read
+            // running pointers: a lone thread runs ~4 clocks per dependent instruction
+            const float* dx_ = direct_ptr(p.x, p.map, jc) - shx;
+            const float* dy_ = direct_ptr(ysrc, p.map, jc) - shy;
+            int64_t j = jc;
+            const int tb = (8 >> lm) - 1;                                      // block B completes segment B - tb
+#pragma unroll 1
+            for (int B = 0; B < nblocks; ++B, j += p.hop, dx_ += p.hop, dy_ += p.hop) {
+                if (B >= nblk) {
+                    // block B - nblk is last read by segment B - nblk
+                    const int need = B - nblk + 1 < nseg ? B - nblk + 1 : nseg;
+                    bool live = true;
+                    while (done_seg < need) {
+                        const volatile int* cp = conv_prog;
+                        int mn = cp[0];
+#pragma unroll
+                        for (int i = 1; i < 8; ++i) { const int v = cp[i]; mn = v < mn ? v : mn; }
+                        done_seg = mn;
+                        if (done_seg < need) {
+                            if (*abort_flag) { live = false; break; }
+                            __nanosleep(64);
+                        }
+                    }
+                    if (!live) break;
+                }
+                const bool in_head = j < p.head_len;
+                const float* sx_ = in_head ? hx + j : dx_;
+                const float* sy_ = in_head ? hy + j : dy_;
+                const int bs = B & (nblk - 1);
+                const uint32_t bar = bar0 + 8 * (RAW_FULL + bs);
+                const uint32_t dst = sm_addr + OFF_RING + bs * bbytes;
+                mbar_expect_tx(bar, 2 * bbytes);
+                bulk_load(dst, sx_, bbytes, bar);
+                bulk_load(dst + RING_CH_FLOATS * 4, sy_, bbytes, bar);
+                if (B >= tb) { PYFFT_TC_TRACE(11, B - tb) }
+            }
+        } else if (tid == 544) {
+            // ================= stage 1: 128 x 64 x 64 (hi + lo) per segment, A from tensor memory == //
             constexpr uint32_t id1 = idesc_f16(128, 64);
             const uint32_t g_lo = sw128_desc_lo(sm_addr + OFF_GHI);
-            const int nseg = 2 * nb;
 #pragma unroll 1
-            for (int si = 0; si < nseg; ++si) {
-                const int g = si & 1, b = si >> 1, d = si % 3;                // A1 slot, batch, D1 slot
-                if (g == 0) { PYFFT_TC_TRACE(12, b) }
-                bool live = mbar_wait_hot(bar0 + 8 * (A1_FULL + g), (uint32_t)b & 1u, abort_flag);
-                if (si >= 3)
-                    live = live && mbar_wait_hot(bar0 + 8 * (D1_FREE + d), ((uint32_t)(si / 3) & 1u) ^ 1u, abort_flag);
+            for (int s = 0; s < nseg; ++s) {
+                const int slot = s & 1;
+                bool live = mbar_wait_hot(bar0 + 8 * (A1_FULL + slot), (uint32_t)(s >> 1) & 1u, abort_flag);
+                if (s >= 2)
+                    live = live && mbar_wait_hot(bar0 + 8 * (D1_FREE + slot), ((uint32_t)(s >> 1) & 1u) ^ 1u, abort_flag);
                 if (!live) break;
                 tc_fence_after();
-                if (g == 0) { PYFFT_TC_TRACE(13, b) }
-                const uint32_t a1 = sw128_desc_lo(sm_addr + OFF_A1 + g * A1_BYTES);
+                PYFFT_TC_TRACE(3, s)
 #pragma unroll
-                for (int h = 0; h < 2; ++h)
+                for (int hh = 0; hh < 2; ++hh)
 #pragma unroll
                     for (int ks = 0; ks < 4; ++ks)
-                        mma_f16_lo(tbase + TM_D1 + d * 64, a1 + ks * 2,
-                                   g_lo + (h ? (OFF_GLO - OFF_GHI) / 16 : 0) + ks * 2, id1, (h | ks) ? 1u : 0u);
-                mma_commit(bar0 + 8 * (S1_DONE + d));
-                PYFFT_TC_TRACE(4 + g, b)
+                        mma_f16_ts_lo(tbase + TM_D1 + slot * 64, tbase + TM_A1 + slot * 32 + ks * 8,
+                                      g_lo + (hh ? (OFF_GLO - OFF_GHI) / 16 : 0) + ks * 2, id1, (hh | ks) ? 1u : 0u);
+                mma_commit(bar0 + 8 * (S1_DONE + slot));
+                PYFFT_TC_TRACE(4, s)
             }
-        } else if (tid == 800) {
-            // stage 2: 128 x 144 x 128 (hi + lo) per batch; the matrix comes from tensor memory, only
-            // the data operand is read from shared memory
-            constexpr uint32_t id2 = idesc_f16(128, N2);
+        } else if (tid == 576 || tid == 608) {
+            // ================= stage 2: 128 x 80 x 128 (hi + lo) per segment; one thread per slot ===== //
+            constexpr uint32_t id2 = idesc_f16(128, NCOL);
+            const int slot = tid == 608 ? 1 : 0;
+            const uint32_t b2 = sw128_desc_lo(sm_addr + OFF_B2 + slot * B2_BYTES);
 #pragma unroll 1
-            for (int bb = 0; bb < nb; ++bb) {
-                const int s = bb & 1;
-                PYFFT_TC_TRACE(14, bb)
-                const uint32_t b2 = sw128_desc_lo(sm_addr + OFF_B2 + s * B2_BYTES);
-                // the operand is ready long before the epilogue has drained the single D2 slot
-                bool live = mbar_wait_hot(bar0 + 8 * (B2_FULL + s), (uint32_t)(bb >> 1) & 1u, abort_flag);
-                if (bb >= 1) live = live && mbar_wait_hot(bar0 + 8 * D2_FREE, (uint32_t)(bb - 1) & 1u, abort_flag);
+            for (int s = slot; s < nseg; s += 2) {
+                bool live = mbar_wait_hot(bar0 + 8 * (B2_FULL + slot), (uint32_t)(s >> 1) & 1u, abort_flag);
+                if (s >= 2)
+                    live = live && mbar_wait_hot(bar0 + 8 * (D2_FREE + slot), ((uint32_t)(s >> 1) & 1u) ^ 1u, abort_flag);
                 if (!live) break;
                 tc_fence_after();
-                PYFFT_TC_TRACE(15, bb)
+                PYFFT_TC_TRACE(7, s)
 #pragma unroll
-                for (int h = 0; h < 2; ++h)
+                for (int hh = 0; hh < 2; ++hh)
 #pragma unroll
                     for (int ks = 0; ks < 8; ++ks)
-                        mma_f16_ts_lo(tbase + TM_D2, tbase + (h ? TM_F2LO : TM_F2HI) + ks * 8,
-                                      b2 + ((ks >> 2) * (N2 * 128) + (ks & 3) * 32) / 16, id2, (h | ks) ? 1u : 0u);
-                mma_commit(bar0 + 8 * S2_DONE);
-                mma_commit(bar0 + 8 * (B2_FREE + s));
-                PYFFT_TC_TRACE(6, bb)
+                        mma_f16_ts_lo(tbase + TM_D2 + slot * NCOL, tbase + (hh ? TM_F2LO : TM_F2HI) + ks * 8,
+                                      b2 + ((ks >> 2) * B2_ATOM + (ks & 3) * 32) / 16, id2, (hh | ks) ? 1u : 0u);
+                mma_commit(bar0 + 8 * (S2_DONE + slot));
+                PYFFT_TC_TRACE(8, s)
             }
         }
     }
 
     tc_fence_before();
     __syncthreads();
-    if (tid == 0 && *abort_flag) atomicExch(p.status, 1);
+    if (tid == 0 && *abort_flag) atomicOr(p.status, 1);
     if (p.trace != nullptr && tid == 0) {
         unsigned long long t_;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));
@@ -537,13 +595,18 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
     }
     if (warp == 0) tmem_free(tbase, 512);
 }
-#undef PYFFT_TC_ACC
 #undef PYFFT_TC_TRACE
 
 // ------------------------------------------------------------------------- //
 // provisional statistics: mean (rounded to float) and a power-of-two scale that brings the
-// rms of (x - mean) to ~1/8, from the first samples of the span
+// rms of (x - mean) to ~1/8, from PREP_BLOCKS runs of PREP_RUN samples spread evenly over the span
+// (a record whose level changes along the way is scaled by its overall rms, not by its head)
 // ------------------------------------------------------------------------- //
+constexpr int PREP_BLOCKS = 64, PREP_RUN = 1024;
+__host__ __device__ __forceinline__ int64_t prep_stride(int64_t span) {
+    const int64_t st = span > PREP_RUN ? (span - PREP_RUN) / (PREP_BLOCKS - 1) : 0;
+    return st < PREP_RUN ? PREP_RUN : st;
+}
 // est[2c] += sum (x - x0), est[2c+1] += sum (x - x0)^2 with x0 = the first sample of the span; the
 // last block of a channel to finish (ticket in prescale[c], zeroed by the host) turns the sums into
 // est[2c] = mean (rounded to fp32), est[2c+1] = 0, prescale[c] = 2^k with rms * 2^k in [1/8, 1/4)
@@ -554,8 +617,9 @@ __global__ void __launch_bounds__(256) tc_prepare_kernel(const float* __restrict
     const float* p = c == 0 ? x : y + (int64_t)(c - 1) * y_stride;
     const double x0 = (double)p[src_index(map, j_begin)];
     double s0 = 0.0, s1 = 0.0;
-    const int64_t step = (int64_t)gridDim.x * 256;
-    for (int64_t j = j_begin + (int64_t)blockIdx.x * 256 + threadIdx.x; j < j_end; j += step) {
+    const int64_t stride = prep_stride(j_end - j_begin);
+    const int64_t r0 = j_begin + (int64_t)blockIdx.x * stride;
+    for (int64_t j = r0 + threadIdx.x; j < r0 + PREP_RUN && j < j_end; j += 256) {
         const double v = (double)p[src_index(map, j)] - x0;
         s0 += v;
         s1 += v * v;
@@ -577,7 +641,12 @@ __global__ void __launch_bounds__(256) tc_prepare_kernel(const float* __restrict
     __threadfence();
     if (atomicAdd(&prescale[c], 1.0) != (double)(gridDim.x - 1)) return;     // not the last block of the channel
     __threadfence();
-    const double n = (double)(j_end - j_begin);
+    int64_t cnt = 0;                                                          // samples the runs covered
+    for (int b = 0; b < PREP_BLOCKS; ++b) {
+        const int64_t lo = j_begin + (int64_t)b * stride, hi = lo + PREP_RUN < j_end ? lo + PREP_RUN : j_end;
+        if (hi > lo) cnt += hi - lo;
+    }
+    const double n = (double)cnt;
     const double md = atomicAdd(&est[2 * c], 0.0) / n;                         // read through L2
     double var = atomicAdd(&est[2 * c + 1], 0.0) / n - md * md;
     if (!(var > 0.0)) var = 0.0;
@@ -599,7 +668,7 @@ __global__ void __launch_bounds__(256) tc_finish_kernel(const float* __restrict_
                                                         const double* __restrict__ dev_sums,
                                                         const double* __restrict__ est, double count, int nch1,
                                                         double* __restrict__ acc, double* __restrict__ lin,
-                                                        double* __restrict__ stats) {
+                                                        double* __restrict__ stats, int* __restrict__ status) {
     using namespace tcw;
     constexpr int PER_PAIR = 4 * NBIN, MAIN_BLOCKS = (PER_PAIR + 31) / 32;
     const int lane = threadIdx.x & 31, g = threadIdx.x >> 5;
@@ -633,20 +702,24 @@ __global__ void __launch_bounds__(256) tc_finish_kernel(const float* __restrict_
 #pragma unroll
         for (int u = 0; u < 8; ++u) t += sh[u][lane];
         (is_lin ? lin : acc)[(size_t)pair * per + i] += t;
+        // an fp16 operand out of range (a record far louder than the sampled statistics said) shows as Inf / NaN
+        if (!isfinite(t)) atomicOr(status, 2);
     }
 }
 static_assert(tcw::NLIN == 8, "tc_finish_kernel maps 32 lanes onto 4 rows x 8 bins");
 
-// materialises the analysed samples j < n of every channel (the reflect-padded zone and the
-// segments that reach into it), so that the loaders never evaluate the record map
+// materialises the analysed samples j < n of every channel (the reflect-padded zone, whole blocks), so that
+// the TMA producer copies plain 16-byte-aligned runs: sample j of channel c sits at head[c][shift_c + j]
+// with shift_c = the offset of the channel's direct samples inside their 16-byte line (the converters use
+// one shift per channel for every block)
 __global__ void __launch_bounds__(256) tc_head_kernel(const float* __restrict__ x, const float* __restrict__ y,
-                                                      int64_t y_stride, int pair0, RecMap map, int64_t n,
+                                                      int64_t y_stride, RecMap map, int64_t n,
                                                       float* __restrict__ head) {
     const int c = blockIdx.y;                       // 0 = x, 1.. = y channels
     const float* p = c == 0 ? x : y + (int64_t)(c - 1) * y_stride;
+    const int sh = align_shift(direct_ptr(p, map, 0));
     const int64_t j = (int64_t)blockIdx.x * 256 + threadIdx.x;
-    if (j < n) head[(int64_t)c * tcw::HEAD + j] = p[src_index(map, j)];
-    (void)pair0;
+    if (j < n) head[(int64_t)c * tcw::HEADP + sh + j] = p[src_index(map, j)];
 }
 
 // ------------------------------------------------------------------------- //
@@ -721,8 +794,7 @@ static int tc_grid_x(int64_t seg_count, int nch) {
     int sms = device_sm_count();
     if (sms <= 0) sms = 148;
     int64_t want = (sms + nch - 1) / nch;
-    const int64_t maxb = (seg_count + tcw::SEGS - 1) / tcw::SEGS;
-    if (want > maxb) want = maxb;
+    if (want > seg_count) want = seg_count;
     if (want < 1) want = 1;
     return (int)want;
 }
@@ -744,7 +816,7 @@ int64_t pyfft_welch_tc_workspace_bytes(const pyfft_segmentation* seg, int32_t nc
     if (!seg || nch <= 0) return fail(PYFFT_EINVAL, "welch_tc_workspace_bytes: bad arguments");
     const int gx = tc_grid_x(seg->seg_count, nch);
     return (int64_t)nch * gx * 4 * (tcw::NBIN + tcw::L / 16) * 4 + 8 * (int64_t)(nch + 1) + 16 +
-           (int64_t)(nch + 1) * tcw::HEAD * 4;
+           (int64_t)(nch + 1) * tcw::HEADP * 4;
 }
 
 int pyfft_welch_tc_prepare(const void* x, const void* y, int64_t y_stride, int32_t nch,
@@ -759,9 +831,7 @@ int pyfft_welch_tc_prepare(const void* x, const void* y, int64_t y_stride, int32
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     PYFFT_CUDA_OK(cudaMemsetAsync(est, 0, sizeof(double) * 2 * (size_t)(nch + 1), st));
     PYFFT_CUDA_OK(cudaMemsetAsync(prescale, 0, sizeof(double) * (size_t)(nch + 1), st));
-    int gx = (int)((j_end - j_begin + 2047) / 2048);
-    if (gx > 64) gx = 64;
-    tc_prepare_kernel<<<dim3(gx, nch + 1), 256, 0, st>>>(static_cast<const float*>(x), static_cast<const float*>(y),
+    tc_prepare_kernel<<<dim3(PREP_BLOCKS, nch + 1), 256, 0, st>>>(static_cast<const float*>(x), static_cast<const float*>(y),
                                                         y_stride, m, j_begin, j_end, est, prescale);
     PYFFT_LAUNCH_OK("tc_prepare_kernel");
     return PYFFT_OK;
@@ -776,8 +846,8 @@ int pyfft_welch_accumulate_tc(const void* x, const void* y, int64_t y_stride, in
     int rc = check_map(map, &m);
     if (rc) return rc;
     if (!seg || seg->nfft != L) return fail(PYFFT_EUNSUPPORTED, "the tensor-core path handles nfft = 4096 only");
-    if (seg->hop <= 0 || seg->hop > L || (seg->hop & 511))
-        return fail(PYFFT_EUNSUPPORTED, "the tensor-core path needs a hop that is a multiple of 512 (got %d)", seg->hop);
+    if (seg->hop != 512 && seg->hop != 1024 && seg->hop != 2048 && seg->hop != 4096)
+        return fail(PYFFT_EUNSUPPORTED, "the tensor-core path needs a hop of 512, 1024, 2048 or 4096 samples (got %d)", seg->hop);
     if (!x || !y || !window || !est || !prescale || !acc || !lin || !stats || !status_flag || nch <= 0)
         return fail(PYFFT_EINVAL, "welch_accumulate_tc: NULL pointer or nch <= 0");
     if (seg->seg_count == 0) return PYFFT_OK;
@@ -793,18 +863,20 @@ int pyfft_welch_accumulate_tc(const void* x, const void* y, int64_t y_stride, in
     const int64_t main_bytes = (int64_t)nch * nparts * 4 * NBIN * 4;
     const int64_t lin_bytes = (int64_t)nch * nparts * 4 * (L / 16) * 4;
     const int64_t sums_bytes = (8 * (int64_t)(nch + 1) + 15) & ~(int64_t)15;
-    const int64_t head_bytes = (int64_t)(nch + 1) * HEAD * 4;
+    const int64_t head_bytes = (int64_t)(nch + 1) * HEADP * 4;
     if (!workspace || workspace_bytes < main_bytes + lin_bytes + sums_bytes + head_bytes)
         return fail(PYFFT_EINVAL, "welch_accumulate_tc: workspace too small");
-    // segments that start before map.reflect read a materialised copy of the head of the record
+    // blocks (one hop of analysed samples) that reach into the reflect-padded zone are copied from a
+    // materialised head of the record; every other block is a plain run of the source
     int64_t head_len = 0;
     if (j_lo < m.reflect) {
-        const int64_t last = (m.reflect - 1) / seg->hop;                        // last segment that starts in the zone
-        const int64_t last_here = last < seg->seg_first + seg->seg_count - 1 ? last : seg->seg_first + seg->seg_count - 1;
-        head_len = last_here * seg->hop + L;
+        head_len = (m.reflect + seg->hop - 1) / seg->hop * seg->hop;
+        if (head_len > m.nsig) head_len = m.nsig;
         if (head_len > HEAD)
-            return fail(PYFFT_EUNSUPPORTED, "the tensor-core path supports reflect padding up to %d samples", 2 * L - 1);
+            return fail(PYFFT_EUNSUPPORTED, "the tensor-core path supports reflect padding up to %d samples", HEAD);
     }
+    if (((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y) | (uintptr_t)(y_stride * 4)) & 3) != 0)
+        return fail(PYFFT_EINVAL, "welch_accumulate_tc: x / y must be 4-byte aligned");
     TcParams p;
     p.x = static_cast<const float*>(x);
     p.y = static_cast<const float*>(y);
@@ -813,10 +885,7 @@ int pyfft_welch_accumulate_tc(const void* x, const void* y, int64_t y_stride, in
     p.hop = seg->hop;
     p.seg_first = seg->seg_first;
     p.seg_count = seg->seg_count;
-    // chunk: a multiple of the batch size so that only the very last batch can be ragged
-    int64_t chunk = (seg->seg_count + gx - 1) / gx;
-    chunk = (chunk + SEGS - 1) / SEGS * SEGS;
-    p.chunk = chunk;
+    p.chunk = (seg->seg_count + gx - 1) / gx;
     p.window = static_cast<const float*>(window);
     p.est = est;
     p.prescale = prescale;
@@ -835,13 +904,13 @@ int pyfft_welch_accumulate_tc(const void* x, const void* y, int64_t y_stride, in
     PYFFT_CUDA_OK(cudaMemsetAsync(p.dev_sums, 0, sizeof(double) * (size_t)(nch + 1), st));
     if (head_len > 0)
         tc_head_kernel<<<dim3((unsigned)((head_len + 255) / 256), nch + 1), 256, 0, st>>>(
-            p.x, p.y, y_stride, 0, m, head_len, head);
+            p.x, p.y, y_stride, m, head_len, head);
     PYFFT_CUDA_OK(cudaFuncSetAttribute(welch_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
     welch_tc_kernel<<<dim3(gx, nch), NTHREADS, SMEM_BYTES, st>>>(p);
     PYFFT_LAUNCH_OK("welch_tc_kernel");
     tc_finish_kernel<<<dim3((4 * NBIN + 31) / 32 + 1, nch), 256, 0, st>>>(
         p.partial, p.lin_partial, nparts, p.dev_sums, est, (double)seg->seg_count * (double)seg->hop, nch + 1, acc, lin,
-        stats);
+        stats, status_flag);
     PYFFT_LAUNCH_OK("tc_finish_kernel");
     return PYFFT_OK;
 }

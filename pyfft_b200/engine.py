@@ -211,6 +211,7 @@ class WelchPlan(object):
         self.nlin = self.nfft // 16
         n_acc, n_lin, n_st = self.nch * 4 * self.nbin, self.nch * 4 * self.nlin, 2 * (self.nch + 1)
         self._peer = None                              # PeerReducer, False (unavailable) or None (not tried)
+        self._peer_group = None
         self.state = torch.zeros(n_acc + n_lin + n_st, dtype=torch.float64, device=self.device)
         self.acc = self.state[:n_acc].view(self.nch, 4, self.nbin)
         self.lin = self.state[n_acc:n_acc + n_lin].view(self.nch, 4, self.nlin)
@@ -228,11 +229,11 @@ class WelchPlan(object):
             np.stack([W.real[:self.nlin], W.imag[:self.nlin]], 1))).to(self.device)
         self.est = None
         self.K_local = 0
-        # tensor-core route (pyfft_welch_accumulate_tc): nfft 4096, fp32, hop % 512 == 0, window
+        # tensor-core route (pyfft_welch_accumulate_tc): nfft 4096, fp32, hop 512 / 1024 / 2048 / 4096, window
         # transform negligible beyond the 8 bins it keeps linear sums for
         leak8 = float(p[8:self.nfft // 2 + 1].max() / (win ** 2).sum()) if self.nfft == 4096 else 1.0
-        self.can_use_tc = (self.nfft == 4096 and precision == "fp32" and self.hop % 512 == 0
-                           and self.hop <= self.nfft and leak8 < 1e-9)
+        self.can_use_tc = (self.nfft == 4096 and precision == "fp32" and self.hop in (512, 1024, 2048, 4096)
+                           and leak8 < 1e-9)
         self.prescale = None
         self._tc_status = None
         self._zero_est = None
@@ -287,9 +288,10 @@ class WelchPlan(object):
         self.K_local += int(seg_count)
 
     # -- tensor-core route -------------------------------------------------- #
-    def prepare_tc(self, x, y, rmap, j_begin, j_end, nsample=65536):
-        """Provisional means and power-of-two scales from the head of the shard."""
-        j1 = min(j_end, j_begin + nsample)
+    def prepare_tc(self, x, y, rmap, j_begin, j_end):
+        """Provisional means and power-of-two scales from 64 runs of 1024 samples spread evenly over
+        the analysed indices [j_begin, j_end) of this shard."""
+        j1 = j_end
         if self._tc_est is None:                       # zeroed by the entry point itself
             self._tc_est = torch.empty(2 * (self.nch + 1), dtype=torch.float64, device=self.device)
             self.prescale = torch.empty(self.nch + 1, dtype=torch.float64, device=self.device)
@@ -339,13 +341,27 @@ class WelchPlan(object):
     def all_reduce_state(self, group=None):
         """The one collective of the sharded fused-mean route: acc | lin | stats in one buffer.
         Over NVLink peer memory (PeerReducer) when the group's GPUs can map each other's memory,
-        else NCCL."""
-        if self._peer is None:
+        else NCCL.  peer_status() is the device flag of the bounded waits (0 = fine)."""
+        gname = getattr(group, "group_name", None)
+        if self._peer is None or self._peer_group != gname:
             self._peer = PeerReducer.create(self.state.numel(), self.device, group)
+            self._peer_group = gname
         if self._peer:
             self._peer.all_reduce(self.state)
         else:
             torch.distributed.all_reduce(self.state, group=group)
+
+    def peer_status(self):
+        """Device int32 tensor raised by a timed-out NVLink reduction, or None (NCCL route / unsharded)."""
+        return self._peer.status if self._peer else None
+
+    def dynamic_range(self, res, onesided=True):
+        """-> (nch+1, 2) double device tensor: min and mean bin power of Pxx and of every Pyy column
+        (pyfft_welch_dynamic_range) -- the data-aware check of the tensor-core route."""
+        out = torch.empty((self.nch + 1, 2), dtype=torch.float64, device=self.device)
+        check(lib.pyfft_welch_dynamic_range(_ptr(res["Pxx"]), _ptr(res["Pyy"]), res["Pxx"].shape[0], self.nch,
+                                            1 if onesided else 0, _ptr(out), _stream()))
+        return out
 
     # -- accumulate --------------------------------------------------------- #
     def accumulate(self, x, y, rmap, seg_first, seg_count):

@@ -212,13 +212,21 @@ def _host_many(tensors):
 _plans = threading.local()
 
 
-def _welch_plan(nfft, hop, nch, precision, win, dev):
+# Data-aware selection of the tensor-core route (fft_pwelch(tensor_cores=None)): after the pass, every
+# auto-spectrum must keep min over bins >= TC_DYNAMIC_RANGE / Navr * mean over bins, else the call is
+# redone on the fp32 CUDA-core kernel.  The fp16 operands leave a white floor of ~1e-7 of the mean bin
+# power; a bin with power P sees a coherence error ~ sqrt(floor / P / Navr) (zero-mean cross term) +
+# floor / P (bias).  Calibrated in tests/test_gpu_tc_parity.py.
+TC_DYNAMIC_RANGE = 400.0
+
+
+def _welch_plan(nfft, hop, nch, precision, win, dev, group=None):
     """engine.WelchPlan of this thread for these parameters, reset (device buffers, the uploaded
     window and its transform are reused from call to call: ~0.2 ms of a 0.4 ms computation)."""
     cache = getattr(_plans, "cache", None)
     if cache is None:
         cache = _plans.cache = {}
-    key = (int(nfft), int(hop), int(nch), precision, str(dev))
+    key = (int(nfft), int(hop), int(nch), precision, str(dev), getattr(group, "group_name", None))
     hit = cache.get(key)
     if hit is not None and np.array_equal(hit[0], win):
         wp = hit[1]
@@ -304,19 +312,6 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
     else:
         sy = np.shape(sigy)
         ny = sy[1] if (len(sy) == 2 and sy[1] == ntv) else sy[0]
-    # host records: start the (asynchronous, when pinned) host->device copies first, so that the
-    # segmentation, window and norm arithmetic below runs on the host while PCIe is busy
-    x_dev = y_dev = staged = None
-    if not is_cplx:
-        precision = _eng.resolve_precision(precision, sigx, sigy)
-        device = _eng.require_cuda(device)
-        with torch.cuda.device(device):
-            staged = _eng.staged_upload(sigx, sigy, precision, device) if group is None else None
-            if staged is not None:
-                x_dev, y_dev = staged[0], staged[1]
-            else:
-                x_dev = _eng.to_device(sigx, precision, device)
-                y_dev = _eng.to_device(sigy, precision, device)
     plan = _Plan(tvec, nx, ny, tbounds, Navr, windowoverlap, windowfunction, kwargs)
     nwins, nfft, K = plan.nwins, plan.nfft, plan.Navr
     if verbose:
@@ -337,103 +332,164 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
     if nfft & (nfft - 1) or nfft < 16 or nfft > 8192:
         raise NotImplementedError("nwins = %d: the GPU path needs a power-of-two window of 16..8192 "
                                   "samples (choose Navr/tper accordingly)" % nfft)
+    precision = _eng.resolve_precision(precision, sigx, sigy)
+    dev = _eng.require_cuda(device)
+    hop = nwins - plan.noverlap
+    if hop <= 0:
+        raise ValueError("windowoverlap leaves no hop between segments")
+    if (K - 1) * hop + nwins > plan.nana:
+        # the reference dies here with a broadcasting ValueError (fft_analysis.py:375)
+        raise ValueError("operands could not be broadcast together: segment %d runs past the "
+                         "analysed record (%d samples, nwins=%d, hop=%d)" % (K - 1, plan.nana, nwins, hop))
+    refl = nwins - 1 if plan.reflect else 0
+    rank, world = 0, 1
+    if group is not None:
+        rank, world = torch.distributed.get_rank(group), torch.distributed.get_world_size(group)
+    lp = _dist.local_plan(K, hop, nwins, plan.nana, plan.i0, refl, rank, world)
+    nseg = lp["k1"] - lp["k0"]
+    mode = _lib.DETREND_MEAN if detrend_style > 0 else (_lib.DETREND_LINEAR if detrend_style < 0
+                                                        else _lib.DETREND_NONE)
+    scale = 1.0 / (fftinfo.S1 ** 2) / fftinfo.ENBW                 # :432-440
 
-    dev = device
-    with torch.cuda.device(dev):
-        x = x_dev
-        y = _eng.channels_first(y_dev, ntv)
-        nch = y.shape[0]
-        if x.dim() != 1:
-            x = x.reshape(-1)
-        x = x.contiguous()
-        refl = nwins - 1 if plan.reflect else 0
-        rmap = _eng.record_map(plan.nana, plan.i0, refl, 0, x.shape[0])
-        hop = nwins - plan.noverlap
-        if hop <= 0:
-            raise ValueError("windowoverlap leaves no hop between segments")
-        if (K - 1) * hop + nwins > plan.nana:
-            # the reference dies here with a broadcasting ValueError (fft_analysis.py:375)
-            raise ValueError("operands could not be broadcast together: segment %d runs past the "
-                             "analysed record (%d samples, nwins=%d, hop=%d)" % (K - 1, plan.nana, nwins, hop))
-        wp = _welch_plan(nfft, hop, nch, precision, win, dev)
-        mode = _lib.DETREND_MEAN if detrend_style > 0 else (_lib.DETREND_LINEAR if detrend_style < 0
-                                                            else _lib.DETREND_NONE)
-        rank, world = 0, 1
-        if group is not None:
-            rank, world = torch.distributed.get_rank(group), torch.distributed.get_world_size(group)
-        lp = _dist.local_plan(K, hop, nwins, plan.nana, plan.i0, refl, rank, world)
-        nseg = lp["k1"] - lp["k0"]
-        fix_nana = None
-        fused = mode == _lib.DETREND_MEAN and wp.can_fuse_mean and nseg > 0 and hop <= nwins and not two_pass
-        if staged is not None and not fused:
-            # only the fused single pass consumes the records piece by piece: wait for all of them
-            torch.cuda.current_stream(dev).wait_event(staged[2][-1])
-            staged = None
-        if fused:
-            # global mean (:356-357) fused into the single pass over the data: provisional mean
-            # from the head of the shard, exact correction by linearity afterwards
-            s_lo, s_hi = lp["stats_span"]
-            c_lo, c_hi = lp["k0"] * hop, lp["k1"] * hop          # what the fused kernel sums
-            # tensor-core DFT (fp16 operands, fp32 accumulation): its per-segment rounding noise
-            # (2^-12 relative, zero mean) averages out as 1/sqrt(K) -- used when enough segments
-            # are averaged for the 1e-5-of-peak contract to hold with margin
-            use_tc = wp.can_use_tc and (nseg >= 16384 if tensor_cores is None else bool(tensor_cores))
-            accumulate = wp.accumulate_tc if use_tc else wp.accumulate_mean
-            if staged is None:
-                (wp.prepare_tc if use_tc else wp.estimate_mean)(x, y, rmap, c_lo, c_hi)
-                accumulate(x, y, rmap, lp["k0"], nseg)
+    def run(tc_choice):
+        """One pass of the device pipeline -> (wp, res, nch, use_tc, host copies of the results)."""
+        with torch.cuda.device(dev):
+            # host records: sharded calls upload only the source slice this rank analyses; unsharded
+            # pinned records cross PCIe in pieces while the segments behind each piece are accumulated
+            staged, src_base = None, 0
+            host_in = not (isinstance(sigx, torch.Tensor) and sigx.is_cuda)
+            if group is not None and world > 1 and host_in:
+                g_lo, g_hi = lp["src"]
+                g_hi = max(g_hi, g_lo + 1)
+                x = _eng.to_device(sigx[g_lo:g_hi], precision, dev)
+                time_major = len(sigy.shape) == 1 or sigy.shape[-1] != ntv
+                ysl = sigy[g_lo:g_hi] if time_major else sigy[..., g_lo:g_hi]
+                y = _eng.channels_first(_eng.to_device(ysl, precision, dev), g_hi - g_lo)
+                src_base = g_lo
             else:
-                # the records are still arriving in pieces (engine.staged_upload): the segments that are
-                # complete behind each piece are accumulated while the next piece crosses PCIe
-                cur = torch.cuda.current_stream(dev)
-                events, bounds = staged[2], staged[3]
-                cur.wait_event(events[0])
-                (wp.prepare_tc if use_tc else wp.estimate_mean)(x, y, rmap, c_lo, c_hi)
-                kdone = lp["k0"]
-                for i, (ev, b_i) in enumerate(zip(events, bounds)):
-                    cur.wait_event(ev)
-                    kend = lp["k1"] if i == len(events) - 1 else \
-                        max(kdone, min(lp["k1"], (b_i - nwins + refl - plan.i0) // hop + 1))
-                    if kend > kdone:
-                        accumulate(x, y, rmap, kdone, kend - kdone)
-                        kdone = kend
-            fftinfo.tensor_cores = bool(use_tc)
-            if s_lo < c_lo:
-                wp.detrend_stats(x, y, rmap, s_lo, c_lo)
-            if s_hi > c_hi:
-                wp.detrend_stats(x, y, rmap, c_hi, s_hi)
-            fix_nana = plan.nana                        # mean correction folded into finalize
-            if group is not None:
-                wp.rereference()                        # common reference, then ONE collective
-                wp.all_reduce_state(group)
-                wp.K = K
-        else:
-            if mode != _lib.DETREND_NONE:
-                # global detrend over the whole analysed record (:356-357): each rank sums its slice
-                wp.detrend_stats(x, y, rmap, lp["stats_span"][0], lp["stats_span"][1])
-                wp.solve_detrend(mode, plan.nana, group)
-            wp.accumulate(x, y, rmap, lp["k0"], nseg)
-        if group is not None and fix_nana is None:
-            wp.all_reduce(group)
-        scale = 1.0 / (fftinfo.S1 ** 2) / fftinfo.ENBW             # :432-440
-        res = wp.finalize(scale, onesided=bool(onesided), K=K, correct_nana=fix_nana)
-        corr = {}
-        for nm, key, halve in (("Rxx", "Pxx", True), ("Ryy", "Pyy", True), ("Rxy", "Pxy", True),
-                               ("iCxy", "Cxy", False)):
-            corr[nm] = wp.correlation(res[key], onesided=bool(onesided), halve_interior=halve)
+                staged = _eng.staged_upload(sigx, sigy, precision, dev) if group is None else None
+                if staged is not None:
+                    x, y = staged[0], staged[1]
+                else:
+                    x = _eng.to_device(sigx, precision, dev)
+                    y = _eng.to_device(sigy, precision, dev)
+                y = _eng.channels_first(y, ntv)
+            nch = y.shape[0]
+            if x.dim() != 1:
+                x = x.reshape(-1)
+            x = x.contiguous()
+            rmap = _eng.record_map(plan.nana, plan.i0, refl, src_base, x.shape[0])
+            wp = _welch_plan(nfft, hop, nch, precision, win, dev, group)
+            fix_nana = None
+            fused = mode == _lib.DETREND_MEAN and wp.can_fuse_mean and nseg > 0 and hop <= nwins and not two_pass
+            if staged is not None and not fused:
+                # only the fused single pass consumes the records piece by piece: wait for all of them
+                torch.cuda.current_stream(dev).wait_event(staged[2][-1])
+                staged = None
+            use_tc = False
+            if fused:
+                # global mean (:356-357) fused into the single pass over the data: provisional mean
+                # from a sample of the shard, exact correction by linearity afterwards
+                s_lo, s_hi = lp["stats_span"]
+                c_lo, c_hi = lp["k0"] * hop, lp["k1"] * hop          # what the fused kernel sums
+                # tensor-core DFT (fp16 operands, fp32 accumulation): its per-segment rounding noise
+                # (2^-12 relative, zero mean) averages out as 1/sqrt(K) -- used when enough segments
+                # are averaged for the 1e-5-of-peak contract to hold with margin, and checked afterwards
+                # against the dynamic range of the result (TC_DYNAMIC_RANGE)
+                use_tc = wp.can_use_tc and (nseg >= 16384 if tc_choice is None else bool(tc_choice))
+                accumulate = wp.accumulate_tc if use_tc else wp.accumulate_mean
+                estimate = wp.prepare_tc if use_tc else wp.estimate_mean
+                if staged is None:
+                    estimate(x, y, rmap, c_lo, c_hi)
+                    accumulate(x, y, rmap, lp["k0"], nseg)
+                else:
+                    # the records are still arriving in pieces (engine.staged_upload): the segments that are
+                    # complete behind each piece are accumulated while the next piece crosses PCIe.  The
+                    # provisional statistics read analysed samples [c_lo, e_hi): wait for the piece that
+                    # holds the last source sample they map to (reflect-padded head: sources 1..refl).
+                    cur = torch.cuda.current_stream(dev)
+                    events, bounds = staged[2], staged[3]
+                    e_hi = min(c_hi, c_lo + (1 << 20))
+                    need_src = max(e_hi + plan.i0 - refl, min(refl, e_hi) + 1)
+                    first = next((i for i, b_i in enumerate(bounds) if b_i >= need_src), len(bounds) - 1)
+                    cur.wait_event(events[first])
+                    estimate(x, y, rmap, c_lo, e_hi)
+                    kdone = lp["k0"]
+                    for i, (ev, b_i) in enumerate(zip(events, bounds)):
+                        if i < first:
+                            continue
+                        cur.wait_event(ev)
+                        kend = lp["k1"] if i == len(events) - 1 else \
+                            max(kdone, min(lp["k1"], (b_i - nwins + refl - plan.i0) // hop + 1))
+                        if kend > kdone:
+                            accumulate(x, y, rmap, kdone, kend - kdone)
+                            kdone = kend
+                if s_lo < c_lo:
+                    wp.detrend_stats(x, y, rmap, s_lo, c_lo)
+                if s_hi > c_hi:
+                    wp.detrend_stats(x, y, rmap, c_hi, s_hi)
+                fix_nana = plan.nana                        # mean correction folded into finalize
+                if group is not None:
+                    wp.rereference()                        # common reference, then ONE collective
+                    wp.all_reduce_state(group)
+                    wp.K = K
+            else:
+                if mode != _lib.DETREND_NONE:
+                    # global detrend over the whole analysed record (:356-357): each rank sums its slice
+                    wp.detrend_stats(x, y, rmap, lp["stats_span"][0], lp["stats_span"][1])
+                    wp.solve_detrend(mode, plan.nana, group)
+                wp.accumulate(x, y, rmap, lp["k0"], nseg)
+            if group is not None and fix_nana is None:
+                wp.all_reduce(group)
+            res = wp.finalize(scale, onesided=bool(onesided), K=K, correct_nana=fix_nana)
+            corr = {}
+            for nm, key, halve in (("Rxx", "Pxx", True), ("Ryy", "Pyy", True), ("Rxy", "Pxy", True),
+                                   ("iCxy", "Cxy", False)):
+                corr[nm] = wp.correlation(res[key], onesided=bool(onesided), halve_interior=halve)
+            extras = []
+            if use_tc:
+                extras = [wp._tc_status, wp.dynamic_range(res, onesided=bool(onesided))]
+            peer = wp.peer_status() if (group is not None and fused) else None
+            if peer is not None:
+                extras.append(peer)
+            hosted = _host_many([res["Pxx"], res["Pyy"], res["Pxy"], res["Cxy"], res["Cxy2"], res["phi_xy"],
+                                 corr["Rxx"], corr["Ryy"], corr["Rxy"], corr["iCxy"]] + extras)
+            if peer is not None and hosted[-1].reshape(-1)[0] != 0:
+                peer.zero_()
+                raise RuntimeError("pyfft_b200: a peer GPU did not reach the NVLink reduction in time; "
+                                   "the partial sums of this call are invalid (PYFFT_PEER_REDUCE=0 selects NCCL)")
+            return wp, res, nch, use_tc, hosted
+
+    wp, res, nch, use_tc, hosted = run(tensor_cores)
+    fftinfo.tensor_cores = bool(use_tc)
+    fftinfo.tc_fallback = None
+    if use_tc:
+        flag, rng = int(hosted[10].reshape(-1)[0]), hosted[11]
+        why = None
+        if flag & 1:
+            why = "a tensor-core pipeline barrier timed out"
+        elif flag & 2:
+            why = "an fp16 operand overflowed (the record is far louder somewhere than its sampled statistics)"
+        elif np.any(rng[:, 0] < (TC_DYNAMIC_RANGE / K) * rng[:, 1]):
+            why = ("the spectrum has bins %.1e below its mean bin power: too close to the fp16 rounding floor "
+                   "of the tensor-core path for the coherence contract"
+                   % float(np.min(rng[:, 0] / np.maximum(rng[:, 1], 1e-300))))
+        if flag:
+            wp._tc_status.zero_()
+        if why is not None:
+            if tensor_cores is None:
+                # data-aware selection: rerun on the fp32 CUDA-core kernel (no CPU fallback)
+                wp, res, nch, use_tc, hosted = run(False)
+                fftinfo.tensor_cores = False
+                fftinfo.tc_fallback = why
+            elif flag:
+                raise RuntimeError("pyfft_b200: tensor_cores=True was forced and the kernel failed: " + why)
+            else:
+                fftinfo.tc_fallback = "forced: " + why
+    (Pxx, Pyy, Pxy, Cxy, Cxy2, phi_xy, h_rxx, h_ryy, h_rxy, h_icxy) = hosted[:10]
 
     freq = np.fft.fftfreq(nfft, 1.0 / plan.Fs)                     # :396
     freq = freq[:plan.Nnyquist] if onesided else np.fft.fftshift(freq)
-    tc_flag = wp._tc_status if getattr(fftinfo, "tensor_cores", False) else None
-    hosted = _host_many([res["Pxx"], res["Pyy"], res["Pxy"], res["Cxy"], res["Cxy2"], res["phi_xy"],
-                         corr["Rxx"], corr["Ryy"], corr["Rxy"], corr["iCxy"]] +
-                        ([tc_flag] if tc_flag is not None else []))
-    (Pxx, Pyy, Pxy, Cxy, Cxy2, phi_xy, h_rxx, h_ryy, h_rxy, h_icxy) = hosted[:10]
-    if tc_flag is not None and hosted[10][0] != 0:
-        # a hand-shake of the tensor-core kernel timed out (bounded waits): the sums are not valid
-        tc_flag.zero_()
-        raise RuntimeError("pyfft_b200: the tensor-core Welch kernel aborted (barrier time-out); "
-                           "call again with tensor_cores=False")
 
     # ---- O(nfreq) bookkeeping on the averaged spectra, as in the reference (:496-540) ---- #
     with np.errstate(all="ignore"):

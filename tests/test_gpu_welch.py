@@ -177,9 +177,15 @@ def test_pinned_host_records_are_uploaded_in_pieces(tensor_cores, navr, cuda_dev
         kw["tensor_cores"] = tensor_cores
     a = fft_pwelch(t, xs, ys, **kw)
     b = fft_pwelch(t, xs.to(cuda_device), ys.to(cuda_device), **kw)
-    for i in (1, 2, 3, 4):
-        assert relerr(a[i], b[i]) <= 2e-6, i
-    assert relerr(a[6].Rxy, b[6].Rxy) <= 2e-6
+    # the staged route takes its provisional mean / fp16 prescale from the first 2^20 samples (what has
+    # arrived), the resident route from the whole record: on the fp32 kernels that cancels exactly; on the
+    # forced tensor-core kernel (K = 2047, below the automatic threshold) the two calls round to fp16
+    # differently and differ by that kernel's noise at this K (6e-4 / sqrt(K) of peak, coherence 10 x)
+    tol = 6e-4 / np.sqrt(navr) * 1.5 if tensor_cores else 2e-6
+    for i in (1, 2, 3):
+        assert relerr(a[i], b[i]) <= tol, i
+    assert np.max(np.abs(a[4] - b[4])) <= (10 * tol if tensor_cores else 2e-6)
+    assert relerr(a[6].Rxy, b[6].Rxy) <= tol
     # a (1, n) second record goes the same way
     c = fft_pwelch(t, xs, ys.view(1, n), **kw)
     assert relerr(c[1], a[1]) <= 1e-12

@@ -4,7 +4,7 @@ import ctypes
 import sys
 import numpy as np
 import torch
-sys.path.insert(0, '/root/repo')
+sys.path.insert(0, __import__('os').path.dirname(__import__('os').path.dirname(__import__('os').path.abspath(__file__))))
 from pyfft_b200 import _lib, engine
 from pyfft_b200.windows import windows
 
@@ -51,16 +51,17 @@ clk = (cta[:, 3] - cta[:, 2]) / np.maximum(cta[:, 1] - cta[:, 0], 1)
 print('SM clock during the kernel (clk/ns): min %.3f mean %.3f max %.3f' % (clk.min(), clk.mean(), clk.max()))
 print('CTA 0: first event at clock %d after CTA start; CTA clocks %d' % (t[t > 0].min() - cta[0, 2], cta[0, 3] - cta[0, 2]))
 t0 = t[t > 0].min()
-names = ["L0 start", "L0 full", "L1 start", "L1 full", "S1(0) iss", "S1(1) iss", "S2 iss", "T got D1(0)", "T got D1(1)",
-         "T B2 full", "E got D2", "E D2 free", "S1(0) pre", "S1(0) go", "S2 pre", "S2 go"]
-print("clock cycles relative to the first event; one row per batch")
-print("batch " + " ".join("%11s" % s for s in names))
-for b in list(range(0, 6)) + list(range(50, 56)):
-    print("%5d " % b + " ".join("%11d" % (t[b, e] - t0 if t[b, e] else -1) for e in range(12)))
-d = np.diff(t[20:100, 6])
-print("steady state: S2 issue to S2 issue %.0f clk (min %d max %d)" % (d.mean(), d.min(), d.max()))
-for e in range(16):
-    print("  %-12s minus S2 issue of the same batch: %8.0f" % (names[e], (t[20:100, e] - t[20:100, 6]).mean()))
+names = ["C start", "C raw ok", "C A1 full", "S1 go", "S1 commit", "T got D1", "T B2 full", "S2 go", "S2 commit",
+         "E got D2", "E D2 free", "P loaded"]
+print("clock cycles relative to the first event; one row per segment")
+print("  seg " + " ".join("%10s" % s for s in names))
+for b in list(range(0, 8)) + list(range(90, 98)):
+    print("%5d " % b + " ".join("%10d" % (t[b, e] - t0 if t[b, e] else -1) for e in range(12)))
+d = np.diff(t[30:120, 8])
+print("steady state: S2 commit to S2 commit %.0f clk per segment (min %d max %d)" % (d.mean(), d.min(), d.max()))
+for e in range(12):
+    print("  %-10s minus S2 commit of the same segment: %8.0f   (own period %.0f)" % (
+        names[e], (t[30:120, e] - t[30:120, 8]).mean(), np.diff(t[30:120, e]).mean()))
 
 cta1 = first[nb * 16:].reshape(160, 4)[:148]
 print('isolated launch: CTA duration ns mean %.0f max %d, SM clock %.3f clk/ns' % (
