@@ -166,6 +166,28 @@ int pyfft_welch_rereference(double* acc, double* lin, int32_t nfft, int32_t nch,
                             const double* est, const double* wlow, void* stream);
 
 /* ------------------------------------------------------------------------- *
+ * pyfft_welch_accumulate without any allocation.
+ * No counterpart in the reference: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arguments, meaning and result as pyfft_welch_accumulate, minus the workspace: the per-CTA partial
+ * sums AND the twiddle table (computed on the device by every call) live in one file-scope
+ * `static __device__` array of the library (16 MiB + 128 KiB; every GPU that loads the library holds it
+ * until exit).  The call performs no cudaMalloc / cudaFree and uses no allocating library routine.
+ * Limit: calls that would need more than pyfft_welch_static_scratch_bytes() = 16 MiB of partial sums
+ * (pyfft_welch_workspace_bytes(dtype, seg, nch) tells) return PYFFT_EUNSUPPORTED with a message; config 2
+ * (fp32, nfft 4096, one y channel: 10.9 MB on 148 SMs) fits, fp64 at nfft >= 4096 does not.
+ * All calls share the array and it keeps the previous call's contents (each call overwrites what it
+ * reads): calls that overlap on the GPU -- different streams, or different host threads -- race; issue
+ * them on one stream.
+ * ------------------------------------------------------------------------- */
+int64_t pyfft_welch_static_scratch_bytes(void);
+
+int pyfft_welch_accumulate_static(int dtype, const void* x, const void* y, int64_t y_stride, int32_t nch,
+                                  const pyfft_record_map* map, const pyfft_segmentation* seg,
+                                  const void* window, const double* coef_x, const double* coef_y,
+                                  double* acc, void* stream);
+
+/* ------------------------------------------------------------------------- *
  * K1-TC, the same accumulation on the tcgen05 tensor cores (float32 input,
  * nfft = 4096, hop 512, 1024, 2048 or 4096)
  * replaces: the same reference lines as pyfft_welch_accumulate_mean.

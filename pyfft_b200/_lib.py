@@ -48,6 +48,8 @@ _PROTOS = {
     "pyfft_welch_workspace_bytes": (_i64, [C.c_int, _pseg, _i32]),
     "pyfft_welch_accumulate": (C.c_int, [C.c_int, _vp, _vp, _i64, _i32, _pmap, _pseg, _vp, _vp, _vp,
                                          _vp, _vp, _i64, _vp]),
+    "pyfft_welch_static_scratch_bytes": (_i64, []),
+    "pyfft_welch_accumulate_static": (C.c_int, [C.c_int, _vp, _vp, _i64, _i32, _pmap, _pseg, _vp, _vp, _vp, _vp, _vp]),
     "pyfft_welch_accumulate_mean": (C.c_int, [C.c_int, _vp, _vp, _i64, _i32, _pmap, _pseg, _vp, _vp, _vp,
                                               _vp, _vp, _vp, _i64, _vp]),
     "pyfft_welch_mean_correct": (C.c_int, [_vp, _vp, _i32, _i32, _i64, _vp, _vp, _i64, _vp, _vp]),

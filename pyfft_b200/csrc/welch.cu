@@ -4,6 +4,9 @@
 // Reference lines replaced: fft_analysis.py:353-393 (detrend, segment loop,
 // window, FFT, products), :402-446 (side selection, scaling, mean),
 // :1662-1680 (coherence), :520 (phase), :544-597 (correlations).
+#include <map>
+#include <mutex>
+
 #include "common.cuh"
 
 namespace pyfft {
@@ -642,6 +645,109 @@ int welch_raw_sums_launch(const double* dev_sums, const double* est, int n, doub
     return PYFFT_OK;
 }
 
+// ------------------------------------------------------------------------- //
+// allocation-free variant of pyfft_welch_accumulate (pyfft_welch_accumulate_static): the per-CTA partial
+// sums and the twiddle table live in ONE file-scope device array instead of a caller workspace and the
+// cudaMalloc'ed twiddle cache.  Every GPU that loads the library holds the array until exit.  All calls
+// share it: calls that overlap on the GPU (different streams) race.
+// ------------------------------------------------------------------------- //
+constexpr int64_t STATIC_TW_BYTES = 8192 * 16;                       // twiddles of one call (nfft <= 8192, complex double)
+constexpr int64_t STATIC_WS_BYTES = 16ll << 20;                      // partial sums: 16 MiB
+static __device__ __align__(256) unsigned char g_static_scratch[STATIC_TW_BYTES + STATIC_WS_BYTES];
+static std::mutex g_static_mutex;
+static std::map<int, void*> g_static_addr;                           // device ordinal -> device address of the array
+
+// the array's NAME is a host-side stand-in; its device address comes from cudaGetSymbolAddress, once per
+// device, with that device current
+static void* static_scratch_address(int* status) {
+    *status = PYFFT_OK;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) { *status = fail(PYFFT_ECUDA, "cudaGetDevice failed"); return nullptr; }
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    auto it = g_static_addr.find(dev);
+    if (it != g_static_addr.end()) return it->second;
+    void* ptr = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&ptr, g_static_scratch);
+    if (e != cudaSuccess || !ptr) {
+        *status = fail(PYFFT_ECUDA, "cudaGetSymbolAddress(static scratch) failed: %s", cudaGetErrorString(e));
+        return nullptr;
+    }
+    g_static_addr[dev] = ptr;
+    return ptr;
+}
+
+// tw[k] = exp(-2 pi i k / L), evaluated on the device in double (sincospi) and rounded to T
+template <typename T>
+__global__ void static_twiddle_kernel(cpx<T>* __restrict__ tw, int L) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= L) return;
+    double s, c;
+    sincospi(-2.0 * (double)k / (double)L, &s, &c);
+    tw[k].x = (T)c;
+    tw[k].y = (T)s;
+}
+
+template <typename T, int LOG2L>
+static int launch_welch_static(const void* x, const void* y, int64_t y_stride, int nch, const RecMap& map,
+                               const pyfft_segmentation* seg, const void* window, const double* coef_x,
+                               const double* coef_y, double* acc, unsigned char* scratch, cudaStream_t st) {
+    using G = WelchGeom<LOG2L>;
+    constexpr bool SINGLE = welch_smem_bytes<T, LOG2L, false>() > 200 * 1024;
+    constexpr size_t smem = welch_smem_bytes<T, LOG2L, SINGLE>();
+    const int gx = welch_grid_x(seg->seg_count, G::SLOTS, nch);
+    const int nparts = gx * G::SLOTS;
+    const int64_t main_bytes = (int64_t)nch * nparts * 4 * G::NBIN * (int64_t)sizeof(T);
+    const int64_t lin_bytes = (int64_t)nch * nparts * 4 * G::TPS * (int64_t)sizeof(T);
+    const int64_t need = main_bytes + lin_bytes + 8 * (int64_t)(nch + 1);
+    if (need > STATIC_WS_BYTES)
+        return fail(PYFFT_EUNSUPPORTED,
+                    "welch_accumulate_static: this call needs %lld bytes of scratch, the static array holds %lld "
+                    "(use pyfft_welch_accumulate with a caller workspace)", (long long)need, (long long)STATIC_WS_BYTES);
+    cpx<T>* tw = reinterpret_cast<cpx<T>*>(scratch);
+    unsigned char* ws = scratch + STATIC_TW_BYTES;
+    static_twiddle_kernel<T><<<(G::L + 255) / 256, 256, 0, st>>>(tw, G::L);
+    PYFFT_LAUNCH_OK("static_twiddle_kernel");
+    WelchParams<T> p;
+    p.x = static_cast<const T*>(x);
+    p.y = static_cast<const T*>(y);
+    p.y_stride = y_stride;
+    p.map = map;
+    p.hop = seg->hop;
+    p.seg_first = seg->seg_first;
+    p.seg_count = seg->seg_count;
+    p.chunk = (seg->seg_count + nparts - 1) / nparts;
+    p.window = static_cast<const T*>(window);
+    p.coef_x = coef_x;
+    p.coef_y = coef_y;
+    p.tw = tw;
+    p.partial = reinterpret_cast<T*>(ws);                  // every CTA writes all of its partial sums: nothing to clear
+    p.nparts = nparts;
+    p.lin_partial = reinterpret_cast<T*>(ws + main_bytes);
+    p.dev_sums = reinterpret_cast<double*>(ws + main_bytes + lin_bytes);
+    auto kern = welch_pair_kernel<T, LOG2L, SINGLE, false>;
+    PYFFT_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<dim3(gx, nch), G::THREADS, smem, st>>>(p);
+    PYFFT_LAUNCH_OK("welch_pair_kernel");
+    const int per_pair = 4 * G::NBIN;
+    welch_reduce_kernel<T><<<dim3((per_pair + 31) / 32, nch), 256, 0, st>>>(p.partial, nparts, per_pair, acc);
+    PYFFT_LAUNCH_OK("welch_reduce_kernel");
+    return PYFFT_OK;
+}
+
+template <typename T>
+static int dispatch_welch_static(int log2l, const void* x, const void* y, int64_t y_stride, int nch, const RecMap& map,
+                                 const pyfft_segmentation* seg, const void* window, const double* coef_x,
+                                 const double* coef_y, double* acc, unsigned char* scratch, cudaStream_t st) {
+#define PYFFT_CASE(N) \
+    case N: return launch_welch_static<T, N>(x, y, y_stride, nch, map, seg, window, coef_x, coef_y, acc, scratch, st);
+    switch (log2l) {
+        PYFFT_CASE(4) PYFFT_CASE(5) PYFFT_CASE(6) PYFFT_CASE(7) PYFFT_CASE(8)
+        PYFFT_CASE(9) PYFFT_CASE(10) PYFFT_CASE(11) PYFFT_CASE(12) PYFFT_CASE(13)
+    }
+#undef PYFFT_CASE
+    return fail(PYFFT_EUNSUPPORTED, "nfft = 2^%d not supported", log2l);
+}
+
 }  // namespace pyfft
 
 using namespace pyfft;
@@ -747,6 +853,34 @@ int pyfft_welch_accumulate(int dtype, const void* x, const void* y, int64_t y_st
                            double* acc, void* workspace, int64_t workspace_bytes, void* stream) {
     return welch_accumulate_common(dtype, x, y, y_stride, nch, map, seg, window, coef_x, coef_y, acc, nullptr,
                                    nullptr, workspace, workspace_bytes, stream);
+}
+
+int64_t pyfft_welch_static_scratch_bytes(void) { return STATIC_WS_BYTES; }
+
+int pyfft_welch_accumulate_static(int dtype, const void* x, const void* y, int64_t y_stride, int32_t nch,
+                                  const pyfft_record_map* map, const pyfft_segmentation* seg,
+                                  const void* window, const double* coef_x, const double* coef_y,
+                                  double* acc, void* stream) {
+    RecMap m;
+    int rc = check_map(map, &m);
+    if (rc) return rc;
+    int log2l;
+    if ((rc = check_seg(seg, 4, 13, &log2l))) return rc;
+    if (!x || !y || !window || !acc || nch <= 0)
+        return fail(PYFFT_EINVAL, "welch_accumulate_static: NULL pointer or nch <= 0");
+    if (seg->seg_count == 0) return PYFFT_OK;
+    const int64_t j_lo = seg->seg_first * (int64_t)seg->hop;
+    const int64_t j_hi = (seg->seg_first + seg->seg_count - 1) * (int64_t)seg->hop + seg->nfft;
+    if ((rc = check_range(m, j_lo, j_hi))) return rc;
+    int status;
+    unsigned char* scratch = static_cast<unsigned char*>(static_scratch_address(&status));
+    if (!scratch) return status;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (dtype == PYFFT_F32)
+        return dispatch_welch_static<float>(log2l, x, y, y_stride, nch, m, seg, window, coef_x, coef_y, acc, scratch, st);
+    if (dtype == PYFFT_F64)
+        return dispatch_welch_static<double>(log2l, x, y, y_stride, nch, m, seg, window, coef_x, coef_y, acc, scratch, st);
+    return fail(PYFFT_EINVAL, "unknown dtype %d", dtype);
 }
 
 int pyfft_welch_accumulate_mean(int dtype, const void* x, const void* y, int64_t y_stride, int32_t nch,
