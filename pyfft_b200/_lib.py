@@ -55,7 +55,7 @@ _PROTOS = {
     "pyfft_welch_mean_correct": (C.c_int, [_vp, _vp, _i32, _i32, _i64, _vp, _vp, _i64, _vp, _vp]),
     "pyfft_welch_rereference": (C.c_int, [_vp, _vp, _i32, _i32, _i64, _vp, _vp, _vp]),
     "pyfft_welch_tc_workspace_bytes": (_i64, [_pseg, _i32]),
-    "pyfft_welch_tc_prepare": (C.c_int, [_vp, _vp, _i64, _i32, _pmap, _i64, _i64, _vp, _vp, _vp]),
+    "pyfft_welch_tc_prepare": (C.c_int, [_vp, _vp, _i64, _i32, _pmap, _i64, _i64, _i64, _vp, _vp, _vp]),
     "pyfft_welch_accumulate_tc": (C.c_int, [_vp, _vp, _i64, _i32, _pmap, _pseg, _vp, _vp, _vp, _vp, _vp, _vp,
                                             _vp, _i64, _vp, _vp]),
     "pyfft_welch_finalize": (C.c_int, [_vp, _i32, _i32, _i64, _dbl, _i32, _vp, _vp, _vp, _vp, _vp,

@@ -609,35 +609,77 @@ __host__ __device__ __forceinline__ int64_t prep_stride(int64_t span) {
 }
 // est[2c] += sum (x - x0), est[2c+1] += sum (x - x0)^2 with x0 = the first sample of the span; the
 // last block of a channel to finish (ticket in prescale[c], zeroed by the host) turns the sums into
-// est[2c] = mean (rounded to fp32), est[2c+1] = 0, prescale[c] = 2^k with rms * 2^k in [1/8, 1/4)
+// est[2c] = mean (rounded to fp32), est[2c+1] = 0, prescale[c] = 2^k with rms * 2^k in [1/8, 1/4).
+// Segment-to-segment repetition: the fp16 roundings of the tensor-core path average out over the segments
+// only if they differ from segment to segment.  A record that repeats EXACTLY after a few hops (a noiseless
+// synthetic signal whose period divides c hops) rounds identically every c segments and nothing averages.
+// prescale[nch1 + c] = min over lags l = 1..PREP_LAGS hops of  sum (x[j + l hop] - x[j])^2 / (2 sum (x - mean)^2)
+// over the sampled runs: ~1 for noise, the noise fraction for tone + noise, 0 for an exact repetition (a noise
+// fraction of 1e-6 already dithers the roundings; the host refuses the path below 1e-4).
+// Stationarity: the 1/sqrt(K) averaging also needs the power to be spread over the segments.
+// prescale[2 nch1 + c] = (sum_b v_b)^2 / (B sum_b v_b^2) with v_b the variance of run b: 1 for a stationary
+// record, 1/64 when one run of the 64 carries all the power (the effective number of segments is that
+// fraction of K); the host refuses the path below 1/2.
+constexpr int PREP_LAGS = 8;
 __global__ void __launch_bounds__(256) tc_prepare_kernel(const float* __restrict__ x, const float* __restrict__ y,
                                                          int64_t y_stride, RecMap map, int64_t j_begin, int64_t j_end,
-                                                         double* __restrict__ est, double* __restrict__ prescale) {
+                                                         int64_t hop, int nch1, double* __restrict__ est,
+                                                         double* __restrict__ prescale) {
     const int c = blockIdx.y;                       // 0 = x, 1.. = y channels
     const float* p = c == 0 ? x : y + (int64_t)(c - 1) * y_stride;
     const double x0 = (double)p[src_index(map, j_begin)];
-    double s0 = 0.0, s1 = 0.0;
+    double s[2 + PREP_LAGS];
+#pragma unroll
+    for (int i = 0; i < 2 + PREP_LAGS; ++i) s[i] = 0.0;
     const int64_t stride = prep_stride(j_end - j_begin);
     const int64_t r0 = j_begin + (int64_t)blockIdx.x * stride;
+    const bool lags_ok = hop > 0 && (j_end - j_begin) >= 2 * PREP_LAGS * hop + PREP_RUN;   // room to look 8 hops forward or back
     for (int64_t j = r0 + threadIdx.x; j < r0 + PREP_RUN && j < j_end; j += 256) {
-        const double v = (double)p[src_index(map, j)] - x0;
-        s0 += v;
-        s1 += v * v;
+        const float v0 = p[src_index(map, j)];
+        const double v = (double)v0 - x0;
+        s[0] += v;
+        s[1] += v * v;
+        if (lags_ok) {
+            // look forward, or backward near the end of the span
+            const int64_t dir = j + PREP_LAGS * hop < j_end ? hop : -hop;
+#pragma unroll
+            for (int l = 1; l <= PREP_LAGS; ++l) {
+                const double d = (double)p[src_index(map, j + l * dir)] - (double)v0;
+                s[1 + l] += d * d;
+            }
+        }
     }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        s0 += __shfl_xor_sync(0xffffffffu, s0, o);
-        s1 += __shfl_xor_sync(0xffffffffu, s1, o);
-    }
-    __shared__ double sh[2][8];
-    if ((threadIdx.x & 31) == 0) { sh[0][threadIdx.x >> 5] = s0; sh[1][threadIdx.x >> 5] = s1; }
+    for (int i = 0; i < 2 + PREP_LAGS; ++i)
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s[i] += __shfl_xor_sync(0xffffffffu, s[i], o);
+    __shared__ double sh[2 + PREP_LAGS][8];
+    if ((threadIdx.x & 31) == 0)
+#pragma unroll
+        for (int i = 0; i < 2 + PREP_LAGS; ++i) sh[i][threadIdx.x >> 5] = s[i];
     __syncthreads();
     if (threadIdx.x != 0) return;
-    s0 = s1 = 0.0;
+    double* lagsum = prescale + 3 * nch1 + PREP_LAGS * c;
+    double* runvar = prescale + (3 + PREP_LAGS) * nch1 + 2 * c;
+    {
+        double t0 = 0.0, t1 = 0.0;
+        for (int w = 0; w < 8; ++w) { t0 += sh[0][w]; t1 += sh[1][w]; }
+        int64_t nb = r0 + PREP_RUN < j_end ? PREP_RUN : j_end - r0;
+        if (nb > 1) {
+            const double mb = t0 / (double)nb;
+            double vb = t1 / (double)nb - mb * mb;
+            if (!(vb > 0.0)) vb = 0.0;
+            atomicAdd(&runvar[0], vb);
+            atomicAdd(&runvar[1], vb * vb);
+        }
+    }
 #pragma unroll
-    for (int w = 0; w < 8; ++w) { s0 += sh[0][w]; s1 += sh[1][w]; }
-    atomicAdd(&est[2 * c], s0);
-    atomicAdd(&est[2 * c + 1], s1);
+    for (int i = 0; i < 2 + PREP_LAGS; ++i) {
+        double t = 0.0;
+        for (int w = 0; w < 8; ++w) t += sh[i][w];
+        if (i < 2) atomicAdd(&est[2 * c + i], t);
+        else atomicAdd(&lagsum[i - 2], t);
+    }
     __threadfence();
     if (atomicAdd(&prescale[c], 1.0) != (double)(gridDim.x - 1)) return;     // not the last block of the channel
     __threadfence();
@@ -650,6 +692,19 @@ __global__ void __launch_bounds__(256) tc_prepare_kernel(const float* __restrict
     const double md = atomicAdd(&est[2 * c], 0.0) / n;                         // read through L2
     double var = atomicAdd(&est[2 * c + 1], 0.0) / n - md * md;
     if (!(var > 0.0)) var = 0.0;
+    double rep = 1.0;
+    if (lags_ok && var > 0.0)
+        for (int l = 0; l < PREP_LAGS; ++l) {
+            const double r = atomicAdd(&lagsum[l], 0.0) / (2.0 * var * n);
+            rep = r < rep ? r : rep;
+        }
+    prescale[nch1 + c] = rep;
+    {
+        int runs = 0;
+        for (int b = 0; b < PREP_BLOCKS; ++b) runs += (j_begin + (int64_t)b * stride + 1 < j_end) ? 1 : 0;
+        const double a = atomicAdd(&runvar[0], 0.0), q = atomicAdd(&runvar[1], 0.0);
+        prescale[2 * nch1 + c] = (q > 0.0 && runs > 0) ? a * a / ((double)runs * q) : 1.0;
+    }
     const double rms = sqrt(var);
     int e = 0;
     if (rms > 0.0 && isfinite(rms)) frexp(rms, &e);   // rms = f * 2^e, f in [0.5, 1)
@@ -820,7 +875,7 @@ int64_t pyfft_welch_tc_workspace_bytes(const pyfft_segmentation* seg, int32_t nc
 }
 
 int pyfft_welch_tc_prepare(const void* x, const void* y, int64_t y_stride, int32_t nch,
-                           const pyfft_record_map* map, int64_t j_begin, int64_t j_end, double* est,
+                           const pyfft_record_map* map, int64_t j_begin, int64_t j_end, int64_t hop, double* est,
                            double* prescale, void* stream) {
     RecMap m;
     int rc = check_map(map, &m);
@@ -830,9 +885,9 @@ int pyfft_welch_tc_prepare(const void* x, const void* y, int64_t y_stride, int32
     if (j_end <= j_begin) return fail(PYFFT_EINVAL, "welch_tc_prepare: empty sample span");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     PYFFT_CUDA_OK(cudaMemsetAsync(est, 0, sizeof(double) * 2 * (size_t)(nch + 1), st));
-    PYFFT_CUDA_OK(cudaMemsetAsync(prescale, 0, sizeof(double) * (size_t)(nch + 1), st));
+    PYFFT_CUDA_OK(cudaMemsetAsync(prescale, 0, sizeof(double) * (size_t)(nch + 1) * (5 + PREP_LAGS), st));
     tc_prepare_kernel<<<dim3(PREP_BLOCKS, nch + 1), 256, 0, st>>>(static_cast<const float*>(x), static_cast<const float*>(y),
-                                                        y_stride, m, j_begin, j_end, est, prescale);
+                                                        y_stride, m, j_begin, j_end, hop, nch + 1, est, prescale);
     PYFFT_LAUNCH_OK("tc_prepare_kernel");
     return PYFFT_OK;
 }

@@ -294,10 +294,20 @@ class WelchPlan(object):
         j1 = j_end
         if self._tc_est is None:                       # zeroed by the entry point itself
             self._tc_est = torch.empty(2 * (self.nch + 1), dtype=torch.float64, device=self.device)
-            self.prescale = torch.empty(self.nch + 1, dtype=torch.float64, device=self.device)
+            self.prescale = torch.empty(16 * (self.nch + 1), dtype=torch.float64, device=self.device)
         self.est = self._tc_est
         check(lib.pyfft_welch_tc_prepare(_ptr(x), _ptr(y), y.stride(0), self.nch, C.byref(rmap), j_begin, j1,
-                                         _ptr(self.est), _ptr(self.prescale), _stream()))
+                                         self.hop, _ptr(self.est), _ptr(self.prescale), _stream()))
+
+    def tc_repetition(self):
+        """(2, nch+1) device view: repetition measure and stationarity of every channel from the last
+        prepare_tc (include/pyfft_b200.h)."""
+        return self.prescale[self.nch + 1:3 * (self.nch + 1)].view(2, self.nch + 1)
+
+    def mean_offset(self, nana):
+        """(nch+1,) device tensor: exact mean of the analysed record minus the provisional mean the fused
+        kernels subtracted (stats must cover the whole record; call before rereference)."""
+        return self.stats[0::2] / float(nana) - self.est[0::2]
 
     def accumulate_tc(self, x, y, rmap, seg_first, seg_count):
         """K1 on the tensor cores (tcgen05): adds to acc, lin and the raw sums in stats."""

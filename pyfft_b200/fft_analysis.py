@@ -218,6 +218,18 @@ _plans = threading.local()
 # power; a bin with power P sees a coherence error ~ sqrt(floor / P / Navr) (zero-mean cross term) +
 # floor / P (bias).  Calibrated in tests/test_gpu_tc_parity.py.
 TC_DYNAMIC_RANGE = 400.0
+TC_MIN_RATIO = 4e-3          # the bias term alone: floor / P <= 1e-4 with margin, whatever Navr
+# ... and no channel may repeat exactly after 1..8 hops (pyfft_welch_tc_prepare's repetition measure: the
+# noise fraction of the record at those lags; 1e-6 already dithers the fp16 roundings)
+TC_MIN_REPETITION = 1e-4
+TC_MIN_STATIONARITY = 0.5    # ... and the power must be spread over the record (64 sampled runs)
+# fp32 fused-mean route (either kernel): the kernel sees the record with a DC offset d = mean - provisional
+# mean; its leak d^2 |W[f]|^2 is accumulated in fp32 with the signal and subtracted afterwards, which costs
+# ~2^-23 x leak in absolute error.  Tolerated: leak <= 500 x the bin's own power (coherence, 1e-4) and
+# <= 10 x the channel's spectral peak (PSD, 1e-5 of peak); above, the call is redone with the exact mean
+# first (two passes over HBM).
+FUSED_MEAN_MAX_LEAK = 500.0
+FUSED_MEAN_MAX_LEAK_PEAK = 10.0
 
 
 def _welch_plan(nfft, hop, nch, precision, win, dev, group=None):
@@ -387,6 +399,7 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
                 torch.cuda.current_stream(dev).wait_event(staged[2][-1])
                 staged = None
             use_tc = False
+            offs = None
             if fused:
                 # global mean (:356-357) fused into the single pass over the data: provisional mean
                 # from a sample of the shard, exact correction by linearity afterwards
@@ -429,6 +442,7 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
                 if s_hi > c_hi:
                     wp.detrend_stats(x, y, rmap, c_hi, s_hi)
                 fix_nana = plan.nana                        # mean correction folded into finalize
+                offs = wp.mean_offset(plan.nana) if (group is None and precision == "fp32") else None
                 if group is not None:
                     wp.rereference()                        # common reference, then ONE collective
                     wp.all_reduce_state(group)
@@ -447,8 +461,10 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
                                    ("iCxy", "Cxy", False)):
                 corr[nm] = wp.correlation(res[key], onesided=bool(onesided), halve_interior=halve)
             extras = []
+            if offs is not None:
+                extras.append(offs)
             if use_tc:
-                extras = [wp._tc_status, wp.dynamic_range(res, onesided=bool(onesided))]
+                extras += [wp._tc_status, wp.dynamic_range(res, onesided=bool(onesided)), wp.tc_repetition()]
             peer = wp.peer_status() if (group is not None and fused) else None
             if peer is not None:
                 extras.append(peer)
@@ -458,19 +474,50 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
                 peer.zero_()
                 raise RuntimeError("pyfft_b200: a peer GPU did not reach the NVLink reduction in time; "
                                    "the partial sums of this call are invalid (PYFFT_PEER_REDUCE=0 selects NCCL)")
-            return wp, res, nch, use_tc, hosted
+            return wp, res, nch, use_tc, hosted, offs is not None
 
-    wp, res, nch, use_tc, hosted = run(tensor_cores)
+    def leak_ratio(hosted, wp):
+        """fp32 fused-mean route: the kernel saw the record with a DC offset d = mean - provisional mean,
+        which leaks into the lowest bins as d^2 |W[f]|^2 and is removed afterwards by linearity; fp32
+        accumulation loses the signal under that leak when it is orders of magnitude larger.  -> max over
+        channels and low bins of leak power / bin power."""
+        d = hosted[10]
+        nl = min(wp.nlin, hosted[0].shape[0])
+        w2 = (wp.wlow[:nl, 0] ** 2 + wp.wlow[:nl, 1] ** 2).cpu().numpy() * scale
+        if onesided:
+            w2 = w2 * np.where((np.arange(nl) > 0), 2.0, 1.0)
+        lo = 0 if onesided else nfft // 2                      # bin 0 after the fftshift of two-sided spectra
+        px = np.abs(hosted[0][lo:lo + nl]).reshape(nl, 1)
+        py = np.abs(hosted[1][lo:lo + nl]).reshape(nl, -1)
+        tiny = 1e-300
+        lx, ly = d[0] ** 2 * w2[:, None], (d[1:] ** 2)[None, :] * w2[:, None]          # leak power per low bin
+        per_bin = max(np.max(lx / np.maximum(px, tiny)), np.max(ly / np.maximum(py, tiny)))
+        pkx = max(float(np.max(np.abs(hosted[0]))), tiny)
+        pky = np.maximum(np.max(np.abs(hosted[1]).reshape(hosted[0].shape[0], -1), axis=0), tiny)
+        per_peak = max(np.max(lx) / pkx, np.max(ly / pky[None, :]))
+        return float(per_bin), float(per_peak)
+
+    wp, res, nch, use_tc, hosted, has_offs = run(tensor_cores)
     fftinfo.tensor_cores = bool(use_tc)
     fftinfo.tc_fallback = None
+    fftinfo.mean_fallback = None
+    base = 11 if has_offs else 10
     if use_tc:
-        flag, rng = int(hosted[10].reshape(-1)[0]), hosted[11]
+        flag, rng, rep = int(hosted[base].reshape(-1)[0]), hosted[base + 1], hosted[base + 2]
+        fftinfo.tc_checks = dict(status=flag, min_over_mean=float(np.min(rng[:, 0] / np.maximum(rng[:, 1], 1e-300))),
+                                 repetition=float(np.min(rep[0])), stationarity=float(np.min(rep[1])))
         why = None
         if flag & 1:
             why = "a tensor-core pipeline barrier timed out"
         elif flag & 2:
             why = "an fp16 operand overflowed (the record is far louder somewhere than its sampled statistics)"
-        elif np.any(rng[:, 0] < (TC_DYNAMIC_RANGE / K) * rng[:, 1]):
+        elif np.min(rep[0]) < TC_MIN_REPETITION:
+            why = ("the record repeats after a few hops (repetition measure %.1e): the fp16 roundings of the "
+                   "tensor-core path would not average out over the segments" % float(np.min(rep[0])))
+        elif np.min(rep[1]) < TC_MIN_STATIONARITY:
+            why = ("the power of the record sits in a fraction %.2g of it: too few effective segments for the "
+                   "fp16 roundings of the tensor-core path to average out" % float(np.min(rep[1])))
+        elif np.any(rng[:, 0] < max(TC_DYNAMIC_RANGE / K, TC_MIN_RATIO) * rng[:, 1]):
             why = ("the spectrum has bins %.1e below its mean bin power: too close to the fp16 rounding floor "
                    "of the tensor-core path for the coherence contract"
                    % float(np.min(rng[:, 0] / np.maximum(rng[:, 1], 1e-300))))
@@ -479,13 +526,22 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
         if why is not None:
             if tensor_cores is None:
                 # data-aware selection: rerun on the fp32 CUDA-core kernel (no CPU fallback)
-                wp, res, nch, use_tc, hosted = run(False)
+                wp, res, nch, use_tc, hosted, has_offs = run(False)
                 fftinfo.tensor_cores = False
                 fftinfo.tc_fallback = why
             elif flag:
                 raise RuntimeError("pyfft_b200: tensor_cores=True was forced and the kernel failed: " + why)
             else:
                 fftinfo.tc_fallback = "forced: " + why
+    if has_offs and not two_pass:
+        r, rpk = leak_ratio(hosted, wp)
+        if not (r <= FUSED_MEAN_MAX_LEAK and rpk <= FUSED_MEAN_MAX_LEAK_PEAK):
+            # the provisional mean was too far off for fp32 accumulation: exact mean first (K0), then K1
+            two_pass = True
+            wp, res, nch, use_tc, hosted, has_offs = run(False)
+            fftinfo.tensor_cores = False
+            fftinfo.mean_fallback = ("provisional mean off by a leak ratio of %.1e: redone with the two-pass "
+                                     "detrend" % r)
     (Pxx, Pyy, Pxy, Cxy, Cxy2, phi_xy, h_rxx, h_ryy, h_rxy, h_icxy) = hosted[:10]
 
     freq = np.fft.fftfreq(nfft, 1.0 / plan.Fs)                     # :396
