@@ -443,39 +443,53 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
 #pragma unroll 1
         for (int s = 0; s < nseg; ++s) {
             const int slot = s & 1;
-            uint32_t pk[16];
-            bool live = true;
             PYFFT_TC_TRACE(0, s)
-#pragma unroll
-            for (int a = 0; a < 4; ++a) {
-                const int U = s * m + 4 * h + a;                             // unit index inside the CTA's span
-                const int blk = U >> lm, bs = blk & (nblk - 1);              // its block and the block's ring slot
-                if (!mbar_wait_abortable<32>(bar0 + 8 * (RAW_FULL + bs), (uint32_t)(blk >> (5 - lm)) & 1u, abort_flag)) {
-                    live = false;
-                    break;
-                }
-                const float* up = ring + bs * bpitch + (U & (m - 1)) * UNIT;
-                float v[8];
-#pragma unroll
-                for (int b = 0; b < 8; ++b) v[b] = up[64 * b];
-                float2 t[4];
-#pragma unroll
-                for (int b = 0; b < 4; ++b) t[b] = __fadd2_rn(make_float2(v[2 * b], v[2 * b + 1]), nm2);
-                if (4 * h + a < m) {                                         // the part of the segment inside its hop
-                    sum2 = __fadd2_rn(sum2, __fadd2_rn(__fadd2_rn(t[0], t[1]), __fadd2_rn(t[2], t[3])));
-                }
-#pragma unroll
-                for (int b = 0; b < 4; ++b) {
-                    const float2 o = __fmul2_rn(t[b], w2[4 * a + b]);
-                    pk[4 * a + b] = pack_h2(o.x, o.y);
-                }
-            }
-            if (!live) break;
-            PYFFT_TC_TRACE(1, s)
-            // the stage-1 MMAs of segment s-2 have finished reading this A1 slot
+            // the stage-1 MMAs of segment s-2 have finished reading this A1 slot (long ago in steady state)
             if (s >= 2 && !mbar_wait_abortable<32>(bar0 + 8 * (S1_DONE + slot), ((uint32_t)(s >> 1) & 1u) ^ 1u, abort_flag)) break;
             tc_fence_after();
-            tmem_st16(ta + 32 * slot, pk);
+            // software pipeline over the four units: the loads of unit a + 1 are in flight while unit a is
+            // converted; a block's barrier is waited for once (m = 4: one wait per segment and warp)
+            bool live = true;
+            int prev_blk = -1;
+            float v[2][8];
+            uint32_t pk[8];
+#define PYFFT_TC_LOAD(A, BUF)                                                                               \
+    {                                                                                                       \
+        const int U = s * m + 4 * h + (A);                     /* unit index inside the CTA's span */       \
+        const int blk = U >> lm, bs = blk & (nblk - 1);        /* its block and the block's ring slot */    \
+        if (blk != prev_blk) {                                                                              \
+            if (!mbar_wait_abortable<32>(bar0 + 8 * (RAW_FULL + bs), (uint32_t)(blk >> (5 - lm)) & 1u, abort_flag)) live = false; \
+            prev_blk = blk;                                                                                 \
+        }                                                                                                   \
+        const float* up = ring + bs * bpitch + (U & (m - 1)) * UNIT;                                        \
+        _Pragma("unroll") for (int b = 0; b < 8; ++b) v[BUF][b] = up[64 * b];                               \
+    }
+#define PYFFT_TC_CONV(A, BUF)                                                                               \
+    {                                                                                                       \
+        float2 t[4];                                                                                        \
+        _Pragma("unroll") for (int b = 0; b < 4; ++b)                                                       \
+            t[b] = __fadd2_rn(make_float2(v[BUF][2 * b], v[BUF][2 * b + 1]), nm2);                          \
+        if (4 * h + (A) < m)                                   /* the part of the segment inside its hop */ \
+            sum2 = __fadd2_rn(sum2, __fadd2_rn(__fadd2_rn(t[0], t[1]), __fadd2_rn(t[2], t[3])));            \
+        _Pragma("unroll") for (int b = 0; b < 4; ++b) {                                                     \
+            const float2 o = __fmul2_rn(t[b], w2[4 * (A) + b]);                                             \
+            pk[4 * ((A) & 1) + b] = pack_h2(o.x, o.y);                                                      \
+        }                                                                                                   \
+    }
+            PYFFT_TC_LOAD(0, 0)
+            PYFFT_TC_LOAD(1, 1)
+            PYFFT_TC_CONV(0, 0)
+            PYFFT_TC_LOAD(2, 0)
+            PYFFT_TC_CONV(1, 1)
+            tmem_st8(ta + 32 * slot, pk[0], pk[1], pk[2], pk[3], pk[4], pk[5], pk[6], pk[7]);
+            PYFFT_TC_LOAD(3, 1)
+            PYFFT_TC_CONV(2, 0)
+            PYFFT_TC_CONV(3, 1)
+            tmem_st8(ta + 32 * slot + 8, pk[0], pk[1], pk[2], pk[3], pk[4], pk[5], pk[6], pk[7]);
+#undef PYFFT_TC_LOAD
+#undef PYFFT_TC_CONV
+            if (!live) break;
+            PYFFT_TC_TRACE(1, s)
             tmem_st_wait();
             tc_fence_before();
             mbar_arrive(bar0 + 8 * (A1_FULL + slot));
@@ -496,9 +510,13 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
             const int64_t jc = (p.seg_first + c0) * p.hop;                     // first analysed sample of the CTA
             const int nblocks = nseg > 0 ? nseg - 1 + (8 >> lm) : 0;           // one block = one hop = m units
             const int nblk = NU >> lm;                                         // blocks in the ring
-            const uint32_t bbytes = (uint32_t)(m * UNIT + 4) * 4;              // bytes of a block per channel
+            const uint32_t bpitchb = (uint32_t)(m * UNIT + 4) * 4;             // bytes between blocks of a channel's ring
             const int shx = align_shift(direct_ptr(p.x, p.map, 0));
             const int shy = align_shift(direct_ptr(ysrc, p.map, 0));
+            // a copy starts at the 16-byte boundary at or below the block's first sample and ends at the one at or
+            // above its last: it never leaves the 16-byte granules that hold valid samples (no read past the
+            // end of the caller's allocation)
+            const uint32_t bx = (uint32_t)(m * UNIT) * 4 + (shx ? 16u : 0u), by = (uint32_t)(m * UNIT) * 4 + (shy ? 16u : 0u);
             const float* hx = p.head;
             const float* hy = p.head + (int64_t)(1 + pair) * HEADP;
             int done_seg = 0;                                                  // segments all converter warps have read
@@ -531,10 +549,10 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
                 const float* sy_ = in_head ? hy + j : dy_;
                 const int bs = B & (nblk - 1);
                 const uint32_t bar = bar0 + 8 * (RAW_FULL + bs);
-                const uint32_t dst = sm_addr + OFF_RING + bs * bbytes;
-                mbar_expect_tx(bar, 2 * bbytes);
-                bulk_load(dst, sx_, bbytes, bar);
-                bulk_load(dst + RING_CH_FLOATS * 4, sy_, bbytes, bar);
+                const uint32_t dst = sm_addr + OFF_RING + bs * bpitchb;
+                mbar_expect_tx(bar, bx + by);
+                bulk_load(dst, sx_, bx, bar);
+                bulk_load(dst + RING_CH_FLOATS * 4, sy_, by, bar);
                 if (B >= tb) { PYFFT_TC_TRACE(11, B - tb) }
             }
         } else if (tid == 544) {

@@ -242,3 +242,26 @@ def test_records_not_aligned_to_16_bytes(shift, refl, cuda_device):
     K = (n - L) // hop + 1
     a, b = _both_routes(cuda_device, x, y, hop, (n, 0, refl, 0, n), 0, K, (0, 65536), shift=shift)
     _assert_close(a, b, K)
+
+
+def test_record_that_ends_with_its_allocation(cuda_device):
+    """the TMA copies must not read past the last sample: a 256 MiB record is a whole number of allocator
+    pages, what follows it may be unmapped (this faulted once)."""
+    import torch
+    from pyfft_b200 import engine
+    from pyfft_b200.windows import windows
+    dev = cuda_device
+    n, hop = 2 ** 26, 2048
+    win = windows("Hanning", nwins=L, verbose=False)
+    torch.cuda.empty_cache()
+    g = torch.Generator(device=dev).manual_seed(1)
+    xd = torch.randn(n, device=dev, generator=g) + 7.0
+    yd = torch.randn(1, n, device=dev, generator=g) + 2.5
+    K = (n - L) // hop + 1
+    rmap = engine.record_map(n, 0, 0, 0, n)
+    wp = engine.WelchPlan(L, hop, 1, "fp32", win, dev)
+    wp.prepare_tc(xd, yd, rmap, 0, K * hop)
+    for _ in range(3):
+        wp.accumulate_tc(xd, yd, rmap, 0, K)
+    torch.cuda.synchronize()
+    assert not wp.tc_failed() and bool(torch.isfinite(wp.acc).all())
