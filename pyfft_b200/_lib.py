@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libpyfft_b200.so")
+LIB_PATH = os.environ.get("PYFFT_B200_LIB") or os.path.join(HERE, "libpyfft_b200.so")   # override: A/B builds (tools/)
 
 PYFFT_OK, PYFFT_EINVAL, PYFFT_EUNSUPPORTED, PYFFT_ECUDA = 0, -1, -2, -3
 F32, F64 = 0, 1

@@ -154,7 +154,6 @@ __device__ __forceinline__ bool mbar_wait_warp(uint32_t mbar, uint32_t parity, v
     if ((threadIdx.x & 31) == 0) ok = mbar_wait_abortable(mbar, parity, abort_flag) ? 1 : 0;
     return __shfl_sync(0xffffffffu, ok, 0) != 0;
 }
-
 // register reallocation between the warpgroups of a warp-specialised kernel
 template <int N>
 __device__ __forceinline__ void setmaxnreg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }

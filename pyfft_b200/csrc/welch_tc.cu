@@ -144,6 +144,13 @@ __device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&v)[16
         : "memory");
 }
 
+// timing experiments only (results invalid): bit 0 converters neither wait for nor read the ring, bit 1 the
+// twiddle role does not store, bit 2 the epilogue only loads, bit 3 no TMA copies (with bit 0), bit 4 only the
+// hi halves of the DFT matrices (12 of 24 MMAs per segment)
+#ifndef PYFFT_TC_ABLATE
+#define PYFFT_TC_ABLATE 0
+#endif
+
 // debug time line (tools/tc_trace.py): event EV of segment S of CTA (0, 0), stamped by one lane of a role
 #define PYFFT_TC_TRACE(EV, S) \
     if (trace_on && (S) < 128) p.trace[(S) * 16 + (EV)] = clock64();
@@ -260,7 +267,7 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
             tmem_ld8(col + 8, xb);
             tmem_ld8(col + YOFF + 8, yb);
 #define PYFFT_TC_ACC4(BASE, XV, YV)                                                                      \
-    _Pragma("unroll") for (int i = 0; i < 4; ++i) {                                                      \
+    if (!(PYFFT_TC_ABLATE & 4)) _Pragma("unroll") for (int i = 0; i < 4; ++i) {                                                      \
         const float2 x2 = make_float2(XV[2 * i], XV[2 * i + 1]), y2 = make_float2(YV[2 * i], YV[2 * i + 1]); \
         const float2 o2 = make_float2(__shfl_xor_sync(0xffffffffu, XV[2 * i], 1),                        \
                                       __shfl_xor_sync(0xffffffffu, XV[2 * i + 1], 1));                   \
@@ -393,8 +400,10 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
         const float2 re = __ffma2_rn(a2, wc[4 * (J) + i], make_float2(-t2.x, -t2.y));                    \
         const float2 im = __ffma2_rn(a2, ws[4 * (J) + i], __fmul2_rn(b2, wc[4 * (J) + i]));              \
         const int k1 = 8 * (J) + 2 * i;                                                                  \
+        if (!(PYFFT_TC_ABLATE & 2)) {                                                                    \
         *reinterpret_cast<uint32_t*>(bp + k1 * 128 + (xbase ^ (uint32_t)((k1 & 7) << 4))) = pack_h2(re.x, im.x);           \
         *reinterpret_cast<uint32_t*>(bp + (k1 + 1) * 128 + (xbase ^ (uint32_t)(((k1 + 1) & 7) << 4))) = pack_h2(re.y, im.y); \
+        }                                                                                                \
     }
             tmem_ld8(ca + 8, rb);
             tmem_ld8(ca + 40, ib);
@@ -448,13 +457,25 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
             if (s >= 2 && !mbar_wait_abortable<32>(bar0 + 8 * (S1_DONE + slot), ((uint32_t)(s >> 1) & 1u) ^ 1u, abort_flag)) break;
             tc_fence_after();
             // software pipeline over the four units: the loads of unit a + 1 are in flight while unit a is
-            // converted; a block's barrier is waited for once (m = 4: one wait per segment and warp)
+            // converted.  m >= 4 (hop 2048 / 4096): the warp's four units sit in ONE block of the ring -- one
+            // barrier wait and one base pointer per segment; otherwise per unit.
             bool live = true;
             int prev_blk = -1;
             float v[2][8];
             uint32_t pk[8];
+            const float* ub = ring;
+            if (m >= 4) {
+                const int U0 = s * m + 4 * h;
+                const int blk = U0 >> lm, bs = blk & (nblk - 1);
+                if (!(PYFFT_TC_ABLATE & 1))
+                    live = mbar_wait_abortable<32>(bar0 + 8 * (RAW_FULL + bs), (uint32_t)(blk >> (5 - lm)) & 1u, abort_flag);
+                ub = ring + bs * bpitch + (U0 & (m - 1)) * UNIT;
+            }
 #define PYFFT_TC_LOAD(A, BUF)                                                                               \
-    {                                                                                                       \
+    if (m >= 4) {                                                                                           \
+        _Pragma("unroll") for (int b = 0; b < 8; ++b)                                                       \
+            v[BUF][b] = (PYFFT_TC_ABLATE & 1) ? (float)(s + b) : ub[(A) * UNIT + 64 * b];                   \
+    } else {                                                                                                \
         const int U = s * m + 4 * h + (A);                     /* unit index inside the CTA's span */       \
         const int blk = U >> lm, bs = blk & (nblk - 1);        /* its block and the block's ring slot */    \
         if (blk != prev_blk) {                                                                              \
@@ -550,9 +571,11 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
                 const int bs = B & (nblk - 1);
                 const uint32_t bar = bar0 + 8 * (RAW_FULL + bs);
                 const uint32_t dst = sm_addr + OFF_RING + bs * bpitchb;
-                mbar_expect_tx(bar, bx + by);
-                bulk_load(dst, sx_, bx, bar);
-                bulk_load(dst + RING_CH_FLOATS * 4, sy_, by, bar);
+                if (!(PYFFT_TC_ABLATE & 8)) {
+                    mbar_expect_tx(bar, bx + by);
+                    bulk_load(dst, sx_, bx, bar);
+                    bulk_load(dst + RING_CH_FLOATS * 4, sy_, by, bar);
+                }
                 if (B >= tb) { PYFFT_TC_TRACE(11, B - tb) }
             }
         } else if (tid == 544) {
@@ -569,7 +592,7 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
                 tc_fence_after();
                 PYFFT_TC_TRACE(3, s)
 #pragma unroll
-                for (int hh = 0; hh < 2; ++hh)
+                for (int hh = 0; hh < ((PYFFT_TC_ABLATE & 16) ? 1 : 2); ++hh)
 #pragma unroll
                     for (int ks = 0; ks < 4; ++ks)
                         mma_f16_ts_lo(tbase + TM_D1 + slot * 64, tbase + TM_A1 + slot * 32 + ks * 8,
@@ -579,6 +602,11 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
             }
         } else if (tid == 576 || tid == 608) {
             // ================= stage 2: 128 x 80 x 128 (hi + lo) per segment; one thread per slot ===== //
+            // Measured alternatives (profiles/r02b_tc_experiments.txt): ONE thread for both slots 0.264 ms (its
+            // 16 x ~86 clocks of issue per segment become the period); the hi and the lo products of a segment
+            // from two threads 0.254 ms; the issuing warps converged with elect.sync (back-to-back UTCHMMA in
+            // SASS) 0.36-0.38 ms; waits parked in hardware instead of hot polls: no change; one polling lane per
+            // warp (+ shuffle) instead of every thread polling: 0.299 ms.
             constexpr uint32_t id2 = idesc_f16(128, NCOL);
             const int slot = tid == 608 ? 1 : 0;
             const uint32_t b2 = sw128_desc_lo(sm_addr + OFF_B2 + slot * B2_BYTES);
@@ -591,7 +619,7 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
                 tc_fence_after();
                 PYFFT_TC_TRACE(7, s)
 #pragma unroll
-                for (int hh = 0; hh < 2; ++hh)
+                for (int hh = 0; hh < ((PYFFT_TC_ABLATE & 16) ? 1 : 2); ++hh)
 #pragma unroll
                     for (int ks = 0; ks < 8; ++ks)
                         mma_f16_ts_lo(tbase + TM_D2 + slot * NCOL, tbase + (hh ? TM_F2LO : TM_F2HI) + ks * 8,
