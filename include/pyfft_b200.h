@@ -309,6 +309,30 @@ int pyfft_stft(int dtype, int32_t complex_in, const void* x, int64_t ch_stride, 
                int32_t power_out, void* out, double* pseg, void* stream);
 
 /* ------------------------------------------------------------------------- *
+ * Transforms of ARBITRARY length (Bluestein's chirp-z on the power-of-two kernels, float64 arithmetic)
+ * replaces: np.fft.fft in fft_pwelch (fft_analysis.py:375-388) and fftanal.fft_win (:2152-2176) when
+ *           nwins is not a power of two -- the reference never zero-pads (:219-221) and derives nwins
+ *           from Navr (:185-189, :2411-2418), default Navr = 8 -- for complex-valued inputs of
+ *           fft_pwelch (:123-127, :422-428), and np.fft.fft / ifft of hilbert.py:44-66 for any n.
+ * pyfft_stft_any: the contract of pyfft_stft for any seg->nfft >= 2 (real or interleaved complex
+ *   samples of `dtype`; window = double[nfft]; coef as pyfft_stft; out of `dtype`), at most 65535 rows
+ *   (nch x seg_count) per call; workspace = pyfft_anyfft_workspace_bytes(nfft, nch * seg_count).
+ * pyfft_fft_any: numpy.fft.fft / ifft (inverse != 0, includes 1/n) of `rows` rows of length n at
+ *   in + r * row_stride (elements; complex elements when complex_in), out complex [rows][n] of `dtype`.
+ * ------------------------------------------------------------------------- */
+int64_t pyfft_anyfft_workspace_bytes(int64_t n, int64_t rows);
+
+int pyfft_fft_any(int dtype, int32_t complex_in, const void* in, int64_t row_stride, int64_t n,
+                  int32_t rows, int32_t inverse, void* out, void* workspace, int64_t workspace_bytes,
+                  void* stream);
+
+int pyfft_stft_any(int dtype, int32_t complex_in, const void* x, int64_t ch_stride, int32_t nch,
+                   const pyfft_record_map* map, const pyfft_segmentation* seg, const double* window,
+                   const double* coef, int32_t detrend_per_segment, int32_t bin_first, int32_t nbins,
+                   const double* bin_scale, int32_t power_out, void* out, double* pseg,
+                   void* workspace, int64_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------- *
  * Spectral products of materialised STFTs (the non-fused path; used for
  * complex inputs and for the fftanal class path that keeps *_seg arrays)
  * replaces: fftanal.Pstft + averagewins means (fft_analysis.py:1944-1990) and

@@ -35,9 +35,6 @@ def fft_win(self, sig, tvec=None, detrendwin=False):
     Fs = self.__Fs__(tvec)
     nfft = nwins
     hop = nwins - noverlap
-    if nfft & (nfft - 1) or nfft < 16 or nfft > 8192:
-        raise NotImplementedError("nwins = %d: the GPU path needs a power-of-two window of 16..8192 "
-                                  "samples" % nfft)
     if (navr - 1) * hop + nwins > n:
         raise ValueError("operands could not be broadcast together: segment %d runs past the record"
                          % (navr - 1))

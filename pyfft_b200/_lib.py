@@ -66,6 +66,10 @@ _PROTOS = {
     "pyfft_welch_correlation": (C.c_int, [_vp, _i32, _i32, _i32, _i32, _vp, _vp]),
     "pyfft_stft": (C.c_int, [C.c_int, _i32, _vp, _i64, _i32, _pmap, _pseg, _vp, _vp, _i32, _i32, _i32,
                              _vp, _i32, _vp, _vp, _vp]),
+    "pyfft_anyfft_workspace_bytes": (_i64, [_i64, _i64]),
+    "pyfft_fft_any": (C.c_int, [C.c_int, _i32, _vp, _i64, _i64, _i32, _i32, _vp, _vp, _i64, _vp]),
+    "pyfft_stft_any": (C.c_int, [C.c_int, _i32, _vp, _i64, _i32, _pmap, _pseg, _vp, _vp, _i32, _i32, _i32,
+                                 _vp, _i32, _vp, _vp, _vp, _i64, _vp]),
     "pyfft_stft_products": (C.c_int, [C.c_int, _vp, _vp, _i32, _i64, _i32, _i32, _vp, _vp, _vp, _vp]),
     "pyfft_bigfft_workspace_bytes": (_i64, [C.c_int, _i64, _i32]),
     "pyfft_hilbert": (C.c_int, [C.c_int, _vp, _i64, _i32, _vp, _vp, _vp, _i64, _vp]),

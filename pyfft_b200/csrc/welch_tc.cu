@@ -146,7 +146,8 @@ __device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&v)[16
 
 // timing experiments only (results invalid): bit 0 converters neither wait for nor read the ring, bit 1 the
 // twiddle role does not store, bit 2 the epilogue only loads, bit 3 no TMA copies (with bit 0), bit 4 only the
-// hi halves of the DFT matrices (12 of 24 MMAs per segment)
+// hi halves of the DFT matrices (12 of 24 MMAs per segment), bit 5 / bit 6 the epilogue / twiddle role frees its
+// D2 / D1 slot before reading it (what more slots could give at best)
 #ifndef PYFFT_TC_ABLATE
 #define PYFFT_TC_ABLATE 0
 #endif
@@ -259,6 +260,7 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
             if (!mbar_wait_hot(bar0 + 8 * (S2_DONE + slot), (uint32_t)(s >> 1) & 1u, abort_flag)) break;
             tc_fence_after();
             PYFFT_TC_TRACE(9, s)
+            if (PYFFT_TC_ABLATE & 32) { tc_fence_before(); mbar_arrive(bar0 + 8 * (D2_FREE + slot)); }   // "free D2 at once"
             const uint32_t col = tl + slot * NCOL;
             float xa[8], ya[8], xb[8], yb[8];
             tmem_ld8(col, xa);
@@ -299,7 +301,7 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
             PYFFT_TC_ACC4(12, xb, yb)
             tmem_ld_wait();
             tc_fence_before();                                // D2 is in registers now
-            mbar_arrive(bar0 + 8 * (D2_FREE + slot));
+            if (!(PYFFT_TC_ABLATE & 32)) mbar_arrive(bar0 + 8 * (D2_FREE + slot));
             PYFFT_TC_TRACE(10, s)
             {
                 const float xo = __shfl_xor_sync(0xffffffffu, x32, 1);
@@ -385,6 +387,7 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
             if (!mbar_wait_hot(bar0 + 8 * (S1_DONE + slot), (uint32_t)(s >> 1) & 1u, abort_flag)) break;
             tc_fence_after();
             PYFFT_TC_TRACE(5, s)
+            if (PYFFT_TC_ABLATE & 64) { tc_fence_before(); mbar_arrive(bar0 + 8 * (D1_FREE + slot)); }   // "free D1 at once"
             const uint32_t ca = tl + slot * 64;
             unsigned char* bp = sm + OFF_B2 + slot * B2_BYTES + thread_off;
             float ra[8], ia[8], rb[8], ib[8];
@@ -418,7 +421,7 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
             PYFFT_TC_TWD(2, ra, ia)
             tmem_ld_wait();
             tc_fence_before();                            // the last D1 columns are in registers: slot free
-            mbar_arrive(bar0 + 8 * (D1_FREE + slot));
+            if (!(PYFFT_TC_ABLATE & 64)) mbar_arrive(bar0 + 8 * (D1_FREE + slot));
             PYFFT_TC_TWD(3, rb, ib)
             *reinterpret_cast<uint32_t*>(bp + 32 * 128 + xbase) = pack_h2(re32 * w32.x, re32 * w32.y);
             fence_async_smem();

@@ -461,18 +461,33 @@ def detrend_coefficients(x, rmap, mode, precision, nsig, group=None, j_span=None
     return coef
 
 
+def pow2_window(nfft):
+    """True when the in-CTA power-of-two transforms (K1 / K2 / K4) take this window length."""
+    nfft = int(nfft)
+    return 16 <= nfft <= 8192 and (nfft & (nfft - 1)) == 0
+
+
+_ANY_BUDGET = 1 << 30          # bytes of Bluestein workspace per call of the arbitrary-length route
+
+
+def _any_rows(n, want):
+    """Rows per pyfft_stft_any / pyfft_fft_any call so that its workspace stays near _ANY_BUDGET."""
+    per_row = check(lib.pyfft_anyfft_workspace_bytes(int(n), 2)) - check(lib.pyfft_anyfft_workspace_bytes(int(n), 1))
+    return int(max(1, min(want, 65535, _ANY_BUDGET // max(per_row, 1))))
+
+
 def stft(x, rmap, nfft, hop, seg_first, seg_count, window, precision, coef=None,
          per_segment=False, bin_first=0, nbins=None, bin_scale=None, power_out=False,
          want_pseg=False):
     """x: (C, n) real device tensor (or complex, interleaved) -> (out [C][K][nbins], pseg [C][K] | None).
 
-    out is complex64/128 (or float32/64 when power_out) following `precision`."""
+    out is complex64/128 (or float32/64 when power_out) following `precision`.  Window lengths that are
+    powers of two in 16..8192 run the fused in-CTA transform (pyfft_stft); every other length goes
+    through Bluestein's identity on the long-transform kernels (pyfft_stft_any, float64 arithmetic)."""
     dev = x.device
     cplx = x.is_complex()
     nch = x.shape[0]
     nbins = nfft if nbins is None else int(nbins)
-    win = torch.from_numpy(np.ascontiguousarray(np.asarray(window, dtype=np.float64))).to(
-        dev, _TORCH_REAL[precision])
     odt = _TORCH_REAL[precision] if power_out else _TORCH_CPLX[precision]
     out = torch.empty((nch, int(seg_count), nbins), dtype=odt, device=dev)
     pseg = torch.zeros((nch, int(seg_count)), dtype=torch.float64, device=dev) if want_pseg else None
@@ -481,14 +496,56 @@ def stft(x, rmap, nfft, hop, seg_first, seg_count, window, precision, coef=None,
         scale = torch.from_numpy(np.ascontiguousarray(np.asarray(bin_scale, dtype=np.float64))).to(dev)
         if scale.numel() != nbins:
             raise ValueError("bin_scale needs nbins entries")
-    seg = Segmentation(int(nfft), int(hop), int(seg_first), int(seg_count))
     xr = torch.view_as_real(x) if cplx else x
-    stride = x.stride(0)                                     # elements (complex elements for complex input)
-    check(lib.pyfft_stft(_CODE[precision], 1 if cplx else 0, _ptr(xr), stride * (2 if cplx else 1), nch,
-                         C.byref(rmap), C.byref(seg), _ptr(win), _ptr(coef), 1 if per_segment else 0,
-                         int(bin_first), nbins, _ptr(scale), 1 if power_out else 0, _ptr(out), _ptr(pseg),
-                         _stream()))
+    stride = x.stride(0) * (2 if cplx else 1)                # real elements between channels
+    if pow2_window(nfft):
+        win = torch.from_numpy(np.ascontiguousarray(np.asarray(window, dtype=np.float64))).to(
+            dev, _TORCH_REAL[precision])
+        seg = Segmentation(int(nfft), int(hop), int(seg_first), int(seg_count))
+        check(lib.pyfft_stft(_CODE[precision], 1 if cplx else 0, _ptr(xr), stride, nch,
+                             C.byref(rmap), C.byref(seg), _ptr(win), _ptr(coef), 1 if per_segment else 0,
+                             int(bin_first), nbins, _ptr(scale), 1 if power_out else 0, _ptr(out), _ptr(pseg),
+                             _stream()))
+        return out, pseg
+    # arbitrary window length: one channel and a chunk of segments per call, written in place
+    win = torch.from_numpy(np.ascontiguousarray(np.asarray(window, dtype=np.float64))).to(dev)
+    rows = _any_rows(nfft, int(seg_count))
+    wsb = check(lib.pyfft_anyfft_workspace_bytes(int(nfft), rows))
+    ws = torch.empty(wsb, dtype=torch.uint8, device=dev)
+    esz = xr.element_size()
+    cstep = 4 if cplx else 2                                  # doubles of coef per channel
+    for c in range(nch):
+        for k0 in range(0, int(seg_count), rows):
+            kc = min(rows, int(seg_count) - k0)
+            seg = Segmentation(int(nfft), int(hop), int(seg_first) + k0, kc)
+            o = out[c, k0:k0 + kc]
+            check(lib.pyfft_stft_any(_CODE[precision], 1 if cplx else 0, C.c_void_p(xr.data_ptr() + c * stride * esz),
+                                     stride, 1, C.byref(rmap), C.byref(seg), _ptr(win),
+                                     C.c_void_p(coef.data_ptr() + 8 * cstep * c) if coef is not None else C.c_void_p(0),
+                                     1 if per_segment else 0, int(bin_first), nbins, _ptr(scale),
+                                     1 if power_out else 0, C.c_void_p(o.data_ptr()),
+                                     C.c_void_p(pseg.data_ptr() + 8 * (c * int(seg_count) + k0)) if pseg is not None
+                                     else C.c_void_p(0), _ptr(ws), wsb, _stream()))
     return out, pseg
+
+
+def fft_any(z, precision, inverse=False):
+    """(batch, n) real or complex device tensor, ANY n -> numpy.fft.fft / ifft along the last axis
+    (complex of `precision`); powers of two >= 16 with complex input take pyfft_fft_c2c directly."""
+    batch, n = z.shape
+    z = z.contiguous()
+    if z.is_complex() and _is_pow2(n) and n >= 16:
+        return fft_c2c(z, precision, inverse=inverse)
+    out = torch.empty((batch, n), dtype=_TORCH_CPLX[precision], device=z.device)
+    rows = _any_rows(n, batch)
+    wsb = check(lib.pyfft_anyfft_workspace_bytes(int(n), rows))
+    ws = torch.empty(wsb, dtype=torch.uint8, device=z.device)
+    zr = torch.view_as_real(z) if z.is_complex() else z
+    for r0 in range(0, batch, rows):
+        rc = min(rows, batch - r0)
+        check(lib.pyfft_fft_any(_CODE[precision], 1 if z.is_complex() else 0, _ptr(zr[r0]), n, n, rc,
+                                1 if inverse else 0, C.c_void_p(out[r0].data_ptr()), _ptr(ws), wsb, _stream()))
+    return out
 
 
 def stft_sharded(x, group, rmap, nfft, hop, seg_first, seg_count, window, precision, gather=False, **kw):

@@ -261,13 +261,21 @@ def _make_segment_loader(sigx, sigy, ntv, plan, win, mode, precision, dev, onesi
         nw, K = plan.nwins, plan.Navr
         hop = nw - plan.noverlap
         with torch.cuda.device(dev):
-            x = _eng.to_device(sigx, precision, dev).reshape(1, -1).contiguous()
-            y = _eng.channels_first(_eng.to_device(sigy, precision, dev), ntv)
+            cplx = any((a.is_complex() if isinstance(a, torch.Tensor) else np.iscomplexobj(a)) for a in (sigx, sigy))
+            x = _eng.to_device(sigx, precision, dev, complex_ok=True).reshape(1, -1).contiguous()
+            y = _eng.channels_first(_eng.to_device(sigy, precision, dev, complex_ok=True), ntv)
+            if cplx:
+                cdt = torch.complex128 if precision == "fp64" else torch.complex64
+                x, y = x.to(cdt), y.to(cdt)
             rmap = _eng.record_map(plan.nana, plan.i0, nw - 1 if plan.reflect else 0, 0, x.shape[1])
             out = {}
             specs = []
             for sig in (x, y):
-                coef = _eng.detrend_coefficients(sig, rmap, mode, precision, plan.nana)
+                if cplx and mode != _lib.DETREND_NONE:
+                    parts = torch.view_as_real(sig).permute(0, 2, 1).reshape(2 * sig.shape[0], -1).contiguous()
+                    coef = _eng.detrend_coefficients(parts, rmap, mode, precision, plan.nana)
+                else:
+                    coef = _eng.detrend_coefficients(sig, rmap, mode, precision, plan.nana)
                 S, _ = _eng.stft(sig, rmap, nw, hop, 0, K, win, precision, coef=coef)
                 specs.append(S.to(torch.complex128))
             X, Y = specs[0][0], specs[1]                               # (K, nfft), (nch, K, nfft)
@@ -287,6 +295,90 @@ def _make_segment_loader(sigx, sigy, ntv, plan, win, mode, precision, dev, onesi
         out["varphi_seg"] = np.zeros_like(out["phixy_seg"])
         return out
     return load
+
+
+def _pwelch_generic(sigx, sigy, ntv, plan, win, mode, precision, dev, onesided, scale, lp, group, is_cplx):
+    """fft_pwelch for any window length and for complex-valued records (fft_analysis.py:359-446 with
+    :123-127, :422-428): segment spectra by pyfft_stft_any in chunks, products summed on the device
+    (pyfft_stft_products, Y conj(X) :393), then the O(nfft) bookkeeping of :402-446, :489-520,
+    :544-597 in numpy on the summed spectra.  -> (nch, [Pxx, Pyy, Pxy, Cxy, Cxy2, phi, Rxx, Ryy, Rxy, iCxy])."""
+    nw, K = plan.nwins, plan.Navr
+    hop = nw - plan.noverlap
+    refl = nw - 1 if plan.reflect else 0
+    k0, k1 = lp["k0"], lp["k1"]
+    with torch.cuda.device(dev):
+        def prep(sig, two_d):
+            t = _eng.to_device(sig, precision, dev, complex_ok=True)
+            t = _eng.channels_first(t, ntv) if two_d else t.reshape(1, -1).contiguous()
+            if is_cplx and not t.is_complex():
+                t = t.to(torch.complex128 if precision == "fp64" else torch.complex64)
+            return t
+        x, y = prep(sigx, False), prep(sigy, True)
+        nch = y.shape[0]
+        rmap = _eng.record_map(plan.nana, plan.i0, refl, 0, x.shape[1])
+
+        def coefs(sig):
+            if mode == _lib.DETREND_NONE:
+                return None
+            if not is_cplx:
+                return _eng.detrend_coefficients(sig, rmap, mode, precision, plan.nana, group=group,
+                                                 j_span=lp["stats_span"])
+            if mode == _lib.DETREND_LINEAR:
+                raise NotImplementedError("linear detrend of complex records")
+            parts = torch.view_as_real(sig).permute(0, 2, 1).reshape(2 * sig.shape[0], -1).contiguous()
+            return _eng.detrend_coefficients(parts, rmap, mode, precision, plan.nana, group=group,
+                                             j_span=lp["stats_span"])
+        cx, cy = coefs(x), coefs(y)
+        sxx = torch.zeros(nw, dtype=torch.float64, device=dev)
+        syy = torch.zeros((nch, nw), dtype=torch.float64, device=dev)
+        sxy = torch.zeros((nch, nw), dtype=torch.complex128, device=dev)
+        # chunk of segments: the spectra of all channels of a chunk live on the device at once
+        per_seg = (nch + 1) * nw * (16 if precision == "fp64" else 8)
+        step = int(max(1, min(k1 - k0, (1 << 28) // per_seg))) if k1 > k0 else 1
+        for a in range(k0, k1, step):
+            kc = min(step, k1 - a)
+            X, _ = _eng.stft(x, rmap, nw, hop, a, kc, win, precision, coef=cx)
+            Y, _ = _eng.stft(y, rmap, nw, hop, a, kc, win, precision, coef=cy)
+            pxx, pyy, pxy = _eng.stft_products(X[0], Y, True, precision)
+            sxx += pxx
+            syy += pyy
+            sxy += pxy
+        if group is not None:
+            packed = torch.cat((sxx, syy.reshape(-1), torch.view_as_real(sxy).reshape(-1)))
+            torch.distributed.all_reduce(packed, group=group)
+            sxx = packed[:nw]
+            syy = packed[nw:nw + nch * nw].view(nch, nw)
+            sxy = torch.view_as_complex(packed[nw + nch * nw:].view(nch, nw, 2))
+        hxx, hyy, hxy = _host_many([sxx, syy, sxy])
+    nnyq = plan.Nnyquist
+    if onesided:                                                   # :402-421
+        wgt = np.ones(nnyq)
+        wgt[1:-1] = 2.0
+        if nw % 2:
+            wgt[-1] = 2.0
+        hxx, hyy, hxy = hxx[:nnyq] * wgt, hyy[:, :nnyq] * wgt, hxy[:, :nnyq] * wgt
+    else:                                                          # :422-428
+        hxx, hyy, hxy = (np.fft.fftshift(a, axes=-1) for a in (hxx, hyy, hxy))
+    sc = scale / K                                                 # :432-446
+    Pxx = (hxx * sc).astype(np.complex128)
+    Pyy = (hyy * sc).T.astype(np.complex128)
+    Pxy = (hxy * sc).T
+    with np.errstate(all="ignore"):
+        Cxy, Cxy2 = Cxy_Cxy2(Pxx, Pyy, Pxy)                        # :489, :1662-1680
+    phi = np.arctan2(Pxy.imag, Pxy.real)                           # :520
+    corr = []
+    for P, halve in ((Pxx, True), (Pyy, True), (Pxy, True), (Cxy, False)):   # :544-597
+        if onesided:
+            q = np.array(P, dtype=np.complex128, copy=True)
+            if halve:
+                q[1:-1, ...] *= 0.5
+                if nw % 2:
+                    q[-1, ...] *= 0.5
+            r = np.fft.irfft(q, n=nw, axis=0)
+        else:
+            r = np.fft.ifft(np.fft.ifftshift(P, axes=0), n=nw, axis=0)
+        corr.append(np.fft.fftshift(r * np.sqrt(nw), axes=0))
+    return nch, [Pxx, Pyy, Pxy, Cxy, Cxy2, phi] + corr
 
 
 def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
@@ -338,12 +430,6 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
     fftinfo.ibnds = [plan.i0, plan.i1]
     fftinfo.S1, fftinfo.S2, fftinfo.NENBW, fftinfo.ENBW = fftanal._getNorms(win, plan.Nnyquist, plan.Fs)
 
-    if is_cplx:
-        raise NotImplementedError("complex-valued inputs (two-sided spectra of complex data) "
-                                  "are not supported yet")
-    if nfft & (nfft - 1) or nfft < 16 or nfft > 8192:
-        raise NotImplementedError("nwins = %d: the GPU path needs a power-of-two window of 16..8192 "
-                                  "samples (choose Navr/tper accordingly)" % nfft)
     precision = _eng.resolve_precision(precision, sigx, sigy)
     dev = _eng.require_cuda(device)
     hop = nwins - plan.noverlap
@@ -497,7 +583,15 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
         per_peak = max(np.max(lx) / pkx, np.max(ly / pky[None, :]))
         return float(per_bin), float(per_peak)
 
-    wp, res, nch, use_tc, hosted, has_offs = run(tensor_cores)
+    generic = is_cplx or not _eng.pow2_window(nfft)
+    if generic:
+        # window lengths that are not powers of two (the reference's default Navr = 8 gives them) and
+        # complex-valued records: per-segment spectra by Bluestein (pyfft_stft_any), products on the device
+        wp, res, use_tc, has_offs = None, None, False, False
+        nch, hosted = _pwelch_generic(sigx, sigy, ntv, plan, win, mode, precision, dev, bool(onesided), scale,
+                                      lp, group, is_cplx)
+    else:
+        wp, res, nch, use_tc, hosted, has_offs = run(tensor_cores)
     fftinfo.tensor_cores = bool(use_tc)
     fftinfo.tc_fallback = None
     fftinfo.mean_fallback = None
@@ -595,6 +689,9 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
     fftinfo._segment_loader = _make_segment_loader(sigx, sigy, ntv, plan, win, mode, precision, dev,
                                                    bool(onesided), scale)
     if return_device:
+        if res is None:
+            res = dict((k, torch.from_numpy(np.ascontiguousarray(v)).to(dev)) for k, v in
+                       (("Pxy", Pxy), ("Pxx", Pxx), ("Pyy", Pyy), ("Cxy", Cxy), ("phi_xy", phi_xy)))
         return (torch.from_numpy(freq).to(dev), res["Pxy"], res["Pxx"], res["Pyy"], res["Cxy"],
                 res["phi_xy"], fftinfo)
     return freq, Pxy, Pxx, Pyy, Cxy, phi_xy, fftinfo

@@ -3,7 +3,9 @@ the bin mask and one long inverse FFT, all inside pyfft_hilbert (K3b).
 
 Same names, arguments and return values as hilbert.py:22-112; the extra keywords
 (``precision``, ``device``, ``return_device``, ``envelope``) default to the reference's
-behaviour.  Lengths that are not powers of two raise NotImplementedError (no CPU fallback).
+behaviour.  Lengths that are not powers of two (or shorter than 16) take Bluestein's identity on the
+same long-transform kernels (pyfft_fft_any: forward, the bin mask of hilbert.py:47-64 including its
+odd-n form, inverse); there is no CPU fallback.
 """
 import numpy as np
 import torch
@@ -34,9 +36,22 @@ def _prepare(uin, nfft, axes, precision, device):
         u2 = u2[:, :nfft]
     elif nfft > n:                                  # ... or zero-pads (hilbert.py:54)
         u2 = torch.nn.functional.pad(u2, (0, nfft - n))
-    if not engine._is_pow2(nfft) or nfft < 16:
-        raise NotImplementedError("hilbert: nfft = %d is not a power of two >= 16 (GPU path only)" % nfft)
     return u2, prec, (u.dim() == 2 and ax == 0), u.dim()
+
+
+def _analytic(u2, prec, want_analytic=True, want_envelope=False):
+    """(analytic | None, envelope | None) of the rows of u2: the fused K3b kernel for powers of two,
+    else forward transform of any length, mask, inverse transform."""
+    n = u2.shape[1]
+    if engine._is_pow2(n) and n >= 16:
+        return engine.hilbert(u2, prec, want_analytic=want_analytic, want_envelope=want_envelope)
+    U = engine.fft_any(u2, prec)                                   # hilbert.py:54
+    nyq = (n + 1) // 2 if n % 2 else n // 2                        # :47-51
+    mask = torch.ones(n, dtype=U.real.dtype, device=U.device)
+    mask[nyq + 1:] = 0.0                                           # :63
+    mask[1:nyq] = 2.0                                              # :64
+    z = engine.fft_any(U * mask, prec, inverse=True)               # :67
+    return (z if want_analytic else None), (z.abs() if want_envelope else None)
 
 
 def hilbert(uin, nfft=None, axes=-1, precision=None, device=None, return_device=False, envelope=False,
@@ -54,7 +69,7 @@ def hilbert(uin, nfft=None, axes=-1, precision=None, device=None, return_device=
         z = torch.empty((0, u2.shape[1]), dtype=engine._TORCH_CPLX[prec], device=u2.device)
         env = torch.empty((0, u2.shape[1]), dtype=engine._TORCH_REAL[prec], device=u2.device)
     else:
-        z, env = engine.hilbert(u2, prec, want_analytic=not envelope, want_envelope=envelope)
+        z, env = _analytic(u2, prec, want_analytic=not envelope, want_envelope=envelope)
     out = env if envelope else z
     if group is not None and ndim == 2 and gather:
         out = _dist.gather_channels(out, nrec, group)
@@ -76,7 +91,7 @@ def hilbert_1d(uin, nfft=None, precision=None, device=None, return_device=False)
     if uin.ndim != 1:
         raise ValueError("hilbert_1d expects a 1-D signal")
     u2, prec, _, _ = _prepare(uin, nfft, -1, precision, device)
-    z, _ = engine.hilbert(u2, prec)
+    z, _ = _analytic(u2, prec)
     if return_device:
         return z[0]
     return z[0].cpu().numpy().astype(np.complex128)

@@ -27,13 +27,37 @@ def test_hilbert_matches_reference_golden(precision, cuda_device):
     assert relerr(hilbert(ub.T.copy(), axes=0, precision=precision), g["z_batch"].T) <= TOLZ[precision]
 
 
-def test_hilbert_non_power_of_two_fails_loudly(cuda_device):
-    from pyfft_b200 import hilbert
+@pytest.mark.parametrize("precision", ["fp64", "fp32"])
+def test_hilbert_any_length_matches_reference(precision, cuda_device):
+    """n = 33 (odd: the reference's own mask rule, hilbert.py:47-51, 63-64) and n = 1000 through
+    Bluestein on the long-transform kernels, against the outputs of the unmodified reference."""
+    from pyfft_b200 import hilbert, hilbert_1d
     g = load_golden("hilbert")
-    with pytest.raises(NotImplementedError):
-        hilbert(g["u_33"])
-    with pytest.raises(NotImplementedError):
-        hilbert(g["u_1000"])
+    for n in (33, 1000):
+        u = g["u_%d" % n] if precision == "fp64" else g["u_%d" % n].astype(np.float32)
+        z = hilbert(u, precision=precision)
+        assert z.shape == (n,) and z.dtype == np.complex128
+        assert relerr(z, g["z_%d" % n]) <= TOLZ[precision], (n, relerr(z, g["z_%d" % n]))
+        assert relerr(hilbert_1d(u, precision=precision), g["z_%d" % n]) <= TOLZ[precision]
+        env = hilbert(u, precision=precision, envelope=True)
+        assert relerr(env, np.abs(g["z_%d" % n])) <= TOLZ[precision]
+
+
+@pytest.mark.parametrize("n", [2, 3, 5, 17, 100, 1023, 1025, 4097, 30011, 65537])
+def test_fft_any_matches_numpy(n, cuda_device):
+    """pyfft_fft_any against numpy.fft for awkward lengths (primes, 2^k +- 1), real and complex rows,
+    forward and inverse."""
+    import torch
+    from pyfft_b200 import engine
+    rng = np.random.default_rng(n)
+    a = rng.standard_normal((3, n)) + 1j * rng.standard_normal((3, n))
+    z = torch.from_numpy(a).to(cuda_device)
+    assert relerr(engine.fft_any(z, "fp64").cpu().numpy(), np.fft.fft(a, axis=-1)) <= 1e-12
+    assert relerr(engine.fft_any(z, "fp64", inverse=True).cpu().numpy(), np.fft.ifft(a, axis=-1)) <= 1e-12
+    r = torch.from_numpy(a.real.copy()).to(cuda_device)
+    assert relerr(engine.fft_any(r, "fp64").cpu().numpy(), np.fft.fft(a.real, axis=-1)) <= 1e-12
+    z32 = z.to(torch.complex64)
+    assert relerr(engine.fft_any(z32, "fp32").cpu().numpy(), np.fft.fft(a.astype(np.complex64).astype(complex), axis=-1)) <= 2e-6
 
 
 @pytest.mark.parametrize("log2n", [14, 19, 22])
