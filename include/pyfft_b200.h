@@ -309,6 +309,33 @@ int pyfft_stft(int dtype, int32_t complex_in, const void* x, int64_t ch_stride, 
                int32_t power_out, void* out, double* pseg, void* stream);
 
 /* ------------------------------------------------------------------------- *
+ * Spectrum post-processing on the device, float64, batched over columns.
+ * pyfft_find_peaks
+ *   replaces: the selection loop of getNpeaks (fft_analysis.py:985-1027): npeaks times argmax of
+ *   L[nfreq][ncol] (column-wise; first occurrence on ties) followed by the removal of irem//2 surviving
+ *   bins on either side -- in the reference's COMPRESSED indexing, with its literal edge rules (:1010-1017).
+ *   idx[ncol][npeaks] receives the original bin of every peak, -1 once nothing survives.  nfreq <= 16384.
+ * pyfft_band_integrate
+ *   replaces: integratespectra's integrals (:890-903) and power-weighted frequency (:931-935): for every
+ *   band [lo, hi] (bands = double[nbands][2]) and column, trapezoid integrals over the bins with
+ *   lo <= freq <= hi of Pxy, Pxx, Pyy (complex128 [nfreq][ncol]; Pxx [nfreq][pxx_cols], pxx_cols 1 or ncol).
+ *   out = double[nbands][ncol][8]: Re/Im Pxy_i, Re/Im Pxx_i, Re/Im Pyy_i, fweighted, bins in the band.
+ * pyfft_mean_angle
+ *   replaces: mean_angle (:1334-1377) along axis 0 of phi[K][ncol] (`dtype` real; vphi, vsyst optional,
+ *   same shape): out = double[ncol][4] = nanmean cos, nanmean sin and their variances incl. the
+ *   propagated terms; the caller finishes with varphi (:1300-1330).
+ * ------------------------------------------------------------------------- */
+int pyfft_find_peaks(const double* L, int32_t nfreq, int32_t ncol, int32_t npeaks, int32_t irem,
+                     int32_t* idx, void* stream);
+
+int pyfft_band_integrate(const double* freq, int32_t nfreq, const double* Pxy, const double* Pxx,
+                         int32_t pxx_cols, const double* Pyy, int32_t ncol, const double* bands,
+                         int32_t nbands, double* out, void* stream);
+
+int pyfft_mean_angle(int dtype, const void* phi, const void* vphi, const void* vsyst, int64_t K,
+                     int64_t ncol, double* out, void* stream);
+
+/* ------------------------------------------------------------------------- *
  * Transforms of ARBITRARY length (Bluestein's chirp-z on the power-of-two kernels, float64 arithmetic)
  * replaces: np.fft.fft in fft_pwelch (fft_analysis.py:375-388) and fftanal.fft_win (:2152-2176) when
  *           nwins is not a power of two -- the reference never zero-pads (:219-221) and derives nwins
@@ -321,6 +348,13 @@ int pyfft_stft(int dtype, int32_t complex_in, const void* x, int64_t ch_stride, 
  *   in + r * row_stride (elements; complex elements when complex_in), out complex [rows][n] of `dtype`.
  * ------------------------------------------------------------------------- */
 int64_t pyfft_anyfft_workspace_bytes(int64_t n, int64_t rows);
+
+/* laplace.laplace_1d (laplace.py:85-113): out[r][k] = rfft over m of
+ * u[m] exp(sigma_r (n-1-m)) / sum_j exp(sigma_r j), k = 0 .. n/2, for every damping sigma_r -- the
+ * exponential weights are applied while the rows are packed; any n; out complex [nsigma][n/2+1] of
+ * `dtype`; workspace = pyfft_anyfft_workspace_bytes(n, nsigma); nsigma <= 65535 per call. */
+int pyfft_laplace_1d(int dtype, const void* u, int64_t n, const double* sigma, int32_t nsigma,
+                     void* out, void* workspace, int64_t workspace_bytes, void* stream);
 
 int pyfft_fft_any(int dtype, int32_t complex_in, const void* in, int64_t row_stride, int64_t n,
                   int32_t rows, int32_t inverse, void* out, void* workspace, int64_t workspace_bytes,

@@ -181,8 +181,63 @@ def gen_fft_deriv():
     print("wrote fft_deriv")
 
 
+def gen_extras():
+    """Round-2 fixtures from the unmodified reference (own RNG): getNpeaks (fft_analysis.py:940-1027),
+    fftanal.fftpwelch + crosscorr (:1794-1803, :1840-1878; 1-D sigy -- with 2-D sigy, and for crosscorr_stft /
+    convert2amplitudes in every case, the reference itself raises), mean_angle (:1334-1377),
+    fftanal.intspectra (:2514-2536) and laplace.laplace_1d (laplace.py:85-113)."""
+    import importlib.util
+    import warnings
+    warnings.simplefilter("ignore")
+    m = ref_shim.load_reference()
+    fa = m["fft_analysis"]
+    rng = np.random.default_rng(835)
+    n = 2 ** 15
+    t = np.arange(n) / 1.0e5
+    x = np.sin(2 * np.pi * 3e3 * t) + 0.6 * np.sin(2 * np.pi * 11e3 * t + 0.3) + 0.3 * rng.standard_normal(n)
+    y = 0.5 * np.sin(2 * np.pi * 3e3 * t - 0.4) + 0.25 * np.sin(2 * np.pi * 11e3 * t + 1.1) \
+        + 0.1 * np.sin(2 * np.pi * 23e3 * t) * 0 + 0.2 * rng.standard_normal(n) + 0.05 * np.roll(x, 7)
+    d = dict(t_n=np.asarray(n), t_fs=np.asarray(1.0e5), x=x, y=y)
+    kw = dict(Navr=63, windowoverlap=0.5, windowfunction="Hanning", detrend_style=1)
+    for npk, tag in ((1, "1"), (4, "4")):
+        out = fa.getNpeaks(npk, t, x, y, plotit=False, useMLAB=False, verbose=False, **kw)
+        d["peaks_" + tag] = np.asarray([[float(v) for v in row] for row in out])
+    out = fa.getNpeaks(3, t, x, y, plotit=False, useMLAB=False, verbose=False, minsep=2000.0, **kw)
+    d["peaks_minsep"] = np.asarray([[float(v) for v in row] for row in out])
+    o = fa.fftanal(t, x, y, Navr=63, windowoverlap=0.5, verbose=False)
+    o.fftpwelch()
+    o.crosscorr()
+    for nm in ("Pxx", "Pyy", "Pxy", "Rxx", "Ryy", "Rxy", "corrcoef", "Ex", "Ey", "lags", "freq"):
+        d["cls_" + nm] = np.asarray(getattr(o, nm))
+    ph = rng.uniform(-1.2, 1.2, (50, 3))
+    vph = rng.uniform(0.0, 0.05, (50, 3))
+    d["ma_phi"], d["ma_vphi"] = ph, vph
+    for tag, args in (("a", dict()), ("b", dict(vphi=vph)), ("c", dict(vphi=vph, dim=1, angle_range=np.pi))):
+        mp, vp = fa.mean_angle(ph, **args)
+        d["ma_mean_" + tag], d["ma_var_" + tag] = np.asarray(mp), np.asarray(vp)
+    fr = np.arange(257) * 195.3125
+    sp = np.abs(rng.standard_normal(257)) + 20.0 * np.exp(-0.5 * ((np.arange(257) - 90) / 2.0) ** 2)
+    d["is_freq"], d["is_spec"] = fr, sp
+    d["is_default"] = np.asarray(fa.fftanal.intspectra(fr, sp)[0])
+    d["is_enbw"] = np.asarray(fa.fftanal.intspectra(fr, sp, ENBW=600.0)[0])
+    d["is_whole"] = np.asarray(fa.fftanal.intspectra(fr, sp, ifreq=40)[0])      # ifreq given, ispan None: whole range
+    # (ifreq AND ispan given leaves ilow unbound in the reference: UnboundLocalError, :2528-2534)
+    spec = importlib.util.spec_from_file_location("FFT.laplace", os.path.join(ref_shim.REFERENCE_DIR, "laplace.py"))
+    lp = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(lp)
+    for nl in (300, 512):
+        u = np.cos(2 * np.pi * 0.02 * np.arange(nl) - 0.2) * np.exp(-np.arange(nl) / 150.0) + 0.05 * rng.standard_normal(nl)
+        sig = np.arange(-0.04, 0.04 + 1e-9, 0.01)
+        d["lp_u_%d" % nl], d["lp_sigma_%d" % nl] = u, sig
+        d["lp_out_%d" % nl] = lp.laplace_1d(u, sig)
+    np.savez_compressed(os.path.join(OUT, "extras.npz"), **d)
+    print("wrote extras", d["peaks_4"])
+
+
 if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "fft_deriv":
         gen_fft_deriv()
+    elif len(sys.argv) > 1 and sys.argv[1] == "extras":
+        gen_extras()
     else:
         main()

@@ -9,7 +9,9 @@ the CUDA extension has not been built (there is no CPU fallback).
 from . import _lib                      # noqa: F401  (fails loudly when the .so is missing)
 from .windows import windows            # noqa: F401
 from .fft_analysis import (fft_pwelch, fftanal, cross_spectral_matrix, fft_deriv, fftinfosc, Cxy_Cxy2,  # noqa: F401
-                           detrend_none, detrend_mean, detrend_linear)
+                           detrend_none, detrend_mean, detrend_linear, getNpeaks, integratespectra,
+                           mean_angle, varcoh, varphi)
+from .laplace import laplace_1d         # noqa: F401,E402
 
 from .spectrogram import stft, specgram  # noqa: F401,E402
 from .hilbert import hilbert, hilbert_1d  # noqa: F401,E402

@@ -66,7 +66,11 @@ _PROTOS = {
     "pyfft_welch_correlation": (C.c_int, [_vp, _i32, _i32, _i32, _i32, _vp, _vp]),
     "pyfft_stft": (C.c_int, [C.c_int, _i32, _vp, _i64, _i32, _pmap, _pseg, _vp, _vp, _i32, _i32, _i32,
                              _vp, _i32, _vp, _vp, _vp]),
+    "pyfft_find_peaks": (C.c_int, [_vp, _i32, _i32, _i32, _i32, _vp, _vp]),
+    "pyfft_band_integrate": (C.c_int, [_vp, _i32, _vp, _vp, _i32, _vp, _i32, _vp, _i32, _vp, _vp]),
+    "pyfft_mean_angle": (C.c_int, [C.c_int, _vp, _vp, _vp, _i64, _i64, _vp, _vp]),
     "pyfft_anyfft_workspace_bytes": (_i64, [_i64, _i64]),
+    "pyfft_laplace_1d": (C.c_int, [C.c_int, _vp, _i64, _vp, _i32, _vp, _vp, _i64, _vp]),
     "pyfft_fft_any": (C.c_int, [C.c_int, _i32, _vp, _i64, _i64, _i32, _i32, _vp, _vp, _i64, _vp]),
     "pyfft_stft_any": (C.c_int, [C.c_int, _i32, _vp, _i64, _i32, _pmap, _pseg, _vp, _vp, _i32, _i32, _i32,
                                  _vp, _i32, _vp, _vp, _vp, _i64, _vp]),

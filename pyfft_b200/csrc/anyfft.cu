@@ -55,6 +55,22 @@ __global__ void __launch_bounds__(256) any_pack_rows_kernel(const In* __restrict
     }
 }
 
+// rows of laplace_1d (laplace.py:85-113): row r = u[m] * exp(sigma_r (n-1-m)) / sum_k exp(sigma_r k), then chirp
+template <typename In>
+__global__ void __launch_bounds__(256) any_pack_laplace_kernel(const In* __restrict__ u, int64_t n, int64_t M,
+                                                               const double* __restrict__ sigma, const zc* __restrict__ c,
+                                                               zc* __restrict__ a) {
+    const int64_t r = blockIdx.y;
+    const double sg = sigma[r];
+    const double S = sg != 0.0 ? expm1(sg * (double)n) / expm1(sg) : (double)n;     // geometric series
+    zc* dst = a + r * M;
+    for (int64_t m = (int64_t)blockIdx.x * 256 + threadIdx.x; m < M; m += (int64_t)gridDim.x * 256) {
+        zc v = mk<double>(0.0, 0.0);
+        if (m < n) v = cmul(mk<double>((double)u[m] * (exp(sg * (double)(n - 1 - m)) / S), 0.0), c[m]);
+        dst[m] = v;
+    }
+}
+
 // segments of channel records (record map, trend, optional per-segment mean, window), one CTA per row (c, k)
 template <typename In, bool CPLX>
 __global__ void __launch_bounds__(256) any_pack_segments_kernel(const In* __restrict__ x, int64_t ch_stride, RecMap map,
@@ -244,6 +260,28 @@ int pyfft_fft_any(int dtype, int32_t complex_in, const void* in, int64_t row_str
     const double scale = inverse ? 1.0 / (double)n : 1.0;
     if (dtype == PYFFT_F32) return any_unpack<float>(w, n, rows, inverse, scale, 0, n, nullptr, 0, out, st);
     return any_unpack<double>(w, n, rows, inverse, scale, 0, n, nullptr, 0, out, st);
+}
+
+int pyfft_laplace_1d(int dtype, const void* u, int64_t n, const double* sigma, int32_t nsigma, void* out,
+                     void* workspace, int64_t workspace_bytes, void* stream) {
+    if (!u || !sigma || !out) return fail(PYFFT_EINVAL, "laplace_1d: NULL pointer");
+    if (nsigma > 65535) return fail(PYFFT_EINVAL, "laplace_1d: at most 65535 rows per call");
+    if (dtype != PYFFT_F32 && dtype != PYFFT_F64) return fail(PYFFT_EINVAL, "unknown dtype %d", dtype);
+    AnyWs w;
+    int rc = any_carve(n, nsigma, workspace, workspace_bytes, &w);
+    if (rc) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if ((rc = any_prepare(n, w, st))) return rc;
+    int64_t gx = (w.M + 255) / 256;
+    if (gx > 64) gx = 64;
+    const dim3 grid((unsigned)gx, (unsigned)nsigma);
+    if (dtype == PYFFT_F32) any_pack_laplace_kernel<float><<<grid, 256, 0, st>>>(static_cast<const float*>(u), n, w.M, sigma, w.chirp, w.work);
+    else any_pack_laplace_kernel<double><<<grid, 256, 0, st>>>(static_cast<const double*>(u), n, w.M, sigma, w.chirp, w.work);
+    PYFFT_LAUNCH_OK("any_pack_laplace_kernel");
+    if ((rc = any_convolve(nsigma, w, st))) return rc;
+    const int64_t nb = n / 2 + 1;                                   // numpy.fft.rfft
+    if (dtype == PYFFT_F32) return any_unpack<float>(w, n, nsigma, 0, 1.0, 0, nb, nullptr, 0, out, st);
+    return any_unpack<double>(w, n, nsigma, 0, 1.0, 0, nb, nullptr, 0, out, st);
 }
 
 int pyfft_stft_any(int dtype, int32_t complex_in, const void* x, int64_t ch_stride, int32_t nch,
