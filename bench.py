@@ -38,6 +38,9 @@ def parse():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--samples", type=int, default=N_PER_GPU, help="samples per channel per GPU")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: --samples per channel PER GPU; strong: --samples per channel in TOTAL")
+    ap.add_argument("--no-graph", action="store_true", help="launch the step's kernels one by one (no CUDA graph)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     return ap.parse_args()
@@ -227,7 +230,10 @@ def run_ours(args):
     clocks = Clocks(local)                                     # sampled over the whole run (100 ms period)
     if rank == 0:
         clocks.start()
-    n, ntot = args.samples, world * args.samples
+    if args.scaling == "strong":
+        n, ntot = args.samples // world, args.samples          # per-rank share (segments are split, + halo)
+    else:
+        n, ntot = args.samples, world * args.samples
     navr = ntot // HOP - 1                                     # -> nwins = 4096 (fft_analysis.py:2411-2418)
     assert fftanal._getNwins(ntot, navr, 0.5) == NFFT
     K, nana, refl = navr, ntot, NFFT - 1                       # whole record => reflect map (:196-205)
@@ -297,7 +303,12 @@ def run_ours(args):
             dist.all_reduce(ms, op=dist.ReduceOp.MAX, group=group)
         return float(ms.item()) / steps
 
-    ms_step = timed(step, args.steps, max(args.warmup, 3))
+    # the step's launches are always the same: captured once into a CUDA graph and replayed (the five small
+    # kernels around K1 then cost their device time, not a Python + ctypes round trip each)
+    step()
+    torch.cuda.synchronize()
+    step_run = step if args.no_graph else engine.GraphedStep(step)
+    ms_step = timed(step_run, args.steps, max(args.warmup, 3))
     # dominant kernel alone (welch_pair_kernel + its partial-sum reductions, ~3 us)
     wp.prepare_tc(x, y, rmap, c_lo, c_hi) if use_tc else wp.estimate_mean(x, y, rmap, c_lo, c_hi)
     ms_k1 = timed(lambda: (wp.accumulate_tc if use_tc else wp.accumulate_mean)(x, y, rmap, k0, k1 - k0),
@@ -305,7 +316,7 @@ def run_ours(args):
     wp.estimate_mean(x, y, rmap, c_lo, c_hi)
     ms_k1_cuda = timed(lambda: wp.accumulate_mean(x, y, rmap, k0, k1 - k0), args.steps, 3)
     ms_two = timed(step_two_pass, args.steps, 3)
-    r1, r2 = step(), step_two_pass()
+    r1, r2 = step_run(), step_two_pass()
     dev_fused = float((r1["Pxy"] - r2["Pxy"]).abs().max() / r2["Pxy"].abs().max())
     assert dev_fused < 1e-5 and not wp.tc_failed(), dev_fused
     dev_coh = float((r1["Cxy"] - r2["Cxy"]).abs().max())
@@ -313,10 +324,10 @@ def run_ours(args):
     t_end = time.perf_counter() + 0.8
     while time.perf_counter() < t_end:
         for _ in range(50):
-            step()
+            step_run()
         torch.cuda.synchronize()
     clk = clocks.stop() if rank == 0 else None
-    res = step()
+    res = step_run()
     pk = int(torch.argmax(res["Pxx"].real))
     assert pk == 400 and bool(torch.isfinite(res["Cxy"].real).all()), "bench sanity check failed"
 
@@ -350,17 +361,28 @@ def run_ours(args):
                 return out[1]
             h2d = 2 * n * 4
         else:
-            def e2e_step():
-                x.copy_(xh, non_blocking=True)
-                y[0].copy_(yh, non_blocking=True)
-                r = step()
-                return r["Pxy"].cpu(), r["Pxx"].cpu(), r["Pyy"].cpu(), r["Cxy"].cpu(), r["phi_xy"].cpu()
+            class Uniform(object):                             # tvec of the global record without 8 bytes per sample
+                def __init__(self, m):
+                    self.m = m
+
+                def __len__(self):
+                    return self.m
+
+                def __getitem__(self, i):
+                    return (i if i >= 0 else self.m + i) / FS
+            tv = Uniform(ntot)
+
+            def e2e_step():                                    # public API, this rank's slice of the record
+                out = fft_pwelch(tv, xh, yh, Navr=navr, windowoverlap=0.5, windowfunction="Hanning",
+                                 plotit=False, detrend_style=1, precision="fp32", group=group,
+                                 shard_offset=g_lo)
+                return out[1]
             h2d = 2 * (g_hi - g_lo) * 4
         es = max(3, min(args.steps, 10))
         ms_e2e = timed(e2e_step, es, 2)
         e2e = {"value": NCH * ntot / (ms_e2e / 1e3) / 1e6, "unit": UNIT, "h2d_bytes_per_step": h2d,
                "d2h_bytes_per_step": 6 * (NFFT // 2) * 16 + 4 * NFFT * 8, "ms_per_step": ms_e2e,
-               "steps": es, "api": "pyfft_b200.fft_pwelch" if world == 1 else "engine.WelchPlan (sharded)"}
+               "steps": es, "api": "pyfft_b200.fft_pwelch" if world == 1 else "pyfft_b200.fft_pwelch(group=, shard_offset=)"}
 
     if rank != 0:
         if group is not None:
@@ -380,7 +402,7 @@ def run_ours(args):
     kname = "welch_tc_kernel (tcgen05)" if use_tc else "welch_pair_kernel<float,12,fused mean>"
     out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
            "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
-           "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
            "config": workload_config(world, n),
            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                         "frac": achieved / peak, "traffic": traffic_of(kname, n),
@@ -392,7 +414,8 @@ def run_ours(args):
                         "vs_two_pass_cuda_core_max_rel": dev_fused, "vs_two_pass_cuda_core_coherence_abs": dev_coh},
            "cpu_baseline": cpu, "e2e": e2e, "clocks": clk,
            # kernels of this library per step; sharded: + rereference + the NVLink peer reduction (csrc/peer.cu)
-           "gpu_launches": (6 if world == 1 else (8 if wp._peer else 7)) * args.steps}
+           "gpu_launches": (6 if world == 1 else (8 if wp._peer else 7)) * args.steps,
+           "launch_mode": "per-kernel launches" if args.no_graph else "one CUDA graph replay per step"}
     if world > 1:
         out["config"]["collective"] = ("one kernel over NVLink peer memory (pyfft_peer_allreduce), 131 KB"
                                        if wp._peer else "one NCCL all-reduce, 131 KB")

@@ -449,8 +449,10 @@ int pyfft_csm_accumulate(int dtype, const void* x, int64_t ch_stride, int32_t nc
  * and peer-mapped by the caller; peer_base is a DEVICE array of `world` 64-bit
  * addresses: where rank r's buffer is mapped in THIS process.  One call per step on
  * every rank with the same epoch = 1, 2, 3, ...: state[0..n) becomes the sum over
- * ranks, formed in rank order (bit-identical on all ranks).  ticket: one zeroed
- * uint32 in device memory; status_flag: device int, set to 1 if a peer did not show
+ * ranks, formed in rank order (bit-identical on all ranks).  epoch = 0: the epoch is
+ * kept on the device in ticket[1] and advanced by the kernel itself, so that the launch
+ * can be replayed from a CUDA graph (all ranks must then use this mode from the first
+ * call on).  ticket: two zeroed uint32 in device memory; status_flag: device int, set to 1 if a peer did not show
  * up within the (bounded) wait -- the result is then undefined and the caller must
  * fall back to another collective.
  * ------------------------------------------------------------------------- */

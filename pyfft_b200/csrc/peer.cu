@@ -45,6 +45,15 @@ __global__ void __launch_bounds__(PEER_THREADS)
 peer_allreduce_kernel(double* __restrict__ state, int64_t n, const int64_t* __restrict__ peer_base, int rank, int world,
                       uint32_t epoch, unsigned int* __restrict__ ticket, int* __restrict__ status) {
     __shared__ int s_last, s_ok;
+    __shared__ uint32_t s_epoch;
+    // epoch == 0: the epoch lives on the device in ticket[1] (the launch can then be replayed from a CUDA
+    // graph): every CTA reads it before it takes its ticket, the last CTA to take one increments it
+    const bool device_epoch = epoch == 0;
+    if (device_epoch) {
+        if (threadIdx.x == 0) s_epoch = *reinterpret_cast<volatile unsigned int*>(ticket + 1) + 1u;
+        __syncthreads();
+        epoch = s_epoch;
+    }
     const int64_t per = (n + gridDim.x - 1) / gridDim.x;
     const int64_t i0 = (int64_t)blockIdx.x * per;
     const int64_t i1 = i0 + per < n ? i0 + per : n;
@@ -57,7 +66,10 @@ peer_allreduce_kernel(double* __restrict__ state, int64_t n, const int64_t* __re
         s_ok = 1;
         const unsigned int t = atomicAdd(ticket, 1u);
         s_last = (t == gridDim.x - 1) ? 1 : 0;
-        if (s_last) *ticket = 0u;                       // every CTA has taken its ticket
+        if (s_last) {
+            *ticket = 0u;                               // every CTA has taken its ticket
+            if (device_epoch) ticket[1] = epoch;
+        }
     }
     __syncthreads();
     if (s_last && threadIdx.x < world) {
@@ -113,7 +125,7 @@ int pyfft_peer_allreduce(double* state, int64_t n, const int64_t* peer_base, int
         return fail(PYFFT_EINVAL, "peer_allreduce: NULL pointer or n <= 0");
     if (world < 1 || world > PEER_THREADS || rank < 0 || rank >= world)
         return fail(PYFFT_EINVAL, "peer_allreduce: bad rank/world %d/%d", rank, world);
-    if (epoch == 0) return fail(PYFFT_EINVAL, "peer_allreduce: epochs start at 1 (flags are zero-initialised)");
+    /* epoch == 0: device-side epoch counter in ticket[1] (ticket = uint32[2], zero-initialised) */
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     int ctas = (int)((n + PEER_THREADS - 1) / PEER_THREADS);
     if (ctas > PEER_CTAS) ctas = PEER_CTAS;

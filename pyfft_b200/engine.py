@@ -146,7 +146,7 @@ class PeerReducer:
         self.buf.zero_()
         self.hdl = symm.rendezvous(self.buf, group.group_name)
         self.peer_base = torch.tensor([int(p) for p in self.hdl.buffer_ptrs], dtype=torch.int64, device=device)
-        self.ticket = torch.zeros(1, dtype=torch.int32, device=device)
+        self.ticket = torch.zeros(2, dtype=torch.int32, device=device)     # [1]: device-side epoch counter
         self.status = torch.zeros(1, dtype=torch.int32, device=device)
         self.epoch = 0
         torch.cuda.synchronize(device)
@@ -179,9 +179,11 @@ class PeerReducer:
         return cls._cache[key]
 
     def all_reduce(self, state):
+        # the epoch is kept on the device (ticket[1]) and advanced by the kernel: the launch is the same
+        # every step and can be replayed from a CUDA graph
         self.epoch += 1
         check(lib.pyfft_peer_allreduce(_ptr(state), self.n, _ptr(self.peer_base), self.rank, self.world,
-                                       self.epoch & 0xFFFFFFFF or 1, _ptr(self.ticket), _ptr(self.status), _stream()))
+                                       0, _ptr(self.ticket), _ptr(self.status), _stream()))
 
     def check_status(self):
         """Synchronising check of the bounded waits (tests / debugging)."""
@@ -433,6 +435,30 @@ class WelchPlan(object):
         check(lib.pyfft_welch_correlation(_ptr(spec), self.nfft, ncol, 1 if onesided else 0,
                                           1 if halve_interior else 0, _ptr(out), _stream()))
         return out
+
+
+class GraphedStep(object):
+    """A fixed sequence of launches (a bench / serving step over resident buffers) captured ONCE into a CUDA
+    graph and replayed: the small kernels around K1 then cost their device time only, not a Python + ctypes
+    round trip each.  fn must allocate nothing new per call except its outputs (kept alive by the graph's
+    pool) and must have run before (twiddle / constant tables are uploaded on first use)."""
+
+    def __init__(self, fn, warmup=3):
+        dev = torch.cuda.current_device()
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(warmup):
+                fn()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.out = fn()
+
+    def __call__(self):
+        self.graph.replay()
+        return self.out
 
 
 def record_map(nsig, i0, reflect, src_base, src_len):

@@ -396,6 +396,9 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
     return_device = kwargs.pop("return_device", False)
     two_pass = kwargs.pop("two_pass_detrend", False)     # force the K0 + K1 route (testing)
     tensor_cores = kwargs.pop("tensor_cores", None)      # None: automatic; True / False: force
+    # sharded calls (group=): sigx / sigy may hold only this rank's slice of the record -- the samples
+    # [shard_offset, shard_offset + len) of the global record that tvec describes (dist.local_plan(...)["src"])
+    shard_offset = kwargs.pop("shard_offset", None)
     if useMLAB:
         raise NotImplementedError("useMLAB=True (matplotlib.mlab backend) is out of scope")
     if plotit:
@@ -416,6 +419,11 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
     else:
         sy = np.shape(sigy)
         ny = sy[1] if (len(sy) == 2 and sy[1] == ntv) else sy[0]
+    nloc = nx
+    if shard_offset is not None:
+        if group is None:
+            raise ValueError("shard_offset needs group=")
+        nx = ny = ntv                                              # the plan is the global record's
     plan = _Plan(tvec, nx, ny, tbounds, Navr, windowoverlap, windowfunction, kwargs)
     nwins, nfft, K = plan.nwins, plan.nfft, plan.Navr
     if verbose:
@@ -456,7 +464,15 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
             # pinned records cross PCIe in pieces while the segments behind each piece are accumulated
             staged, src_base = None, 0
             host_in = not (isinstance(sigx, torch.Tensor) and sigx.is_cuda)
-            if group is not None and world > 1 and host_in:
+            if shard_offset is not None:
+                g_lo, g_hi = lp["src"]
+                if shard_offset > g_lo or shard_offset + nloc < g_hi:
+                    raise ValueError("this rank analyses source samples [%d, %d) but holds [%d, %d)"
+                                     % (g_lo, g_hi, shard_offset, shard_offset + nloc))
+                x = _eng.to_device(sigx, precision, dev)
+                y = _eng.channels_first(_eng.to_device(sigy, precision, dev), nloc)
+                src_base = int(shard_offset)
+            elif group is not None and world > 1 and host_in:
                 g_lo, g_hi = lp["src"]
                 g_hi = max(g_hi, g_lo + 1)
                 x = _eng.to_device(sigx[g_lo:g_hi], precision, dev)
