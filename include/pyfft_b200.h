@@ -204,14 +204,14 @@ int pyfft_welch_accumulate_static(int dtype, const void* x, const void* y, int64
  *   pyfft_welch_tc_prepare: est (pairs, as above; the mean is rounded to float so
  *     that the kernel's subtraction is the one the correction assumes) and
  *     prescale = double[16 (nch+1)]: [0, nch] powers of two bringing the rms of each
- *     channel to [1/8, 1/4), from 64 runs of 1024 samples spread evenly over the analysed
+ *     channel to [1/8, 1/4), from 256 runs of 256 samples spread evenly over the analysed
  *     indices [j_begin, j_end); [nch+1, 2 nch+1] the repetition measure of each channel,
  *     min over l = 1..8 of sum (x[j + l hop] - x[j])^2 / (2 sum (x - mean)^2) over the same
  *     runs (1 when the span is shorter than 16 hops): a record that repeats exactly after a
  *     few hops rounds to fp16 identically segment after segment and the errors do not
  *     average out -- the host takes the tensor-core path only above 1e-4;
- *     [2 (nch+1), 3 nch+2] the stationarity of each channel, (sum_b v_b)^2 / (64 sum_b v_b^2)
- *     over the variances v_b of the 64 runs (1 = stationary; the effective number of segments
+ *     [2 (nch+1), 3 nch+2] the stationarity of each channel, (sum_b v_b)^2 / (256 sum_b v_b^2)
+ *     over the variances v_b of the 256 runs (1 = stationary; the effective number of segments
  *     is that fraction of Navr) -- the host wants >= 1/2; the rest is scratch.
  *   status_flag (device int32, zeroed by the caller): bit 0 is set if a tensor-core
  *     completion barrier timed out, bit 1 if a partial sum is not finite (an fp16

@@ -651,7 +651,7 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
 // rms of (x - mean) to ~1/8, from PREP_BLOCKS runs of PREP_RUN samples spread evenly over the span
 // (a record whose level changes along the way is scaled by its overall rms, not by its head)
 // ------------------------------------------------------------------------- //
-constexpr int PREP_BLOCKS = 64, PREP_RUN = 1024;
+constexpr int PREP_BLOCKS = 256, PREP_RUN = 256;     // one sample (and its 8 lagged partners) per thread: all loads independent
 __host__ __device__ __forceinline__ int64_t prep_stride(int64_t span) {
     const int64_t st = span > PREP_RUN ? (span - PREP_RUN) / (PREP_BLOCKS - 1) : 0;
     return st < PREP_RUN ? PREP_RUN : st;
@@ -667,7 +667,7 @@ __host__ __device__ __forceinline__ int64_t prep_stride(int64_t span) {
 // fraction of 1e-6 already dithers the roundings; the host refuses the path below 1e-4).
 // Stationarity: the 1/sqrt(K) averaging also needs the power to be spread over the segments.
 // prescale[2 nch1 + c] = (sum_b v_b)^2 / (B sum_b v_b^2) with v_b the variance of run b: 1 for a stationary
-// record, 1/64 when one run of the 64 carries all the power (the effective number of segments is that
+// record, 1/256 when one run of the 256 carries all the power (the effective number of segments is that
 // fraction of K); the host refuses the path below 1/2.
 constexpr int PREP_LAGS = 8;
 __global__ void __launch_bounds__(256) tc_prepare_kernel(const float* __restrict__ x, const float* __restrict__ y,

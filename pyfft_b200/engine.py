@@ -291,7 +291,7 @@ class WelchPlan(object):
 
     # -- tensor-core route -------------------------------------------------- #
     def prepare_tc(self, x, y, rmap, j_begin, j_end):
-        """Provisional means and power-of-two scales from 64 runs of 1024 samples spread evenly over
+        """Provisional means and power-of-two scales from 256 runs of 256 samples spread evenly over
         the analysed indices [j_begin, j_end) of this shard."""
         j1 = j_end
         if self._tc_est is None:                       # zeroed by the entry point itself

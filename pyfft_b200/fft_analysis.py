@@ -222,7 +222,7 @@ TC_MIN_RATIO = 4e-3          # the bias term alone: floor / P <= 1e-4 with margi
 # ... and no channel may repeat exactly after 1..8 hops (pyfft_welch_tc_prepare's repetition measure: the
 # noise fraction of the record at those lags; 1e-6 already dithers the fp16 roundings)
 TC_MIN_REPETITION = 1e-4
-TC_MIN_STATIONARITY = 0.5    # ... and the power must be spread over the record (64 sampled runs)
+TC_MIN_STATIONARITY = 0.5    # ... and the power must be spread over the record (256 sampled runs)
 # fp32 fused-mean route (either kernel): the kernel sees the record with a DC offset d = mean - provisional
 # mean; its leak d^2 |W[f]|^2 is accumulated in fp32 with the signal and subtracted afterwards, which costs
 # ~2^-23 x leak in absolute error.  Tolerated: leak <= 500 x the bin's own power (coherence, 1e-4) and
@@ -593,9 +593,11 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
         py = np.abs(hosted[1][lo:lo + nl]).reshape(nl, -1)
         tiny = 1e-300
         lx, ly = d[0] ** 2 * w2[:, None], (d[1:] ** 2)[None, :] * w2[:, None]          # leak power per low bin
-        per_bin = max(np.max(lx / np.maximum(px, tiny)), np.max(ly / np.maximum(py, tiny)))
         pkx = max(float(np.max(np.abs(hosted[0]))), tiny)
         pky = np.maximum(np.max(np.abs(hosted[1]).reshape(hosted[0].shape[0], -1), axis=0), tiny)
+        # bins that are (legitimately) empty -- DC after the mean removal of a periodic record -- count with a
+        # floor of 1e-4 of the channel's peak: their coherence is undefined, their PSD error is relative to the peak
+        per_bin = max(np.max(lx / np.maximum(px, 1e-4 * pkx)), np.max(ly / np.maximum(py, 1e-4 * pky[None, :])))
         per_peak = max(np.max(lx) / pkx, np.max(ly / pky[None, :]))
         return float(per_bin), float(per_peak)
 

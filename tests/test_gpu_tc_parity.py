@@ -159,7 +159,7 @@ def test_level_step_of_1e6_after_the_head(factor, cuda_device):
 def test_burst_between_the_sampled_runs_overflows_fp16_and_is_rerun(cuda_device):
     n = N_SHORT
     t, x, y = _sine_noise(n, 12)
-    # a glitch common to both channels, not in any of the 64 sampled runs (stride ~ 532 k samples)
+    # a glitch common to both channels, not in any of the 256 sampled runs of 256 samples (stride ~ 131.6 k samples)
     x[100000:100512] *= np.float32(3.0e6)
     y[100000:100512] *= np.float32(3.0e6)
     out = _ours(t, x, y, _navr(n))

@@ -40,6 +40,8 @@ def main():
     only = set(sys.argv[1:])
 
     def timed(fn, reps=5, warm=3):
+        if os.environ.get("PYFFT_BENCH_ONCE") == "1":          # under ncu: one launch of everything is enough
+            reps, warm = 1, 1
         for _ in range(warm):
             fn()
         torch.cuda.synchronize()
