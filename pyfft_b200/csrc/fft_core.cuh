@@ -23,6 +23,18 @@ template <typename T> struct __align__(2 * sizeof(T)) cpx { T x, y; };
 template <typename T> __device__ __forceinline__ cpx<T> mk(T a, T b) { cpx<T> r; r.x = a; r.y = b; return r; }
 template <typename T> __device__ __forceinline__ cpx<T> operator+(cpx<T> a, cpx<T> b) { return mk<T>(a.x + b.x, a.y + b.y); }
 template <typename T> __device__ __forceinline__ cpx<T> operator-(cpx<T> a, cpx<T> b) { return mk<T>(a.x - b.x, a.y - b.y); }
+#ifndef PYFFT_NO_F32X2
+// fp32: one packed FADD2 per complex add / subtract (sm_100 f32x2 pipe: the same FP32 throughput from half the
+// issue slots -- the register FFT is issue-bound and 42 % of its instructions are FADD, profiles/r01a)
+__device__ __forceinline__ cpx<float> operator+(cpx<float> a, cpx<float> b) {
+    const float2 r = __fadd2_rn(make_float2(a.x, a.y), make_float2(b.x, b.y));
+    return mk<float>(r.x, r.y);
+}
+__device__ __forceinline__ cpx<float> operator-(cpx<float> a, cpx<float> b) {
+    const float2 r = __fadd2_rn(make_float2(a.x, a.y), make_float2(-b.x, -b.y));
+    return mk<float>(r.x, r.y);
+}
+#endif
 template <typename T> __device__ __forceinline__ cpx<T> cmul(cpx<T> a, cpx<T> b) {
     return mk<T>(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
 }
