@@ -55,6 +55,9 @@ template <typename T> struct BigPass {
     const double* bscale;                     // OUT_XCORR: per-batch factor (or null)
     int64_t nsig;                             // OUT_XCORR: record length n (output has 2n-1 lags)
     int nreal;                                // IN_REAL2 / OUT_*2: number of real records (two per transform)
+    const double* gscale;                     // IN_REAL2 / OUT_*2: power-of-two scale per real record (or null): two
+                                              // records of very different amplitude share one transform, and the
+                                              // smaller one would lose log10(ratio) digits to the rounding of the larger
     double d_dx;                              // OUT_DERIV: grid step (the record spans N * d_dx)
     int d_modified;                           // OUT_DERIV: modified wavenumber i sin(k dx)/dx instead of i k
 };
@@ -151,11 +154,13 @@ bigfft_pass_kernel(const BigPass<T> p) {
             const T* sb = hb ? sa + p.in_bs : sa;
             const T ma = p.mean ? (T)p.mean[2 * bat] : T(0);
             const T mb = (p.mean && hb) ? (T)p.mean[2 * bat + 1] : T(0);
+            const T ga = p.gscale ? (T)p.gscale[2 * bat] : T(1);
+            const T gb = (p.gscale && hb) ? (T)p.gscale[2 * bat + 1] : T(1);
 #pragma unroll
             for (int s = 0; s < 16; ++s) {
                 const int64_t i = base_addr + (int64_t)(t + TPS * s) * p.B;
                 const bool ok = i < p.n_valid;
-                v[s] = mk<T>(ok ? sa[i] - ma : T(0), (ok && hb) ? sb[i] - mb : T(0));
+                v[s] = mk<T>(ok ? (sa[i] - ma) * ga : T(0), (ok && hb) ? (sb[i] - mb) * gb : T(0));
             }
         } else {
             const cpx<T>* src = static_cast<const cpx<T>*>(p.in) + bat * p.in_bs;
@@ -234,11 +239,13 @@ bigfft_pass_kernel(const BigPass<T> p) {
         // real results of two records that shared the transform: Re -> record 2 bat, Im -> 2 bat + 1
         const bool hb = 2 * bat + 1 < p.nreal;
         T* da = static_cast<T*>(p.out) + 2 * bat * p.out_bs;
+        const T sa_ = p.gscale ? (T)(p.scale / p.gscale[2 * bat]) : sc;
+        const T sb_ = (p.gscale && hb) ? (T)(p.scale / p.gscale[2 * bat + 1]) : sc;
 #pragma unroll
         for (int s = 0; s < 16; ++s) {
             const int64_t i = base_addr + (int64_t)(t + TPS * s) * p.B;
-            da[i] = v[s].x * sc;
-            if (hb) da[p.out_bs + i] = v[s].y * sc;
+            da[i] = v[s].x * sa_;
+            if (hb) da[p.out_bs + i] = v[s].y * sb_;
         }
     } else if (p.out_mode == OUT_MULCONJ) {
         cpx<T>* dst = static_cast<cpx<T>*>(p.out) + bat * p.out_bs;
@@ -259,17 +266,19 @@ bigfft_pass_kernel(const BigPass<T> p) {
             if (env) env[i] = sqrt(re * re + im * im);
         }
     } else if (p.out_mode == OUT_HILBERT2) {
-        // v = A(a + i b): H(a) = Im v - b, H(b) = a - Re v; records 2 bat and 2 bat + 1
+        // v = A(ga a + i gb b): ga H(a) = Im v - gb b, gb H(b) = ga a - Re v; records 2 bat and 2 bat + 1
         const bool hb = 2 * bat + 1 < p.nreal;
         const T* ua = static_cast<const T*>(p.in2) + 2 * bat * p.in2_bs;
         const T* ub = hb ? ua + p.in2_bs : ua;
         cpx<T>* za = p.out ? static_cast<cpx<T>*>(p.out) + 2 * bat * p.out_bs : nullptr;
         T* env = p.out2 ? static_cast<T*>(p.out2) + 2 * bat * p.out2_bs : nullptr;
+        const T ga2 = p.gscale ? (T)p.gscale[2 * bat] : T(1), gb2 = (p.gscale && hb) ? (T)p.gscale[2 * bat + 1] : T(1);
+        const T iga = T(1) / ga2, igb = T(1) / gb2;               // powers of two: exact
 #pragma unroll
         for (int s = 0; s < 16; ++s) {
             const int64_t i = base_addr + (int64_t)(t + TPS * s) * p.B;
             const T a = ua[i], b = hb ? ub[i] : T(0);
-            const T ha = v[s].y * sc - b, hbv = a - v[s].x * sc;
+            const T ha = (v[s].y * sc - gb2 * b) * iga, hbv = (ga2 * a - v[s].x * sc) * igb;
             if (za) za[i] = mk<T>(a, ha);
             if (env) env[i] = sqrt(a * a + ha * ha);
             if (hb) {
@@ -281,8 +290,8 @@ bigfft_pass_kernel(const BigPass<T> p) {
         // v = c(x, a) - i c(x, b): records 2 bat and 2 bat + 1 of the second operand
         const bool hb = 2 * bat + 1 < p.nreal;
         T* da = static_cast<T*>(p.out) + 2 * bat * p.out_bs;
-        const T fa = (T)(p.scale * (p.bscale ? p.bscale[2 * bat] : 1.0));
-        const T fb = hb ? -(T)(p.scale * (p.bscale ? p.bscale[2 * bat + 1] : 1.0)) : T(0);
+        const T fa = (T)(p.scale * (p.bscale ? p.bscale[2 * bat] : 1.0) / (p.gscale ? p.gscale[2 * bat] : 1.0));
+        const T fb = hb ? -(T)(p.scale * (p.bscale ? p.bscale[2 * bat + 1] : 1.0) / (p.gscale ? p.gscale[2 * bat + 1] : 1.0)) : T(0);
         const int64_t n = p.nsig, tail = p.N - (n - 1);
 #pragma unroll
         for (int s = 0; s < 16; ++s) {
@@ -340,6 +349,36 @@ __global__ void __launch_bounds__(256) moments_kernel(const T* __restrict__ x, i
 }
 
 // mean[b] = sums[2b] / n
+// power-of-two scale per real record from a strided sample of <= 65 536 values: rms * g in [1/2, 1)
+// (any g is exact mathematically -- it only balances the two records that share a transform)
+template <typename T>
+__global__ void __launch_bounds__(256) record_scale_kernel(const T* __restrict__ x, int64_t stride, int64_t n,
+                                                           const double* __restrict__ mean, double* __restrict__ g) {
+    const int rec = blockIdx.x;
+    const T* p = x + (int64_t)rec * stride;
+    const double m = mean ? mean[rec] : 0.0;
+    const int64_t step = n > 65536 ? n / 65536 : 1;
+    double s = 0.0, c = 0.0;
+    for (int64_t i = (int64_t)threadIdx.x * step; i < n; i += 256 * step) {
+        const double v = (double)p[i] - m;
+        s += v * v;
+        c += 1.0;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { s += __shfl_xor_sync(0xffffffffu, s, o); c += __shfl_xor_sync(0xffffffffu, c, o); }
+    __shared__ double sh[2][8];
+    if ((threadIdx.x & 31) == 0) { sh[0][threadIdx.x >> 5] = s; sh[1][threadIdx.x >> 5] = c; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        s = c = 0.0;
+        for (int w = 0; w < 8; ++w) { s += sh[0][w]; c += sh[1][w]; }
+        const double rms = c > 0.0 ? sqrt(s / c) : 0.0;
+        int e = 0;
+        if (rms > 0.0 && isfinite(rms)) frexp(rms, &e);
+        g[rec] = ldexp(1.0, -e);
+    }
+}
+
 __global__ void mean_from_sums_kernel(const double* sums, int nb, int64_t n, double* mean) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < nb) mean[i] = sums[2 * i] / (double)n;
@@ -431,7 +470,7 @@ template <typename T> static BigPass<T> blank_pass(int64_t N) {
     p.tw_mode = TW_NONE; p.tw_lo = p.tw_hi = nullptr; p.lo_bits = 0; p.tw = nullptr;
     p.in_mode = IN_CPLX; p.n_valid = N; p.mean = nullptr;
     p.out_mode = OUT_CPLX; p.scale = 1.0; p.bscale = nullptr; p.nsig = 0; p.nreal = 0;
-    p.d_dx = 1.0; p.d_modified = 0;
+    p.d_dx = 1.0; p.d_modified = 0; p.gscale = nullptr;
     return p;
 }
 
@@ -455,7 +494,7 @@ static int run_dif(int m, bool inv, const BigPass<T>& first, const BigPass<T>& l
         p.in = buf; p.in_bs = N; p.out = buf; p.out_bs = N;
         if (i == 0) {
             p.in = first.in; p.in_bs = first.in_bs; p.in_mode = first.in_mode;
-            p.n_valid = first.n_valid; p.mean = first.mean; p.nreal = first.nreal;
+            p.n_valid = first.n_valid; p.mean = first.mean; p.nreal = first.nreal; p.gscale = first.gscale;
         }
         if (i == pl.npass - 1) {
             p.out_mode = last.out_mode; p.scale = last.scale;
@@ -490,7 +529,7 @@ static int run_dit_inverse(int m, const BigPass<T>& last, void* buf, int batch, 
             p.out_mode = last.out_mode; p.out = last.out; p.out_bs = last.out_bs;
             p.out2 = last.out2; p.out2_bs = last.out2_bs; p.scale = last.scale;
             p.bscale = last.bscale; p.nsig = last.nsig;
-            p.in2 = last.in2; p.in2_bs = last.in2_bs; p.nreal = last.nreal;
+            p.in2 = last.in2; p.in2_bs = last.in2_bs; p.nreal = last.nreal; p.gscale = last.gscale;
         }
         int rc = launch_pass<T>(pl.bits[i], true, p, batch, st);
         if (rc) return rc;
@@ -509,6 +548,17 @@ static int check_pow2(int64_t n, int lo, int hi, int* m) {
     return PYFFT_OK;
 }
 
+// scales of `nrec` real records into the workspace slack at byte offset `used` (null when there is no room)
+template <typename T>
+static double* pair_scales(const void* x, int64_t stride, int64_t n, int nrec, const double* mean, void* ws, int64_t used,
+                           int64_t wsb, cudaStream_t st) {
+    const int64_t off = (used + 15) & ~(int64_t)15;
+    if (!ws || wsb < off + 8 * (int64_t)nrec) return nullptr;
+    double* g = reinterpret_cast<double*>(static_cast<char*>(ws) + off);
+    record_scale_kernel<T><<<nrec, 256, 0, st>>>(static_cast<const T*>(x), stride, n, mean, g);
+    return g;
+}
+
 template <typename T>
 static int hilbert_impl(const void* in, int64_t n, int batch, void* analytic, void* envelope, void* ws,
                         int64_t wsb, cudaStream_t st) {
@@ -520,11 +570,14 @@ static int hilbert_impl(const void* in, int64_t n, int batch, void* analytic, vo
         // two records per transform (see the top of the file); the work buffer is the workspace
         BigPass<T> first = blank_pass<T>(n), last = blank_pass<T>(n);
         first.in = in; first.in_bs = n; first.in_mode = IN_REAL2; first.n_valid = n; first.nreal = batch;
+        // per-record scales live in the slack pyfft_bigfft_workspace_bytes adds behind the work buffer
+        double* gs = pair_scales<T>(in, n, n, batch, nullptr, ws, (int64_t)npair * n * (int64_t)sizeof(cpx<T>), wsb, st);
+        first.gscale = gs;
         last.out_mode = OUT_MASK;
         if ((rc = run_dif<T>(m, false, first, last, ws, npair, st))) return rc;
         BigPass<T> fin = blank_pass<T>(n);
         fin.out_mode = OUT_HILBERT2; fin.out = analytic; fin.out_bs = n; fin.out2 = envelope; fin.out2_bs = n;
-        fin.in2 = in; fin.in2_bs = n; fin.nreal = batch;
+        fin.in2 = in; fin.in2_bs = n; fin.nreal = batch; fin.gscale = gs;
         fin.scale = 1.0 / (double)n;
         return run_dit_inverse<T>(m, fin, ws, npair, st);
     }
@@ -558,10 +611,12 @@ static int deriv_impl(const void* in, int64_t n, int batch, int modified, double
                     (long long)((int64_t)npair * n * sizeof(cpx<T>)));
     BigPass<T> first = blank_pass<T>(n), last = blank_pass<T>(n);
     first.in = in; first.in_bs = n; first.in_mode = IN_REAL2; first.n_valid = n; first.nreal = batch;
+    double* gs = pair_scales<T>(in, n, n, batch, nullptr, ws, (int64_t)npair * n * (int64_t)sizeof(cpx<T>), wsb, st);
+    first.gscale = gs;
     last.out_mode = OUT_DERIV; last.d_dx = dx; last.d_modified = modified;
     if ((rc = run_dif<T>(m, false, first, last, ws, npair, st))) return rc;
     BigPass<T> fin = blank_pass<T>(n);
-    fin.out_mode = OUT_REAL2; fin.out = out; fin.out_bs = n; fin.nreal = batch;
+    fin.out_mode = OUT_REAL2; fin.out = out; fin.out_bs = n; fin.nreal = batch; fin.gscale = gs;
     fin.scale = 1.0 / (double)n;
     return run_dit_inverse<T>(m, fin, ws, npair, st);
 }
@@ -614,11 +669,14 @@ static int xcorr_impl(const void* x, int64_t xs, const void* y, int64_t ys, int6
         const int npair = (pairs + 1) / 2;
         first.in = y; first.in_bs = ys; first.in_mode = IN_REAL2; first.nreal = pairs;
         first.mean = normalise ? mean_y : nullptr;
+        double* gs = norm + pairs;                                           // inside the 64 (nx + pairs) bytes of slack
+        record_scale_kernel<T><<<pairs, 256, 0, st>>>(yp, ys, n, normalise ? mean_y : nullptr, gs);
+        first.gscale = gs;
         last.out_mode = OUT_MULCONJ; last.in2 = bufx; last.in2_bs = 0;
         if ((rc = run_dif<T>(m, false, first, last, bufy, npair, st))) return rc;
         BigPass<T> fin2 = blank_pass<T>(N);
         fin2.out_mode = OUT_XCORR2; fin2.out = out; fin2.out_bs = 2 * n - 1; fin2.scale = 1.0 / (double)N;
-        fin2.bscale = normalise == 1 ? norm : nullptr; fin2.nsig = n; fin2.nreal = pairs;
+        fin2.bscale = normalise == 1 ? norm : nullptr; fin2.nsig = n; fin2.nreal = pairs; fin2.gscale = gs;
         return run_dit_inverse<T>(m, fin2, bufy, npair, st);
     }
     first.in = y; first.in_bs = ys; first.mean = normalise ? mean_y : nullptr;

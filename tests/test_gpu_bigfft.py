@@ -241,3 +241,29 @@ def test_spectral_derivative_kernel_against_numpy(log2n, batch, cuda_device):
         ref = np.real(np.fft.ifft(wn * np.fft.fft(u, axis=1), axis=1))
         got = engine.spectral_derivative(torch.from_numpy(u).to(cuda_device), dx, "fp64", modified=modified)
         assert relerr(got.cpu().numpy(), ref) <= 1e-11, (modified, relerr(got.cpu().numpy(), ref))
+
+
+def test_paired_records_of_very_different_amplitude_keep_their_digits(cuda_device):
+    """two real records share one complex transform (Hilbert, ccf with a shared first record); each is
+    scaled by its own power of two first, so a 10^6 amplitude mismatch between neighbours costs no digits
+    (it used to cost log10 of the ratio in fp32)."""
+    from oracle import restatement as R
+    from pyfft_b200 import ccf, hilbert
+    n = 1 << 16
+    rng = np.random.default_rng(77)
+    t = np.arange(n) / 1.0e5
+    base = [(1 + 0.5 * np.sin(2 * np.pi * 40.0 * t + c)) * np.sin(2 * np.pi * (3e3 + 500 * c) * t) + 0.05 * rng.standard_normal(n)
+            for c in range(4)]
+    amp = np.array([1.0, 1.0e-6, 1.0e5, 3.0e-3])
+    u = (np.stack(base) * amp[:, None]).astype(np.float32)
+    z = hilbert(u, precision="fp32")
+    env = hilbert(u, precision="fp32", envelope=True)
+    for c in range(4):
+        ref = R.hilbert(u[c].astype(np.float64))
+        assert relerr(z[c], ref) <= 1e-5, (c, relerr(z[c], ref))            # the fp32 contract, per record
+        assert relerr(env[c], np.abs(ref)) <= 1e-5, c
+    x0 = base[0].astype(np.float32)
+    _, cm = ccf(x0, u, 1.0e5, precision="fp32")
+    for c in range(4):
+        _, c1 = ccf(x0.astype(np.float64), u[c].astype(np.float64), 1.0e5, precision="fp64")
+        assert np.max(np.abs(cm[c] - c1)) <= 1e-5, (c, np.max(np.abs(cm[c] - c1)))
