@@ -210,3 +210,27 @@ def test_pinned_host_records_are_uploaded_in_pieces(tensor_cores, navr, cuda_dev
     # a (1, n) second record goes the same way
     c = fft_pwelch(t, xs, ys.view(1, n), **kw)
     assert relerr(c[1], a[1]) <= 1e-12
+
+
+@pytest.mark.parametrize("tensor_cores", [True, False])
+def test_pinned_host_records_with_tbounds_in_the_second_half(tensor_cores, cuda_device):
+    """staged upload + an analysis window that starts far behind the first piece: the provisional statistics
+    must wait for the piece that holds the samples they read (they used to read memory not yet uploaded)."""
+    import torch
+    from oracle import restatement as R
+    from oracle import signals
+    from pyfft_b200 import fft_pwelch
+    n = 2 ** 23
+    t, x, y = signals.c2_cross(n=n, dc=(7.0, 2.5))
+    x32, y32 = x.astype(np.float32), y.astype(np.float32)
+    tb = [t[n // 2 + 12345], t[n // 2 + 12345 + 2 ** 21 - 1]]      # 2^21 samples from the second half on
+    kw = dict(Navr=1023, windowoverlap=0.5, windowfunction="Hanning", detrend_style=1)
+    with np.errstate(all="ignore"):
+        ref = R.fft_pwelch(t, x32.astype(np.float64), y32.astype(np.float64), tb, **kw)
+    for rep in range(3):                                      # the race was nondeterministic
+        xs, ys = torch.from_numpy(x32).pin_memory(), torch.from_numpy(y32).pin_memory()
+        out = fft_pwelch(t, xs, ys, tb, plotit=False, precision="fp32", tensor_cores=tensor_cores, **kw)
+        assert out[6].nwins == int(ref["nwins"]) == 4096 and out[6].Navr == 1023
+        tol = 1.5 * 6e-4 / np.sqrt(1023) if tensor_cores else 1e-5
+        for i, nm in ((1, "Pxy"), (2, "Pxx"), (3, "Pyy")):
+            assert np.isfinite(out[i]).all() and relerr(out[i], ref[nm]) <= tol, (rep, nm, relerr(out[i], ref[nm]))
