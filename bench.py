@@ -41,6 +41,11 @@ def parse():
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="weak: --samples per channel PER GPU; strong: --samples per channel in TOTAL")
     ap.add_argument("--no-graph", action="store_true", help="launch the step's kernels one by one (no CUDA graph)")
+    ap.add_argument("--sync-exchange", action="store_true",
+                    help="N > 1: every step waits for its own exchange (default: collected by the next step)")
+    ap.add_argument("--unfused", action="store_true",
+                    help="the step as separate calls (prepare, accumulate, tail sums, [rereference, reduce,] finalize) "
+                         "instead of the three launches of pyfft_welch_tc_step")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     return ap.parse_args()
@@ -254,10 +259,21 @@ def run_ours(args):
 
     use_tc = wp.can_use_tc and os.environ.get("PYFFT_NO_TC") != "1"
 
+    tails = ((s_lo, c_lo), (c_hi, s_hi))
+    fused_step = use_tc and not args.unfused
+    defer = world > 1 and not args.sync_exchange
+
     def step():
         # ONE pass over HBM: provisional mean (+ scale) from 64 Ki samples, fused Welch
         # accumulation (tensor-core DFT when available), exact mean correction by linearity
         # after the (all-reduced) raw sums are known
+        if fused_step:
+            # three launches: statistics + head + tail sums | main kernel | partial sums + NVLink exchange + finalize
+            # sharded: the exchange of a step is collected by the next one (a stream of records; no rank waits for
+            # a slower one inside a step); the timed region ends with the flush that completes its last step
+            out = wp.step_tc(x, y, rmap, k0, k1 - k0, tails, K, nana, scale, True, group, deferred=defer)
+            if out is not None or wp._deferred_args is not None:
+                return out
         wp.reset()
         if use_tc:
             wp.prepare_tc(x, y, rmap, c_lo, c_hi)
@@ -288,7 +304,7 @@ def run_ours(args):
             dist.barrier(group=group)
         torch.cuda.synchronize()
 
-    def timed(fn, steps, warmup):
+    def timed(fn, steps, warmup, last=None):
         for _ in range(warmup):
             fn()
         barrier()
@@ -296,6 +312,8 @@ def run_ours(args):
         e0.record()
         for _ in range(steps):
             fn()
+        if last is not None:
+            last()
         e1.record()
         barrier()
         ms = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
@@ -307,8 +325,23 @@ def run_ours(args):
     # kernels around K1 then cost their device time, not a Python + ctypes round trip each)
     step()
     torch.cuda.synchronize()
+    step_is_fused = fused_step and wp._aux is not None
     step_run = step if args.no_graph else engine.GraphedStep(step)
-    ms_step = timed(step_run, args.steps, max(args.warmup, 3))
+    deferred_on = step_is_fused and defer and wp._deferred_args is not None
+    flush = (lambda: wp.flush_tc(force=True)) if deferred_on else None
+    ms_step = timed(step_run, args.steps, max(args.warmup, 3), flush)
+
+    def run_complete():
+        """One more step and, when the exchange is deferred, the flush that completes it -> its spectra."""
+        r = step_run()
+        return wp.flush_tc(force=True) if deferred_on else r
+
+    ms_sync = None
+    if deferred_on:
+        # the same step with its own exchange waited for inside the step (what one isolated call costs)
+        def step_sync():
+            return wp.step_tc(x, y, rmap, k0, k1 - k0, tails, K, nana, scale, True, group, deferred=False)
+        ms_sync = timed(step_sync if args.no_graph else engine.GraphedStep(step_sync), args.steps, 3)
     # dominant kernel alone (welch_pair_kernel + its partial-sum reductions, ~3 us)
     wp.prepare_tc(x, y, rmap, c_lo, c_hi) if use_tc else wp.estimate_mean(x, y, rmap, c_lo, c_hi)
     ms_k1 = timed(lambda: (wp.accumulate_tc if use_tc else wp.accumulate_mean)(x, y, rmap, k0, k1 - k0),
@@ -316,7 +349,7 @@ def run_ours(args):
     wp.estimate_mean(x, y, rmap, c_lo, c_hi)
     ms_k1_cuda = timed(lambda: wp.accumulate_mean(x, y, rmap, k0, k1 - k0), args.steps, 3)
     ms_two = timed(step_two_pass, args.steps, 3)
-    r1, r2 = step_run(), step_two_pass()
+    r1, r2 = run_complete(), step_two_pass()
     dev_fused = float((r1["Pxy"] - r2["Pxy"]).abs().max() / r2["Pxy"].abs().max())
     assert dev_fused < 1e-5 and not wp.tc_failed(), dev_fused
     dev_coh = float((r1["Cxy"] - r2["Cxy"]).abs().max())
@@ -327,7 +360,7 @@ def run_ours(args):
             step_run()
         torch.cuda.synchronize()
     clk = clocks.stop() if rank == 0 else None
-    res = step_run()
+    res = run_complete()
     pk = int(torch.argmax(res["Pxx"].real))
     assert pk == 400 and bool(torch.isfinite(res["Cxy"].real).all()), "bench sanity check failed"
 
@@ -414,11 +447,18 @@ def run_ours(args):
                         "vs_two_pass_cuda_core_max_rel": dev_fused, "vs_two_pass_cuda_core_coherence_abs": dev_coh},
            "cpu_baseline": cpu, "e2e": e2e, "clocks": clk,
            # kernels of this library per step; sharded: + rereference + the NVLink peer reduction (csrc/peer.cu)
-           "gpu_launches": (6 if world == 1 else (8 if wp._peer else 7)) * args.steps,
+           "gpu_launches": (3 if step_is_fused else (6 if world == 1 else (8 if wp._peer else 7))) * args.steps,
+           "step_kernels": ("tc_pre_kernel, welch_tc_kernel, tc_post_kernel" if step_is_fused else "unfused sequence"),
+           "exchange": (None if world == 1 else
+                        ("deferred: collected by the next step's tc_post_kernel, the timed region ends with the flush "
+                         "of its last step" if deferred_on else "waited for inside every step")),
+           "sync_exchange_ms_per_step": ms_sync,
            "launch_mode": "per-kernel launches" if args.no_graph else "one CUDA graph replay per step"}
     if world > 1:
-        out["config"]["collective"] = ("one kernel over NVLink peer memory (pyfft_peer_allreduce), 131 KB"
-                                       if wp._peer else "one NCCL all-reduce, 131 KB")
+        out["config"]["collective"] = (
+            "inside tc_post_kernel: per-item pushes over NVLink peer memory, 131 KB per rank" if step_is_fused else
+            ("one kernel over NVLink peer memory (pyfft_peer_allreduce), 131 KB" if wp._peer
+             else "one NCCL all-reduce, 131 KB"))
     print(json.dumps(out), flush=True)
     if group is not None:
         dist.destroy_process_group()

@@ -231,6 +231,48 @@ int pyfft_welch_accumulate_tc(const void* x, const void* y, int64_t y_stride, in
                               double* acc, double* lin, double* stats, void* workspace,
                               int64_t workspace_bytes, int32_t* status_flag, void* stream);
 
+/* The whole fused tensor-core step of a resident record in THREE launches (+ one 168 (nch+1)-byte fill):
+ *   tc_pre_kernel   = pyfft_welch_tc_prepare over the segments' own span + the reflect-padded head + the raw
+ *                     sums of the analysed samples outside that span (tail_a = [a0, a1), tail_b = [b0, b1):
+ *                     what pyfft_detrend_stats_xy adds for the exact global mean, fft_analysis.py:356-357),
+ *   welch_tc_kernel = the main kernel of pyfft_welch_accumulate_tc,
+ *   tc_post_kernel  = sum of the per-CTA partials -> [sharded: rereference + exchange over NVLink peer memory]
+ *                     -> state and the finalised spectra of pyfft_welch_finalize_mean, 32 bins per CTA.
+ * Same results as prepare + accumulate_tc + detrend_stats_xy (+ rereference + peer_allreduce) + finalize_mean;
+ * the step is launch-bound around the main kernel, so the boundaries between the small kernels are what it saves.
+ *   aux   = double[21 (nch+1)], written: est (2 per channel) | prescale (16 per channel, as pyfft_welch_tc_prepare)
+ *           | tail sums (2 per channel) | raw sums of the segments' span (1 per channel).
+ *   state = acc [nch][4][2049] | lin [nch][4][256] | stats [2 (nch+1)], WRITTEN (not added to): the sums of this call,
+ *           summed over the ranks when sharded (then about the reference 0: mean correction with est = 0).
+ *   wlow  = the window's transform, bins 0..7 at least, (re, im) pairs (double).
+ *   K_total / nana: segments and analysed samples of the WHOLE record (all ranks); seg = this rank's segments (>= 1).
+ *   world > 1: peer_base = device array of `world` addresses of the ranks' peer buffers (each
+ *           pyfft_welch_tc_step_peer_bytes(nch, world) bytes, zero-filled once, peer-mapped by the host:
+ *           torch.distributed._symmetric_memory); every rank must make the same sequence of calls.
+ *   status_flag bits: 1 pipeline barrier time-out, 2 non-finite partial sum, 4 a peer did not arrive (the outputs
+ *           are then NaN).
+ * No reference counterpart for the exchange (the reference is single-process): it is the sum over shards of the
+ * per-segment sums of fft_analysis.py:444-446. */
+int64_t pyfft_welch_tc_step_peer_bytes(int32_t nch, int32_t world);
+
+int pyfft_welch_tc_step(const void* x, const void* y, int64_t y_stride, int32_t nch,
+                        const pyfft_record_map* map, const pyfft_segmentation* seg, const void* window,
+                        const double* wlow, int64_t tail_a0, int64_t tail_a1, int64_t tail_b0, int64_t tail_b1,
+                        int64_t K_total, int64_t nana, double scale, int32_t onesided, double* aux, double* state,
+                        double* Pxx, double* Pyy, double* Pxy, double* Cxy, double* Cxy2, double* phi,
+                        void* workspace, int64_t workspace_bytes, int32_t* status_flag,
+                        const int64_t* peer_base, int32_t rank, int32_t world, int32_t deferred, void* stream);
+
+/* deferred != 0 (world > 1 only; a stream of steps over successive records): the exchange of a step is collected by
+ * the NEXT deferred step (or by pyfft_welch_tc_step_flush), a whole main kernel after it was pushed, so that no rank
+ * ever waits for a slower one inside a step.  The outputs and `state` written by a deferred call are those of the
+ * PREVIOUS deferred call (nothing is written by the first one); _flush writes those of the last one.  Do not mix
+ * deferred and plain calls on one peer buffer without a flush in between. */
+int pyfft_welch_tc_step_flush(int32_t nch, const double* wlow, int64_t K_total, int64_t nana, double scale,
+                              int32_t onesided, double* state, double* Pxx, double* Pyy, double* Pxy,
+                              double* Cxy, double* Cxy2, double* phi, int32_t* status_flag,
+                              const int64_t* peer_base, int32_t rank, int32_t world, void* stream);
+
 /* ------------------------------------------------------------------------- *
  * Welch finalize
  * replaces: one-/two-sided selection and doubling (fft_analysis.py:402-428),

@@ -58,6 +58,12 @@ _PROTOS = {
     "pyfft_welch_tc_prepare": (C.c_int, [_vp, _vp, _i64, _i32, _pmap, _i64, _i64, _i64, _vp, _vp, _vp]),
     "pyfft_welch_accumulate_tc": (C.c_int, [_vp, _vp, _i64, _i32, _pmap, _pseg, _vp, _vp, _vp, _vp, _vp, _vp,
                                             _vp, _i64, _vp, _vp]),
+    "pyfft_welch_tc_step_peer_bytes": (_i64, [_i32, _i32]),
+    "pyfft_welch_tc_step": (C.c_int, [_vp, _vp, _i64, _i32, _pmap, _pseg, _vp, _vp, _i64, _i64, _i64, _i64, _i64, _i64,
+                                      _dbl, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _vp, _i32,
+                                      _i32, _i32, _vp]),
+    "pyfft_welch_tc_step_flush": (C.c_int, [_i32, _vp, _i64, _i64, _dbl, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
+                                            _vp, _i32, _i32, _vp]),
     "pyfft_welch_finalize": (C.c_int, [_vp, _i32, _i32, _i64, _dbl, _i32, _vp, _vp, _vp, _vp, _vp,
                                        _vp, _vp]),
     "pyfft_welch_finalize_mean": (C.c_int, [_vp, _vp, _i32, _i32, _i64, _vp, _vp, _i64, _vp, _dbl, _i32,

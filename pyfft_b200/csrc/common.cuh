@@ -64,6 +64,21 @@ void free_twiddles();
 
 int device_sm_count();
 
+// ---- system-scope accesses of the NVLink peer exchanges (peer.cu, welch_tc.cu) ---- //
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ double ld_relaxed_sys(const double* p) {
+    double v;
+    asm volatile("ld.relaxed.sys.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
+    return v;
+}
+
 // shared between welch.cu and welch_tc.cu
 int welch_reduce_launch_f32(const float* partial, int nparts, int per_pair, int nch, double* acc, cudaStream_t st);
 int welch_raw_sums_launch(const double* dev_sums, const double* est, int n, double count, double* stats,

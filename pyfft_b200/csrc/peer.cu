@@ -27,20 +27,6 @@ namespace pyfft {
 constexpr int PEER_CTAS = 96;      // all CTAs spin on the peers' flags: keep the grid co-resident (148 SMs)
 constexpr int PEER_THREADS = 256;
 
-__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
-    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
-    uint32_t v;
-    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ double ld_relaxed_sys(const double* p) {
-    double v;
-    asm volatile("ld.relaxed.sys.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
-    return v;
-}
-
 __global__ void __launch_bounds__(PEER_THREADS)
 peer_allreduce_kernel(double* __restrict__ state, int64_t n, const int64_t* __restrict__ peer_base, int rank, int world,
                       uint32_t epoch, unsigned int* __restrict__ ticket, int* __restrict__ status) {

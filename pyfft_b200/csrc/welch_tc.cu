@@ -116,6 +116,13 @@ struct TcParams {
     long long* trace;         // debug: per-CTA start / end stamps and the time line of CTA (0, 0), or NULL
 };
 
+// programmatic dependent launch (pyfft_welch_tc_step): a kernel launched with the programmatic-serialization
+// attribute may start while its predecessor in the stream still runs; pdl_wait() returns once the predecessor
+// grid has completed and its writes are visible (at once when the kernel was launched the ordinary way),
+// pdl_launch_dependents() lets the successor be scheduled as soon as resources free up
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 __device__ __forceinline__ uint32_t pack_h2(float a, float b) {
     __half2 h = __floats2half2_rn(a, b);
     return *reinterpret_cast<uint32_t*>(&h);
@@ -183,6 +190,7 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
         p.trace[2048 + 4 * (blockIdx.y * gridDim.x + blockIdx.x) + 2] = clock64();
     }
 
+    pdl_launch_dependents();
     // ---- one-time setup: stage-1 matrix, barriers, tensor memory --------------------------- //
     {
         const uint4* src = reinterpret_cast<const uint4*>(p.consts);
@@ -234,6 +242,7 @@ __global__ void __launch_bounds__(tcw::NTHREADS, 1) welch_tc_kernel(const TcPara
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
+    pdl_wait();            // est, prescale, head and the zeroed raw sums come from the kernels before this one
 
     const int64_t c0 = (int64_t)blockIdx.x * p.chunk;
     const int64_t c1 = (c0 + p.chunk < p.seg_count) ? c0 + p.chunk : p.seg_count;
@@ -670,18 +679,18 @@ __host__ __device__ __forceinline__ int64_t prep_stride(int64_t span) {
 // record, 1/256 when one run of the 256 carries all the power (the effective number of segments is that
 // fraction of K); the host refuses the path below 1/2.
 constexpr int PREP_LAGS = 8;
-__global__ void __launch_bounds__(256) tc_prepare_kernel(const float* __restrict__ x, const float* __restrict__ y,
-                                                         int64_t y_stride, RecMap map, int64_t j_begin, int64_t j_end,
-                                                         int64_t hop, int nch1, double* __restrict__ est,
-                                                         double* __restrict__ prescale) {
-    const int c = blockIdx.y;                       // 0 = x, 1.. = y channels
+// block bx of nblk (= PREP_BLOCKS) of channel c
+__device__ __forceinline__ void tc_prepare_block(const float* __restrict__ x, const float* __restrict__ y,
+                                                 int64_t y_stride, const RecMap& map, int64_t j_begin, int64_t j_end,
+                                                 int64_t hop, int nch1, double* __restrict__ est,
+                                                 double* __restrict__ prescale, int bx, int nblk, int c) {
     const float* p = c == 0 ? x : y + (int64_t)(c - 1) * y_stride;
     const double x0 = (double)p[src_index(map, j_begin)];
     double s[2 + PREP_LAGS];
 #pragma unroll
     for (int i = 0; i < 2 + PREP_LAGS; ++i) s[i] = 0.0;
     const int64_t stride = prep_stride(j_end - j_begin);
-    const int64_t r0 = j_begin + (int64_t)blockIdx.x * stride;
+    const int64_t r0 = j_begin + (int64_t)bx * stride;
     const bool lags_ok = hop > 0 && (j_end - j_begin) >= 2 * PREP_LAGS * hop + PREP_RUN;   // room to look 8 hops forward or back
     for (int64_t j = r0 + threadIdx.x; j < r0 + PREP_RUN && j < j_end; j += 256) {
         const float v0 = p[src_index(map, j)];
@@ -730,30 +739,38 @@ __global__ void __launch_bounds__(256) tc_prepare_kernel(const float* __restrict
         else atomicAdd(&lagsum[i - 2], t);
     }
     __threadfence();
-    if (atomicAdd(&prescale[c], 1.0) != (double)(gridDim.x - 1)) return;     // not the last block of the channel
+    if (atomicAdd(&prescale[c], 1.0) != (double)(nblk - 1)) return;     // not the last block of the channel
     __threadfence();
-    int64_t cnt = 0;                                                          // samples the runs covered
-    for (int b = 0; b < PREP_BLOCKS; ++b) {
-        const int64_t lo = j_begin + (int64_t)b * stride, hi = lo + PREP_RUN < j_end ? lo + PREP_RUN : j_end;
-        if (hi > lo) cnt += hi - lo;
-    }
+    // samples the runs covered / runs with at least two samples, in closed form (this thread is the critical
+    // path of the step: the main kernel waits for it); block b covers [b stride, b stride + PREP_RUN) of the span
+    const int64_t span = j_end - j_begin;
+    int64_t nfull = span >= PREP_RUN ? (span - PREP_RUN) / stride + 1 : 0;
+    if (nfull > PREP_BLOCKS) nfull = PREP_BLOCKS;
+    int64_t cnt = nfull * PREP_RUN;
+    if (nfull < PREP_BLOCKS && nfull * stride < span) cnt += span - nfull * stride;
+    int64_t runs = span > 1 ? (span - 1 + stride - 1) / stride : 0;
+    if (runs > PREP_BLOCKS) runs = PREP_BLOCKS;
     const double n = (double)cnt;
-    const double md = atomicAdd(&est[2 * c], 0.0) / n;                         // read through L2
-    double var = atomicAdd(&est[2 * c + 1], 0.0) / n - md * md;
+    // the sums, read through L2 with independent loads
+    double sums[4 + PREP_LAGS];
+    sums[0] = __ldcg(&est[2 * c]);
+    sums[1] = __ldcg(&est[2 * c + 1]);
+    sums[2] = __ldcg(&runvar[0]);
+    sums[3] = __ldcg(&runvar[1]);
+#pragma unroll
+    for (int l = 0; l < PREP_LAGS; ++l) sums[4 + l] = __ldcg(&lagsum[l]);
+    const double md = sums[0] / n;
+    double var = sums[1] / n - md * md;
     if (!(var > 0.0)) var = 0.0;
     double rep = 1.0;
     if (lags_ok && var > 0.0)
+#pragma unroll
         for (int l = 0; l < PREP_LAGS; ++l) {
-            const double r = atomicAdd(&lagsum[l], 0.0) / (2.0 * var * n);
+            const double r = sums[4 + l] / (2.0 * var * n);
             rep = r < rep ? r : rep;
         }
     prescale[nch1 + c] = rep;
-    {
-        int runs = 0;
-        for (int b = 0; b < PREP_BLOCKS; ++b) runs += (j_begin + (int64_t)b * stride + 1 < j_end) ? 1 : 0;
-        const double a = atomicAdd(&runvar[0], 0.0), q = atomicAdd(&runvar[1], 0.0);
-        prescale[2 * nch1 + c] = (q > 0.0 && runs > 0) ? a * a / ((double)runs * q) : 1.0;
-    }
+    prescale[2 * nch1 + c] = (sums[3] > 0.0 && runs > 0) ? sums[2] * sums[2] / ((double)runs * sums[3]) : 1.0;
     const double rms = sqrt(var);
     int e = 0;
     if (rms > 0.0 && isfinite(rms)) frexp(rms, &e);   // rms = f * 2^e, f in [0.5, 1)
@@ -763,6 +780,14 @@ __global__ void __launch_bounds__(256) tc_prepare_kernel(const float* __restrict
     est[2 * c] = (double)(float)(x0 + md);            // exactly representable in fp32
     est[2 * c + 1] = 0.0;
     prescale[c] = ldexp(1.0, sh2);
+}
+
+__global__ void __launch_bounds__(256) tc_prepare_kernel(const float* __restrict__ x, const float* __restrict__ y,
+                                                         int64_t y_stride, RecMap map, int64_t j_begin, int64_t j_end,
+                                                         int64_t hop, int nch1, double* __restrict__ est,
+                                                         double* __restrict__ prescale) {
+    tc_prepare_block(x, y, y_stride, map, j_begin, j_end, hop, nch1, est, prescale, (int)blockIdx.x, (int)gridDim.x,
+                     (int)blockIdx.y);             // channel 0 = x, 1.. = y channels
 }
 
 // after the main kernel, in one launch: acc += sum of the per-CTA partial spectra, lin += sum of the
@@ -824,6 +849,334 @@ __global__ void __launch_bounds__(256) tc_head_kernel(const float* __restrict__ 
     const int sh = align_shift(direct_ptr(p, map, 0));
     const int64_t j = (int64_t)blockIdx.x * 256 + threadIdx.x;
     if (j < n) head[(int64_t)c * tcw::HEADP + sh + j] = p[src_index(map, j)];
+}
+
+// ------------------------------------------------------------------------- //
+// The whole fused step in three launches (pyfft_welch_tc_step): tc_pre_kernel -> welch_tc_kernel ->
+// tc_post_kernel.  A step over resident records is launch-bound around the main kernel: every boundary
+// between two small kernels costs ~2 us of a 0.26 ms step, and the sharded step had three of them around
+// its exchange.
+// ------------------------------------------------------------------------- //
+constexpr int TAIL_BLOCKS = 4;
+
+// grid.x = PREP_BLOCKS (provisional statistics) + head_blocks (reflect-padded head of the record) + TAIL_BLOCKS
+// (raw sums of the analysed samples outside the segments' own span: tail[2c] += sum x, tail[2c+1] += sum j x)
+__global__ void __launch_bounds__(256) tc_pre_kernel(const float* __restrict__ x, const float* __restrict__ y,
+                                                     int64_t y_stride, RecMap map, int64_t j_begin, int64_t j_end,
+                                                     int64_t hop, int nch1, double* __restrict__ est,
+                                                     double* __restrict__ prescale, int64_t head_len,
+                                                     float* __restrict__ head, int head_blocks, int64_t ta0,
+                                                     int64_t ta1, int64_t tb0, int64_t tb1, double* __restrict__ tail) {
+    pdl_launch_dependents();
+    const int c = blockIdx.y;
+    int bx = blockIdx.x;
+    if (bx < PREP_BLOCKS) {
+        tc_prepare_block(x, y, y_stride, map, j_begin, j_end, hop, nch1, est, prescale, bx, PREP_BLOCKS, c);
+        return;
+    }
+    bx -= PREP_BLOCKS;
+    const float* p = c == 0 ? x : y + (int64_t)(c - 1) * y_stride;
+    if (bx < head_blocks) {
+        const int sh = align_shift(direct_ptr(p, map, 0));
+        const int64_t j = (int64_t)bx * 256 + threadIdx.x;
+        if (j < head_len) head[(int64_t)c * tcw::HEADP + sh + j] = p[src_index(map, j)];
+        return;
+    }
+    bx -= head_blocks;
+    if (ta1 <= ta0 && tb1 <= tb0) return;
+    double s0 = 0.0, s1 = 0.0;
+    for (int64_t j = ta0 + (int64_t)bx * 256 + threadIdx.x; j < ta1; j += TAIL_BLOCKS * 256) {
+        const double v = (double)p[src_index(map, j)];
+        s0 += v;
+        s1 += v * (double)j;
+    }
+    for (int64_t j = tb0 + (int64_t)bx * 256 + threadIdx.x; j < tb1; j += TAIL_BLOCKS * 256) {
+        const double v = (double)p[src_index(map, j)];
+        s0 += v;
+        s1 += v * (double)j;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        s0 += __shfl_xor_sync(0xffffffffu, s0, o);
+        s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+    }
+    __shared__ double sh2[2][8];
+    if ((threadIdx.x & 31) == 0) { sh2[0][threadIdx.x >> 5] = s0; sh2[1][threadIdx.x >> 5] = s1; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double a = 0.0, b = 0.0;
+        for (int i = 0; i < 8; ++i) { a += sh2[0][i]; b += sh2[1][i]; }
+        atomicAdd(&tail[2 * c], a);
+        atomicAdd(&tail[2 * c + 1], b);
+    }
+}
+
+// One work item = 32 bins of one channel pair:
+//   A. the sums over the main kernel's per-CTA partials (4 rows x 32 bins; the item of bins 0..31 also the linear
+//      sums of bins < NLIN and the raw sample sums),
+//   B. sharded (world > 1): the shard's sums are moved to the common reference 0 (welch_rereference_kernel),
+//      WRITTEN into slot [rank] of every peer's staging buffer over NVLink, published with one release store per
+//      peer, and -- once the item's flags of all ranks have arrived -- summed from the local staging buffer in rank
+//      order (bit-identical on every GPU).  Flags are per item: no CTA waits for another CTA of its own grid.
+//   C. state (acc | lin | stats) is written and the 32 bins are finalised (welch_finalize_kernel with the mean
+//      correction).
+// Peer buffer of one rank (doubles): stage[2][world][items][POST_SLOT] | uint32 flags[world][items] | uint32
+// epochs[items]; zero-filled once.  A rank can be at most one epoch ahead of a peer (it needs the peer's flag of
+// epoch e to finish e, which the peer sets after it has read epoch e-1), hence two staging copies.
+constexpr int POST_SLOT = 168;                    // 128 acc + 32 lin + 2 raw sums, padded
+constexpr int POST_NBB = (tcw::NBIN + 31) / 32;   // items per pair
+constexpr int POST_THREADS = 512, POST_WARPS = POST_THREADS / 32;
+struct TcPostParams {
+    const float* partial;
+    const float* lin_partial;
+    int nparts;
+    const double* dev_sums;
+    const double* tail;
+    const double* est;
+    double count, K_local, K_total, nana, scale_over_k;
+    int nch, onesided, F;
+    const double* W;
+    double* acc;
+    double* lin;
+    double* stats;
+    double* Pxx;
+    double* Pyy;
+    double* Pxy;
+    double* Cxy;
+    double* Cxy2;
+    double* phi;
+    int* status;
+    const int64_t* peer_base;
+    int rank, world;
+    int mode;                 // 0 = this step, exchange waited for; 1 = deferred exchange; 2 = flush
+};
+
+// mode 0: reduce -> [exchange: push, wait, sum] -> finalize, all for THIS step (what pyfft_welch_tc_step returns
+//         is complete when the kernel ends; every step waits for the slowest rank);
+// mode 1: deferred exchange of a stream of steps: an item first collects and finalises the sums that it pushed in
+//         the PREVIOUS deferred step (they arrived a whole main kernel ago: no rank waits for another unless it is
+//         a full step ahead), then reduces and pushes this step's; outputs and state are the previous step's;
+// mode 2: flush -- collect and finalise what is pending, push nothing.
+// per item on the device: epochs[item] (last epoch pushed) and pending[item] (pushed, not yet collected).
+__global__ void __launch_bounds__(POST_THREADS) tc_post_kernel(const TcPostParams p) {
+    using namespace tcw;
+    constexpr int PER_PAIR = 4 * NBIN, LROW = L / 16;
+    const int lane = threadIdx.x & 31, g = threadIdx.x >> 5;
+    const int items = p.nch * POST_NBB;
+    __shared__ double sh[POST_WARPS][5][33];
+    __shared__ double sa[4][32], sl[4][NLIN], sraw[2];
+    __shared__ uint32_t s_epoch, s_pending;
+    __shared__ int s_ok;
+    const size_t stage_doubles = (size_t)2 * p.world * items * POST_SLOT;
+    uint32_t* const my_words = p.world > 1 ? reinterpret_cast<uint32_t*>(reinterpret_cast<double*>(p.peer_base[p.rank]) + stage_doubles)
+                                           : nullptr;      // flags[world][items] | epochs[items] | pending[items]
+    pdl_wait();
+    for (int item = blockIdx.x; item < items; item += gridDim.x) {
+        const int pair = item / POST_NBB, bb = item - pair * POST_NBB;
+        const int f = bb * 32 + lane;
+        const int nval = bb == 0 ? 162 : 128;               // 4 x 32 sums (+ 4 x 8 linear sums + 2 raw sums)
+        if (threadIdx.x == 0) {
+            s_ok = 1;
+            s_epoch = p.world > 1 ? my_words[(size_t)p.world * items + item] : 0u;
+            s_pending = p.world > 1 ? my_words[(size_t)(p.world + 1) * items + item] : 0u;
+        }
+        __syncthreads();
+        const uint32_t epoch_prev = s_epoch;
+        const bool pending = s_pending != 0u;
+        // phases of this item: collect + finalise what was pushed before / reduce this step / push it / collect it
+        const bool do_old = p.world > 1 && p.mode != 0 && pending;
+        const bool do_reduce = p.mode != 2;
+        const bool do_push = p.world > 1 && p.mode != 2;
+        const bool do_now = p.mode == 0;                    // finalise this step's sums inside this launch
+        for (int phase = do_old ? 0 : 1; phase < 2; ++phase) {
+            double ex = 0.0, ey = 0.0, Kc = p.K_total;      // sums that went through the exchange are about the reference 0
+            if (phase == 1) {
+                if (!do_reduce) break;
+                // ---- A: reduce the partials of the main kernel ---------------------------------- //
+                // every warp takes every 16th part: up to 10 parts x 4 rows = 40 independent loads per thread and round
+                double s[4] = {0.0, 0.0, 0.0, 0.0};
+                if (f < NBIN) {
+                    const float* pp = p.partial + (size_t)pair * p.nparts * PER_PAIR + f;
+                    for (int k0 = g; k0 < p.nparts; k0 += 10 * POST_WARPS) {
+                        float r[10][4];
+#pragma unroll
+                        for (int u = 0; u < 10; ++u) {
+                            const int k = k0 + POST_WARPS * u;
+#pragma unroll
+                            for (int q = 0; q < 4; ++q) r[u][q] = k < p.nparts ? pp[(size_t)k * PER_PAIR + q * NBIN] : 0.f;
+                        }
+#pragma unroll
+                        for (int u = 0; u < 10; ++u)
+#pragma unroll
+                            for (int q = 0; q < 4; ++q) s[q] += (double)r[u][q];
+                    }
+                }
+#pragma unroll
+                for (int q = 0; q < 4; ++q) sh[g][q][lane] = s[q];
+                double t = 0.0;
+                if (bb == 0) {                    // lane -> row (re/im of U, V) = lane >> 3, bin = lane & 7
+                    const float* lp = p.lin_partial + (size_t)pair * p.nparts * 4 * LROW + (lane >> 3) * LROW + (lane & 7);
+                    for (int k0 = g; k0 < p.nparts; k0 += 10 * POST_WARPS) {
+                        float r[10];
+#pragma unroll
+                        for (int u = 0; u < 10; ++u) {
+                            const int k = k0 + POST_WARPS * u;
+                            r[u] = k < p.nparts ? lp[(size_t)k * 4 * LROW] : 0.f;
+                        }
+#pragma unroll
+                        for (int u = 0; u < 10; ++u) t += (double)r[u];
+                    }
+                }
+                sh[g][4][lane] = t;
+                __syncthreads();
+                if (g < 5) {
+                    double v = 0.0;
+#pragma unroll
+                    for (int u = 0; u < POST_WARPS; ++u) v += sh[u][g][lane];
+                    if (g < 4) {
+                        sa[g][lane] = v;
+                        // an fp16 operand out of range (a record far louder than the sampled statistics said) shows as Inf / NaN
+                        if (f < NBIN && !isfinite(v)) atomicOr(p.status, 2);
+                    } else if (bb == 0) {
+                        sl[lane >> 3][lane & 7] = v;
+                    }
+                } else if (threadIdx.x == 160 && bb == 0) {
+                    sraw[0] = p.tail[0] + p.dev_sums[0] + p.count * p.est[0];
+                    sraw[1] = p.tail[2 * (1 + pair)] + p.dev_sums[1 + pair] + p.count * p.est[2 * (1 + pair)];
+                }
+                __syncthreads();
+                ex = p.est[0];
+                ey = p.est[2 * (1 + pair)];
+                Kc = p.K_local;
+                if (do_push) {
+                    // ---- B1: to the common reference 0 (welch_rereference_kernel), then into every peer --- //
+                    if (bb == 0 && threadIdx.x < NLIN) {
+                        const int b = threadIdx.x;
+                        const double dx = -ex, dy = -ey;
+                        const double wr = p.W[2 * b], wi = p.W[2 * b + 1], w2 = wr * wr + wi * wi;
+                        const double sur = sl[0][b], sui = sl[1][b], svr = sl[2][b], svi = sl[3][b];
+                        sa[0][b] += -2.0 * dx * (wr * sur + wi * sui) + Kc * dx * dx * w2;
+                        sa[1][b] += -2.0 * dy * (wr * svr + wi * svi) + Kc * dy * dy * w2;
+                        sa[2][b] += -dx * (wr * svr + wi * svi) - dy * (wr * sur + wi * sui) + Kc * dx * dy * w2;
+                        sa[3][b] += -dx * (wr * svi - wi * svr) - dy * (wi * sur - wr * sui);
+                        sl[0][b] = sur - Kc * dx * wr;
+                        sl[1][b] = sui - Kc * dx * wi;
+                        sl[2][b] = svr - Kc * dy * wr;
+                        sl[3][b] = svi - Kc * dy * wi;
+                    }
+                    __syncthreads();
+                    const uint32_t epoch = epoch_prev + 1u;
+                    const size_t slot0 = ((size_t)(epoch & 1u) * p.world * items + item) * POST_SLOT;   // + r * items * POST_SLOT
+                    if ((int)threadIdx.x < nval) {
+                        const int i = threadIdx.x;
+                        const double v = i < 128 ? sa[i >> 5][i & 31] : (i < 160 ? sl[(i - 128) >> 3][(i - 128) & 7] : sraw[i - 160]);
+                        for (int r = 0; r < p.world; ++r)
+                            (reinterpret_cast<double*>(p.peer_base[r]) + slot0 + (size_t)p.rank * items * POST_SLOT)[i] = v;
+                    }
+                    __threadfence_system();
+                    __syncthreads();
+                    if ((int)threadIdx.x < p.world) {
+                        uint32_t* theirs = reinterpret_cast<uint32_t*>(reinterpret_cast<double*>(p.peer_base[threadIdx.x]) + stage_doubles);
+                        st_release_sys(theirs + (size_t)p.rank * items + item, epoch);
+                    }
+                    if (threadIdx.x == 0) {
+                        my_words[(size_t)p.world * items + item] = epoch;
+                        my_words[(size_t)(p.world + 1) * items + item] = do_now ? 0u : 1u;
+                    }
+                    if (!do_now) break;                       // collected by the next deferred step or the flush
+                    ex = 0.0;
+                    ey = 0.0;
+                    Kc = p.K_total;
+                }
+            }
+            if (p.world > 1) {
+                // ---- B2: wait for the item's flags of all ranks, sum the local staging copy in rank order ---- //
+                const uint32_t epoch = phase == 0 ? epoch_prev : epoch_prev + 1u;
+                const size_t slot0 = ((size_t)(epoch & 1u) * p.world * items + item) * POST_SLOT;
+                if ((int)threadIdx.x < p.world) {
+                    bool ok = false;
+                    for (uint32_t it = 0; it < (1u << 24); ++it) {
+                        if ((int32_t)(ld_acquire_sys(my_words + (size_t)threadIdx.x * items + item) - epoch) >= 0) { ok = true; break; }
+                        __nanosleep(20);
+                    }
+                    if (!ok) { s_ok = 0; atomicOr(p.status, 4); }
+                }
+                __syncthreads();
+                if ((int)threadIdx.x < nval) {
+                    const int i = threadIdx.x;
+                    double s = 0.0;
+                    if (s_ok) {
+                        const double* st = reinterpret_cast<const double*>(p.peer_base[p.rank]) + slot0 + i;
+                        for (int r = 0; r < p.world; ++r) s += ld_relaxed_sys(st + (size_t)r * items * POST_SLOT);
+                    } else {
+                        s = __longlong_as_double(0x7ff8000000000000ll);       // a peer never arrived: fail loudly
+                    }
+                    if (i < 128) sa[i >> 5][i & 31] = s;
+                    else if (i < 160) sl[(i - 128) >> 3][(i - 128) & 7] = s;
+                    else sraw[i - 160] = s;
+                }
+                if (phase == 0 && threadIdx.x == 0 && !do_push) my_words[(size_t)(p.world + 1) * items + item] = 0u;
+                __syncthreads();
+            }
+            // ---- C: state and the finalised spectra ------------------------------------------------- //
+            if (threadIdx.x < 128) {
+                const int q = threadIdx.x >> 5;
+                if (f < NBIN) p.acc[((size_t)pair * 4 + q) * NBIN + f] = sa[q][lane];
+            }
+            if (bb == 0) {
+                for (int i = threadIdx.x; i < 4 * LROW; i += POST_THREADS)
+                    p.lin[(size_t)pair * 4 * LROW + i] = (i & (LROW - 1)) < NLIN ? sl[i / LROW][i & (LROW - 1)] : 0.0;
+                if (threadIdx.x == 0) {
+                    if (pair == 0) { p.stats[0] = sraw[0]; p.stats[1] = 0.0; }
+                    p.stats[2 * (1 + pair)] = sraw[1];
+                    p.stats[2 * (1 + pair) + 1] = 0.0;
+                }
+            }
+            if (threadIdx.x < 32 && f < NBIN) {
+                double a0 = sa[0][lane], a1 = sa[1][lane], a2 = sa[2][lane], a3 = sa[3][lane];
+                if (bb == 0 && lane < NLIN) {
+                    const double dx = sraw[0] / p.nana - ex, dy = sraw[1] / p.nana - ey;
+                    const double wr = p.W[2 * f], wi = p.W[2 * f + 1], w2 = wr * wr + wi * wi;
+                    const double sur = sl[0][f], sui = sl[1][f], svr = sl[2][f], svi = sl[3][f];
+                    a0 += -2.0 * dx * (wr * sur + wi * sui) + Kc * dx * dx * w2;
+                    a1 += -2.0 * dy * (wr * svr + wi * svi) + Kc * dy * dy * w2;
+                    a2 += -dx * (wr * svr + wi * svi) - dy * (wr * sur + wi * sui) + Kc * dx * dy * w2;
+                    a3 += -dx * (wr * svi - wi * svr) - dy * (wi * sur - wr * sui);
+                }
+                const int nch = p.nch;
+                // outputs of bin f: one-sided o = f (< F = L/2), x2 on bins 1..F-2 (fft_analysis.py:414-416);
+                // two-sided, fftshift order (:423-427): o = (f + L/2) mod L and, mirrored, o = L/2 - f with Pxy conjugated
+                for (int side = 0; side < 2; ++side) {
+                    int o;
+                    double wgt = 1.0;
+                    bool conj = false;
+                    if (p.onesided) {
+                        if (side == 1 || f >= p.F) break;
+                        o = f;
+                        if (o >= 1 && o <= p.F - 2) wgt = 2.0;
+                    } else if (side == 0) {
+                        o = (f + L / 2) & (L - 1);
+                    } else {
+                        if (f == 0 || f == L / 2) break;
+                        o = L / 2 - f;
+                        conj = true;
+                    }
+                    const double s = p.scale_over_k * wgt;
+                    const double pxx = a0 * s, pyy = a1 * s, pr = a2 * s, pi = (conj ? -a3 : a3) * s;
+                    const size_t idx = (size_t)o * nch + pair;
+                    if (p.Pxx && pair == 0) { p.Pxx[2 * o] = pxx; p.Pxx[2 * o + 1] = 0.0; }
+                    if (p.Pyy) { p.Pyy[2 * idx] = pyy; p.Pyy[2 * idx + 1] = 0.0; }
+                    if (p.Pxy) { p.Pxy[2 * idx] = pr; p.Pxy[2 * idx + 1] = pi; }
+                    const double den = fabs(pxx) * fabs(pyy);                 // fft_analysis.py:1672, 1677
+                    if (p.Cxy) { const double r = 1.0 / sqrt(den); p.Cxy[2 * idx] = pr * r; p.Cxy[2 * idx + 1] = pi * r; }
+                    if (p.Cxy2) { p.Cxy2[2 * idx] = (pr * pr + pi * pi) / den; p.Cxy2[2 * idx + 1] = 0.0 / den; }
+                    if (p.phi) p.phi[idx] = atan2(pi, pr);                    // fft_analysis.py:520
+                }
+            }
+            __syncthreads();
+        }
+        __syncthreads();
+    }
 }
 
 // ------------------------------------------------------------------------- //
@@ -903,6 +1256,91 @@ static int tc_grid_x(int64_t seg_count, int nch) {
     return (int)want;
 }
 
+// argument checks and kernel parameters shared by pyfft_welch_accumulate_tc and pyfft_welch_tc_step
+// (dev_sums is placed by the caller)
+static int tc_setup(const void* x, const void* y, int64_t y_stride, int32_t nch, const pyfft_record_map* map,
+                    const pyfft_segmentation* seg, const void* window, const double* est, const double* prescale,
+                    void* workspace, int64_t workspace_bytes, int32_t* status_flag, TcParams* out, int* gx_out) {
+    using namespace tcw;
+    RecMap m;
+    int rc = check_map(map, &m);
+    if (rc) return rc;
+    if (!seg || seg->nfft != L) return fail(PYFFT_EUNSUPPORTED, "the tensor-core path handles nfft = 4096 only");
+    if (seg->hop != 512 && seg->hop != 1024 && seg->hop != 2048 && seg->hop != 4096)
+        return fail(PYFFT_EUNSUPPORTED, "the tensor-core path needs a hop of 512, 1024, 2048 or 4096 samples (got %d)", seg->hop);
+    if (!x || !y || !window || !est || !prescale || !status_flag || nch <= 0)
+        return fail(PYFFT_EINVAL, "tensor-core Welch: NULL pointer or nch <= 0");
+    if (seg->seg_count <= 0) return fail(PYFFT_EINVAL, "tensor-core Welch: no segments");
+    const int64_t j_lo = seg->seg_first * (int64_t)seg->hop;
+    const int64_t j_hi = (seg->seg_first + seg->seg_count - 1) * (int64_t)seg->hop + seg->nfft;
+    if ((rc = check_range(m, j_lo, j_hi))) return rc;
+    int status;
+    const unsigned char* consts = tc_constants(&status);
+    if (!consts) return status;
+    const int gx = tc_grid_x(seg->seg_count, nch);
+    const int nparts = gx;                        // one partial per CTA
+    const int64_t main_bytes = (int64_t)nch * nparts * 4 * NBIN * 4;
+    const int64_t lin_bytes = (int64_t)nch * nparts * 4 * (L / 16) * 4;
+    const int64_t sums_bytes = (8 * (int64_t)(nch + 1) + 15) & ~(int64_t)15;
+    const int64_t head_bytes = (int64_t)(nch + 1) * HEADP * 4;
+    if (!workspace || workspace_bytes < main_bytes + lin_bytes + sums_bytes + head_bytes)
+        return fail(PYFFT_EINVAL, "tensor-core Welch: workspace too small");
+    // blocks (one hop of analysed samples) that reach into the reflect-padded zone are copied from a
+    // materialised head of the record; every other block is a plain run of the source
+    int64_t head_len = 0;
+    if (j_lo < m.reflect) {
+        head_len = (m.reflect + seg->hop - 1) / seg->hop * seg->hop;
+        if (head_len > m.nsig) head_len = m.nsig;
+        if (head_len > HEAD)
+            return fail(PYFFT_EUNSUPPORTED, "the tensor-core path supports reflect padding up to %d samples", HEAD);
+    }
+    if (((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y) | (uintptr_t)(y_stride * 4)) & 3) != 0)
+        return fail(PYFFT_EINVAL, "tensor-core Welch: x / y must be 4-byte aligned");
+    TcParams p;
+    p.x = static_cast<const float*>(x);
+    p.y = static_cast<const float*>(y);
+    p.y_stride = y_stride;
+    p.map = m;
+    p.hop = seg->hop;
+    p.seg_first = seg->seg_first;
+    p.seg_count = seg->seg_count;
+    p.chunk = (seg->seg_count + gx - 1) / gx;
+    p.window = static_cast<const float*>(window);
+    p.est = est;
+    p.prescale = prescale;
+    p.consts = consts;
+    p.head = reinterpret_cast<float*>(static_cast<char*>(workspace) + main_bytes + lin_bytes + sums_bytes);
+    p.head_len = head_len;
+    p.partial = static_cast<float*>(workspace);
+    p.nparts = nparts;
+    p.lin_partial = reinterpret_cast<float*>(static_cast<char*>(workspace) + main_bytes);
+    p.dev_sums = reinterpret_cast<double*>(static_cast<char*>(workspace) + main_bytes + lin_bytes);
+    p.status = status_flag;
+    p.trace = g_tc_trace;
+    *out = p;
+    *gx_out = gx;
+    return PYFFT_OK;
+}
+
+static int tc_post_launch(const TcPostParams& q, bool pdl, cudaStream_t st) {
+    int sms = device_sm_count();
+    if (sms <= 0) sms = 148;
+    int64_t blocks = (int64_t)q.nch * POST_NBB;
+    if (blocks > 3 * (int64_t)sms) blocks = 3 * (int64_t)sms;      // co-resident: a CTA of the sharded step may wait for its peers
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)blocks);
+    cfg.blockDim = dim3(POST_THREADS);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = st;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    PYFFT_CUDA_OK(cudaLaunchKernelEx(&cfg, tc_post_kernel, q));
+    return PYFFT_OK;
+}
+
 }  // namespace pyfft
 
 using namespace pyfft;
@@ -946,63 +1384,18 @@ int pyfft_welch_accumulate_tc(const void* x, const void* y, int64_t y_stride, in
                               const double* est, const double* prescale, double* acc, double* lin, double* stats,
                               void* workspace, int64_t workspace_bytes, int32_t* status_flag, void* stream) {
     using namespace tcw;
-    RecMap m;
-    int rc = check_map(map, &m);
-    if (rc) return rc;
-    if (!seg || seg->nfft != L) return fail(PYFFT_EUNSUPPORTED, "the tensor-core path handles nfft = 4096 only");
-    if (seg->hop != 512 && seg->hop != 1024 && seg->hop != 2048 && seg->hop != 4096)
-        return fail(PYFFT_EUNSUPPORTED, "the tensor-core path needs a hop of 512, 1024, 2048 or 4096 samples (got %d)", seg->hop);
-    if (!x || !y || !window || !est || !prescale || !acc || !lin || !stats || !status_flag || nch <= 0)
-        return fail(PYFFT_EINVAL, "welch_accumulate_tc: NULL pointer or nch <= 0");
-    if (seg->seg_count == 0) return PYFFT_OK;
-    const int64_t j_lo = seg->seg_first * (int64_t)seg->hop;
-    const int64_t j_hi = (seg->seg_first + seg->seg_count - 1) * (int64_t)seg->hop + seg->nfft;
-    if ((rc = check_range(m, j_lo, j_hi))) return rc;
-    int status;
-    const unsigned char* consts = tc_constants(&status);
-    if (!consts) return status;
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
-    const int gx = tc_grid_x(seg->seg_count, nch);
-    const int nparts = gx;                        // one partial per CTA
-    const int64_t main_bytes = (int64_t)nch * nparts * 4 * NBIN * 4;
-    const int64_t lin_bytes = (int64_t)nch * nparts * 4 * (L / 16) * 4;
-    const int64_t sums_bytes = (8 * (int64_t)(nch + 1) + 15) & ~(int64_t)15;
-    const int64_t head_bytes = (int64_t)(nch + 1) * HEADP * 4;
-    if (!workspace || workspace_bytes < main_bytes + lin_bytes + sums_bytes + head_bytes)
-        return fail(PYFFT_EINVAL, "welch_accumulate_tc: workspace too small");
-    // blocks (one hop of analysed samples) that reach into the reflect-padded zone are copied from a
-    // materialised head of the record; every other block is a plain run of the source
-    int64_t head_len = 0;
-    if (j_lo < m.reflect) {
-        head_len = (m.reflect + seg->hop - 1) / seg->hop * seg->hop;
-        if (head_len > m.nsig) head_len = m.nsig;
-        if (head_len > HEAD)
-            return fail(PYFFT_EUNSUPPORTED, "the tensor-core path supports reflect padding up to %d samples", HEAD);
-    }
-    if (((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y) | (uintptr_t)(y_stride * 4)) & 3) != 0)
-        return fail(PYFFT_EINVAL, "welch_accumulate_tc: x / y must be 4-byte aligned");
+    if (!acc || !lin || !stats) return fail(PYFFT_EINVAL, "welch_accumulate_tc: NULL pointer");
+    if (seg && seg->seg_count == 0 && seg->nfft == L) return PYFFT_OK;
     TcParams p;
-    p.x = static_cast<const float*>(x);
-    p.y = static_cast<const float*>(y);
-    p.y_stride = y_stride;
-    p.map = m;
-    p.hop = seg->hop;
-    p.seg_first = seg->seg_first;
-    p.seg_count = seg->seg_count;
-    p.chunk = (seg->seg_count + gx - 1) / gx;
-    p.window = static_cast<const float*>(window);
-    p.est = est;
-    p.prescale = prescale;
-    p.consts = consts;
-    float* head = reinterpret_cast<float*>(static_cast<char*>(workspace) + main_bytes + lin_bytes + sums_bytes);
-    p.head = head;
-    p.head_len = head_len;
-    p.partial = static_cast<float*>(workspace);
-    p.nparts = nparts;
-    p.lin_partial = reinterpret_cast<float*>(static_cast<char*>(workspace) + main_bytes);
-    p.dev_sums = reinterpret_cast<double*>(static_cast<char*>(workspace) + main_bytes + lin_bytes);
-    p.status = status_flag;
-    p.trace = g_tc_trace;
+    int gx;
+    const int rc = tc_setup(x, y, y_stride, nch, map, seg, window, est, prescale, workspace, workspace_bytes, status_flag,
+                            &p, &gx);
+    if (rc) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int nparts = p.nparts;
+    const int64_t head_len = p.head_len;
+    float* head = const_cast<float*>(p.head);
+    const RecMap m = p.map;
     // every CTA (also one that gets no segment) writes all of its partial sums and the NLIN bins of
     // the linear sums that tc_finish_kernel reads: only the raw-sum accumulators need clearing
     PYFFT_CUDA_OK(cudaMemsetAsync(p.dev_sums, 0, sizeof(double) * (size_t)(nch + 1), st));
@@ -1017,6 +1410,131 @@ int pyfft_welch_accumulate_tc(const void* x, const void* y, int64_t y_stride, in
         stats, status_flag);
     PYFFT_LAUNCH_OK("tc_finish_kernel");
     return PYFFT_OK;
+}
+
+int64_t pyfft_welch_tc_step_peer_bytes(int32_t nch, int32_t world) {
+    if (nch <= 0 || world <= 0) return fail(PYFFT_EINVAL, "welch_tc_step_peer_bytes: bad arguments");
+    const int64_t items = (int64_t)nch * POST_NBB;
+    return 2 * (int64_t)world * items * POST_SLOT * 8 + 4 * ((int64_t)world * items + 2 * items) + 64;
+}
+
+int pyfft_welch_tc_step(const void* x, const void* y, int64_t y_stride, int32_t nch, const pyfft_record_map* map,
+                        const pyfft_segmentation* seg, const void* window, const double* wlow, int64_t tail_a0,
+                        int64_t tail_a1, int64_t tail_b0, int64_t tail_b1, int64_t K_total, int64_t nana, double scale,
+                        int32_t onesided, double* aux, double* state, double* Pxx, double* Pyy, double* Pxy,
+                        double* Cxy, double* Cxy2, double* phi, void* workspace, int64_t workspace_bytes,
+                        int32_t* status_flag, const int64_t* peer_base, int32_t rank, int32_t world, int32_t deferred,
+                        void* stream) {
+    using namespace tcw;
+    if (!aux || !state || !wlow) return fail(PYFFT_EINVAL, "welch_tc_step: NULL pointer");
+    if (K_total <= 0 || nana <= 0) return fail(PYFFT_EINVAL, "welch_tc_step: K_total and nana must be positive");
+    if (world < 1 || world > 256 || rank < 0 || rank >= world || (world > 1 && !peer_base))
+        return fail(PYFFT_EINVAL, "welch_tc_step: bad rank / world / peer_base");
+    const int nch1 = nch + 1;
+    double* est = aux;
+    double* prescale = aux + 2 * nch1;
+    double* tail = aux + 18 * nch1;
+    double* dev_sums = aux + 20 * nch1;
+    TcParams p;
+    int gx;
+    int rc = tc_setup(x, y, y_stride, nch, map, seg, window, est, prescale, workspace, workspace_bytes, status_flag, &p,
+                      &gx);
+    if (rc) return rc;
+    p.dev_sums = dev_sums;
+    const int64_t c_lo = seg->seg_first * (int64_t)seg->hop, c_hi = c_lo + seg->seg_count * (int64_t)seg->hop;
+    if (tail_a1 > tail_a0 && (rc = check_range(p.map, tail_a0, tail_a1))) return rc;
+    if (tail_b1 > tail_b0 && (rc = check_range(p.map, tail_b0, tail_b1))) return rc;
+    if ((rc = check_range(p.map, c_lo, c_hi))) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    PYFFT_CUDA_OK(cudaMemsetAsync(aux, 0, sizeof(double) * 21 * (size_t)nch1, st));
+    const int head_blocks = (int)((p.head_len + 255) / 256);
+    tc_pre_kernel<<<dim3(PREP_BLOCKS + head_blocks + TAIL_BLOCKS, nch1), 256, 0, st>>>(
+        p.x, p.y, y_stride, p.map, c_lo, c_hi, seg->hop, nch1, est, prescale, p.head_len, const_cast<float*>(p.head),
+        head_blocks, tail_a0, tail_a1, tail_b0, tail_b1, tail);
+    PYFFT_LAUNCH_OK("tc_pre_kernel");
+    PYFFT_CUDA_OK(cudaFuncSetAttribute(welch_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    // the main kernel and the post kernel are launched programmatically dependent: their CTAs are scheduled as
+    // the predecessor's drain away, the main kernel's set-up (constants, barriers, tensor memory) overlaps
+    // tc_pre_kernel, and both wait (griddepcontrol.wait) before touching what the predecessor writes
+    const bool pdl = getenv("PYFFT_NO_PDL") == nullptr;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(gx, nch);
+        cfg.blockDim = dim3(NTHREADS);
+        cfg.dynamicSmemBytes = SMEM_BYTES;
+        cfg.stream = st;
+        cfg.attrs = attr;
+        cfg.numAttrs = pdl ? 1 : 0;
+        PYFFT_CUDA_OK(cudaLaunchKernelEx(&cfg, welch_tc_kernel, p));
+    }
+    TcPostParams q;
+    q.partial = p.partial;
+    q.lin_partial = p.lin_partial;
+    q.nparts = p.nparts;
+    q.dev_sums = dev_sums;
+    q.tail = tail;
+    q.est = est;
+    q.count = (double)seg->seg_count * (double)seg->hop;
+    q.K_local = (double)seg->seg_count;
+    q.K_total = (double)K_total;
+    q.nana = (double)nana;
+    q.scale_over_k = scale / (double)K_total;
+    q.nch = nch;
+    q.onesided = onesided;
+    q.F = onesided ? L / 2 : L;
+    q.W = wlow;
+    q.acc = state;
+    q.lin = state + (size_t)nch * 4 * NBIN;
+    q.stats = q.lin + (size_t)nch * 4 * (L / 16);
+    q.Pxx = Pxx;
+    q.Pyy = Pyy;
+    q.Pxy = Pxy;
+    q.Cxy = Cxy;
+    q.Cxy2 = Cxy2;
+    q.phi = phi;
+    q.status = status_flag;
+    q.peer_base = peer_base;
+    q.rank = rank;
+    q.world = world;
+    q.mode = (deferred && world > 1) ? 1 : 0;
+    return tc_post_launch(q, pdl, st);
+}
+
+int pyfft_welch_tc_step_flush(int32_t nch, const double* wlow, int64_t K_total, int64_t nana, double scale,
+                              int32_t onesided, double* state, double* Pxx, double* Pyy, double* Pxy, double* Cxy,
+                              double* Cxy2, double* phi, int32_t* status_flag, const int64_t* peer_base, int32_t rank,
+                              int32_t world, void* stream) {
+    using namespace tcw;
+    if (!state || !wlow || !status_flag || nch <= 0) return fail(PYFFT_EINVAL, "welch_tc_step_flush: NULL pointer or nch <= 0");
+    if (K_total <= 0 || nana <= 0) return fail(PYFFT_EINVAL, "welch_tc_step_flush: K_total and nana must be positive");
+    if (world < 2 || world > 256 || rank < 0 || rank >= world || !peer_base)
+        return fail(PYFFT_EINVAL, "welch_tc_step_flush: bad rank / world / peer_base (only sharded steps are deferred)");
+    TcPostParams q = {};
+    q.K_total = (double)K_total;
+    q.nana = (double)nana;
+    q.scale_over_k = scale / (double)K_total;
+    q.nch = nch;
+    q.onesided = onesided;
+    q.F = onesided ? L / 2 : L;
+    q.W = wlow;
+    q.acc = state;
+    q.lin = state + (size_t)nch * 4 * NBIN;
+    q.stats = q.lin + (size_t)nch * 4 * (L / 16);
+    q.Pxx = Pxx;
+    q.Pyy = Pyy;
+    q.Pxy = Pxy;
+    q.Cxy = Cxy;
+    q.Cxy2 = Cxy2;
+    q.phi = phi;
+    q.status = status_flag;
+    q.peer_base = peer_base;
+    q.rank = rank;
+    q.world = world;
+    q.mode = 2;
+    return tc_post_launch(q, false, static_cast<cudaStream_t>(stream));
 }
 
 }  // extern "C"

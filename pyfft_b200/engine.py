@@ -191,6 +191,49 @@ class PeerReducer:
             raise RuntimeError("pyfft_b200: a peer did not reach the NVLink reduction in time")
 
 
+class PeerStepBuffer:
+    """Symmetric staging buffer of the fused sharded step (pyfft_welch_tc_step, world > 1): two staging copies per
+    rank and per 32-bin work item, per-item flags and epochs; peer-mapped like PeerReducer's."""
+
+    _cache = {}
+
+    def __init__(self, nch, device, group):
+        import torch.distributed._symmetric_memory as symm
+        dist = torch.distributed
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        nbytes = check(lib.pyfft_welch_tc_step_peer_bytes(int(nch), self.world))
+        self.buf = symm.empty((nbytes + 7) // 8, dtype=torch.float64, device=device)
+        self.buf.zero_()
+        self.hdl = symm.rendezvous(self.buf, group.group_name)
+        self.peer_base = torch.tensor([int(p) for p in self.hdl.buffer_ptrs], dtype=torch.int64, device=device)
+        torch.cuda.synchronize(device)
+        dist.barrier(group=group)                      # every rank's flags are zero before the first epoch
+
+    @classmethod
+    def create(cls, nch, device, group):
+        """-> PeerStepBuffer, or False when peer memory is not available (the caller keeps the unfused sequence)."""
+        if os.environ.get("PYFFT_PEER_REDUCE", "1") == "0":
+            return False
+        dist = torch.distributed
+        if not (dist.is_available() and dist.is_initialized()):
+            return False
+        g = dist.group.WORLD if group is None else group
+        if dist.get_world_size(g) < 2 or dist.get_backend(g) != "nccl":
+            return False
+        key = (int(nch), str(device), g.group_name)
+        if key not in cls._cache:
+            try:
+                ok = cls(nch, device, g)
+            except Exception as exc:                   # no peer mapping on this machine
+                import warnings
+                warnings.warn("pyfft_b200: NVLink peer exchange unavailable (%s); using the unfused step" % (exc,))
+                ok = False
+            flag = torch.tensor([1 if ok else 0], dtype=torch.int32, device=device)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=g)          # all ranks must take the same route
+            cls._cache[key] = ok if int(flag.item()) == 1 else False
+        return cls._cache[key]
+
+
 class WelchPlan(object):
     """Streaming Welch accumulator for one x channel against nch y channels.
 
@@ -240,6 +283,9 @@ class WelchPlan(object):
         self._tc_status = None
         self._zero_est = None
         self._tc_est = None
+        self._aux = None
+        self._deferred = None
+        self._deferred_args = None
 
     def reset(self):
         """Zeroes acc, lin, stats and the segment counts (one fill)."""
@@ -326,6 +372,90 @@ class WelchPlan(object):
                                             _ptr(self._tc_status), _stream()))
         self.K += int(seg_count)
         self.K_local += int(seg_count)
+
+    def step_tc(self, x, y, rmap, seg_first, seg_count, tails, K, nana, scale, onesided=True, group=None,
+                peer_override=None, deferred=False):
+        """The whole fused tensor-core step over resident records in three launches (pyfft_welch_tc_step):
+        provisional statistics + head + tail sums, the main kernel, and ONE kernel that sums the partials,
+        exchanges them with the other ranks of `group` over NVLink peer memory, writes `state` and the
+        finalised spectra.  tails = ((a0, a1), (b0, b1)): analysed-index spans outside [seg_first*hop,
+        (seg_first+seg_count)*hop) whose raw sums the exact mean needs.  -> the dict of finalize(), or None when
+        the group has no peer memory (nothing was launched: use the unfused sequence).
+        peer_override = (peer_base int64 device tensor, rank, world): tests drive several ranks from one process.
+        deferred (sharded streams of steps): the exchange pushed by this call is collected by the NEXT deferred call
+        or by flush_tc(), a whole main kernel later -- no rank waits for a slower one inside a step.  The dict
+        returned then holds the PREVIOUS deferred step's spectra once this call's kernels have run (None for the
+        first call of a stream); flush_tc() returns the last step's."""
+        world, rank, peer = 1, 0, None
+        if peer_override is not None:
+            class _P(object):
+                pass
+            peer = _P()
+            peer.peer_base, rank, world = peer_override
+        elif group is not None and torch.distributed.get_world_size(group) > 1:
+            peer = PeerStepBuffer.create(self.nch, self.device, group)
+            if not peer:
+                return None
+            world, rank = peer.world, peer.rank
+        n1 = self.nch + 1
+        if self._aux is None:
+            self._aux = torch.empty(21 * n1, dtype=torch.float64, device=self.device)
+        self.est, self.prescale = self._aux[:2 * n1], self._aux[2 * n1:18 * n1]
+        seg = Segmentation(self.nfft, self.hop, seg_first, seg_count)
+        need = check(lib.pyfft_welch_tc_workspace_bytes(C.byref(seg), self.nch))
+        if self._ws is None or self._ws.numel() < need:
+            self._ws = torch.empty(need, dtype=torch.uint8, device=self.device)
+        if self._tc_status is None:
+            self._tc_status = torch.zeros(1, dtype=torch.int32, device=self.device)
+        F = self.nfft // 2 if onesided else self.nfft
+        dev = self.device
+        out = dict(Pxx=torch.empty(F, dtype=torch.complex128, device=dev),
+                   Pyy=torch.empty((F, self.nch), dtype=torch.complex128, device=dev),
+                   Pxy=torch.empty((F, self.nch), dtype=torch.complex128, device=dev),
+                   Cxy=torch.empty((F, self.nch), dtype=torch.complex128, device=dev),
+                   Cxy2=torch.empty((F, self.nch), dtype=torch.complex128, device=dev),
+                   phi_xy=torch.empty((F, self.nch), dtype=torch.float64, device=dev))
+        (a0, a1), (b0, b1) = tails
+        check(lib.pyfft_welch_tc_step(_ptr(x), _ptr(y), y.stride(0), self.nch, C.byref(rmap), C.byref(seg),
+                                      _ptr(self.window), _ptr(self.wlow), int(a0), int(a1), int(b0), int(b1),
+                                      int(K), int(nana), float(scale), 1 if onesided else 0, _ptr(self._aux),
+                                      _ptr(self.state), _ptr(out["Pxx"]), _ptr(out["Pyy"]), _ptr(out["Pxy"]),
+                                      _ptr(out["Cxy"]), _ptr(out["Cxy2"]), _ptr(out["phi_xy"]), _ptr(self._ws),
+                                      self._ws.numel(), _ptr(self._tc_status),
+                                      _ptr(peer.peer_base) if peer else C.c_void_p(0), rank, world,
+                                      1 if (deferred and world > 1) else 0, _stream()))
+        self.K = int(K)
+        self.K_local = int(seg_count)
+        self.coef = None
+        if deferred and world > 1:
+            first = self._deferred is None
+            self._deferred = self._deferred_args = (peer, rank, world, int(K), int(nana), float(scale), bool(onesided))
+            return None if first else out
+        if self._deferred is not None:
+            raise RuntimeError("step_tc: a deferred step is pending; call flush_tc() before a plain step")
+        return out
+
+    def flush_tc(self, force=False):
+        """Collects the exchange of the last deferred step_tc -> its dict of spectra (None if nothing is pending).
+        force: the deferred steps were replayed from a CUDA graph, which this object does not see -- launch the
+        flush with the arguments of the last deferred call (the device keeps the pending flags itself)."""
+        if self._deferred is None and not (force and self._deferred_args is not None):
+            return None
+        peer, rank, world, K, nana, scale, onesided = self._deferred or self._deferred_args
+        self._deferred = None
+        F = self.nfft // 2 if onesided else self.nfft
+        dev = self.device
+        out = dict(Pxx=torch.empty(F, dtype=torch.complex128, device=dev),
+                   Pyy=torch.empty((F, self.nch), dtype=torch.complex128, device=dev),
+                   Pxy=torch.empty((F, self.nch), dtype=torch.complex128, device=dev),
+                   Cxy=torch.empty((F, self.nch), dtype=torch.complex128, device=dev),
+                   Cxy2=torch.empty((F, self.nch), dtype=torch.complex128, device=dev),
+                   phi_xy=torch.empty((F, self.nch), dtype=torch.float64, device=dev))
+        check(lib.pyfft_welch_tc_step_flush(self.nch, _ptr(self.wlow), K, nana, scale, 1 if onesided else 0,
+                                            _ptr(self.state), _ptr(out["Pxx"]), _ptr(out["Pyy"]), _ptr(out["Pxy"]),
+                                            _ptr(out["Cxy"]), _ptr(out["Cxy2"]), _ptr(out["phi_xy"]),
+                                            _ptr(self._tc_status), _ptr(peer.peer_base), rank, world, _stream()))
+        return out
 
     def tc_failed(self):
         """True when a tensor-core barrier wait timed out (synchronises)."""

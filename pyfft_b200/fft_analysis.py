@@ -25,6 +25,7 @@ Deliberate differences from the reference (documented in DESIGN.md):
   * the per-segment fields of fftinfo (Pxx_seg, Xfft_seg, ...) are computed lazily
     on first access instead of being materialised on every call.
 """
+import os
 import threading
 
 import numpy as np
@@ -514,7 +515,15 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
                 use_tc = wp.can_use_tc and (nseg >= 16384 if tc_choice is None else bool(tc_choice))
                 accumulate = wp.accumulate_tc if use_tc else wp.accumulate_mean
                 estimate = wp.prepare_tc if use_tc else wp.estimate_mean
-                if staged is None:
+                res = None
+                if staged is None and use_tc and K >= world and os.environ.get("PYFFT_UNFUSED_STEP") != "1":
+                    # resident records: the whole step in three launches (statistics + head + tail sums | main
+                    # kernel | partial sums + NVLink exchange + finalize); None = the group has no peer memory
+                    res = wp.step_tc(x, y, rmap, lp["k0"], nseg, ((s_lo, c_lo), (c_hi, s_hi)), K, plan.nana, scale,
+                                     bool(onesided), group if world > 1 else None)
+                if res is not None:
+                    pass
+                elif staged is None:
                     estimate(x, y, rmap, c_lo, c_hi)
                     accumulate(x, y, rmap, lp["k0"], nseg)
                 else:
@@ -539,13 +548,14 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
                         if kend > kdone:
                             accumulate(x, y, rmap, kdone, kend - kdone)
                             kdone = kend
-                if s_lo < c_lo:
-                    wp.detrend_stats(x, y, rmap, s_lo, c_lo)
-                if s_hi > c_hi:
-                    wp.detrend_stats(x, y, rmap, c_hi, s_hi)
+                if res is None:
+                    if s_lo < c_lo:
+                        wp.detrend_stats(x, y, rmap, s_lo, c_lo)
+                    if s_hi > c_hi:
+                        wp.detrend_stats(x, y, rmap, c_hi, s_hi)
                 fix_nana = plan.nana                        # mean correction folded into finalize
                 offs = wp.mean_offset(plan.nana) if (group is None and precision == "fp32") else None
-                if group is not None:
+                if group is not None and res is None:
                     wp.rereference()                        # common reference, then ONE collective
                     wp.all_reduce_state(group)
                     wp.K = K
@@ -557,7 +567,9 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
                 wp.accumulate(x, y, rmap, lp["k0"], nseg)
             if group is not None and fix_nana is None:
                 wp.all_reduce(group)
-            res = wp.finalize(scale, onesided=bool(onesided), K=K, correct_nana=fix_nana)
+            fused_step = fused and res is not None
+            if not fused_step:
+                res = wp.finalize(scale, onesided=bool(onesided), K=K, correct_nana=fix_nana)
             corr = {}
             for nm, key, halve in (("Rxx", "Pxx", True), ("Ryy", "Pyy", True), ("Rxy", "Pxy", True),
                                    ("iCxy", "Cxy", False)):
@@ -567,7 +579,7 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
                 extras.append(offs)
             if use_tc:
                 extras += [wp._tc_status, wp.dynamic_range(res, onesided=bool(onesided)), wp.tc_repetition()]
-            peer = wp.peer_status() if (group is not None and fused) else None
+            peer = wp.peer_status() if (group is not None and fused and not fused_step) else None
             if peer is not None:
                 extras.append(peer)
             hosted = _host_many([res["Pxx"], res["Pyy"], res["Pxy"], res["Cxy"], res["Cxy2"], res["phi_xy"],
@@ -619,6 +631,10 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
         fftinfo.tc_checks = dict(status=flag, min_over_mean=float(np.min(rng[:, 0] / np.maximum(rng[:, 1], 1e-300))),
                                  repetition=float(np.min(rep[0])), stationarity=float(np.min(rep[1])))
         why = None
+        if flag & 4:
+            wp._tc_status.zero_()
+            raise RuntimeError("pyfft_b200: a peer GPU did not reach the NVLink exchange of the fused step in time; "
+                               "the results of this call are invalid (PYFFT_PEER_REDUCE=0 selects NCCL)")
         if flag & 1:
             why = "a tensor-core pipeline barrier timed out"
         elif flag & 2:
