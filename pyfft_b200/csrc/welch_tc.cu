@@ -920,9 +920,11 @@ __global__ void __launch_bounds__(256) tc_pre_kernel(const float* __restrict__ x
 //      order (bit-identical on every GPU).  Flags are per item: no CTA waits for another CTA of its own grid.
 //   C. state (acc | lin | stats) is written and the 32 bins are finalised (welch_finalize_kernel with the mean
 //      correction).
-// Peer buffer of one rank (doubles): stage[2][world][items][POST_SLOT] | uint32 flags[world][items] | uint32
-// epochs[items]; zero-filled once.  A rank can be at most one epoch ahead of a peer (it needs the peer's flag of
-// epoch e to finish e, which the peer sets after it has read epoch e-1), hence two staging copies.
+// Peer buffer of one rank: stage[2][world][items][POST_SLOT] values of 16 bytes | uint32 flags[world][items] |
+// uint32 epochs[items] | uint32 pending[items]; zero-filled once.  A value travels as two 8-byte words (32 data bits
+// | epoch), valid by themselves on arrival (the protocol NCCL calls LL); PYFFT_POST_FENCE=1 selects plain stores +
+// system fence + one flag per item and rank instead.  A rank can be at most one epoch ahead of a peer (it needs
+// the peer's words of epoch e to finish e, which the peer sends after it has read epoch e-1), hence two copies.
 constexpr int POST_SLOT = 168;                    // 128 acc + 32 lin + 2 raw sums, padded
 constexpr int POST_NBB = (tcw::NBIN + 31) / 32;   // items per pair
 constexpr int POST_THREADS = 512, POST_WARPS = POST_THREADS / 32;
@@ -949,6 +951,7 @@ struct TcPostParams {
     const int64_t* peer_base;
     int rank, world;
     int mode;                 // 0 = this step, exchange waited for; 1 = deferred exchange; 2 = flush
+    int ll;                   // exchange protocol: 1 = flagged 8-byte words (default), 0 = plain stores + fence + flag
 };
 
 // mode 0: reduce -> [exchange: push, wait, sum] -> finalize, all for THIS step (what pyfft_welch_tc_step returns
@@ -967,7 +970,7 @@ __global__ void __launch_bounds__(POST_THREADS) tc_post_kernel(const TcPostParam
     __shared__ double sa[4][32], sl[4][NLIN], sraw[2];
     __shared__ uint32_t s_epoch, s_pending;
     __shared__ int s_ok;
-    const size_t stage_doubles = (size_t)2 * p.world * items * POST_SLOT;
+    const size_t stage_doubles = (size_t)4 * p.world * items * POST_SLOT;     // 16 bytes per value (two flagged words)
     uint32_t* const my_words = p.world > 1 ? reinterpret_cast<uint32_t*>(reinterpret_cast<double*>(p.peer_base[p.rank]) + stage_doubles)
                                            : nullptr;      // flags[world][items] | epochs[items] | pending[items]
     pdl_wait();
@@ -983,6 +986,22 @@ __global__ void __launch_bounds__(POST_THREADS) tc_post_kernel(const TcPostParam
         __syncthreads();
         const uint32_t epoch_prev = s_epoch;
         const bool pending = s_pending != 0u;
+        // the loads of this step's partials are issued first and stay in registers while a deferred exchange is
+        // collected and finalised: every warp takes every 16th part, up to 10 parts x 4 rows (+ 10 linear sums) per
+        // thread, all independent
+        float rp[10][4], rl[10];
+        {
+            const float* pp = p.partial + (size_t)pair * p.nparts * PER_PAIR + f;
+            const float* lp = p.lin_partial + (size_t)pair * p.nparts * 4 * LROW + (lane >> 3) * LROW + (lane & 7);
+            const bool main_ok = p.mode != 2 && f < NBIN, lin_ok = p.mode != 2 && bb == 0;
+#pragma unroll
+            for (int u = 0; u < 10; ++u) {
+                const int k = g + POST_WARPS * u;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) rp[u][q] = (main_ok && k < p.nparts) ? pp[(size_t)k * PER_PAIR + q * NBIN] : 0.f;
+                rl[u] = (lin_ok && k < p.nparts) ? lp[(size_t)k * 4 * LROW] : 0.f;
+            }
+        }
         // phases of this item: collect + finalise what was pushed before / reduce this step / push it / collect it
         const bool do_old = p.world > 1 && p.mode != 0 && pending;
         const bool do_reduce = p.mode != 2;
@@ -993,40 +1012,23 @@ __global__ void __launch_bounds__(POST_THREADS) tc_post_kernel(const TcPostParam
             if (phase == 1) {
                 if (!do_reduce) break;
                 // ---- A: reduce the partials of the main kernel ---------------------------------- //
-                // every warp takes every 16th part: up to 10 parts x 4 rows = 40 independent loads per thread and round
-                double s[4] = {0.0, 0.0, 0.0, 0.0};
-                if (f < NBIN) {
-                    const float* pp = p.partial + (size_t)pair * p.nparts * PER_PAIR + f;
-                    for (int k0 = g; k0 < p.nparts; k0 += 10 * POST_WARPS) {
-                        float r[10][4];
+                double s[4] = {0.0, 0.0, 0.0, 0.0}, t = 0.0;
 #pragma unroll
-                        for (int u = 0; u < 10; ++u) {
-                            const int k = k0 + POST_WARPS * u;
+                for (int u = 0; u < 10; ++u) {
 #pragma unroll
-                            for (int q = 0; q < 4; ++q) r[u][q] = k < p.nparts ? pp[(size_t)k * PER_PAIR + q * NBIN] : 0.f;
-                        }
+                    for (int q = 0; q < 4; ++q) s[q] += (double)rp[u][q];
+                    t += (double)rl[u];
+                }
+                for (int k = g + 10 * POST_WARPS; k < p.nparts; k += POST_WARPS) {       // more than 160 parts: never on 148 SMs
+                    if (f < NBIN)
 #pragma unroll
-                        for (int u = 0; u < 10; ++u)
-#pragma unroll
-                            for (int q = 0; q < 4; ++q) s[q] += (double)r[u][q];
-                    }
+                        for (int q = 0; q < 4; ++q)
+                            s[q] += (double)p.partial[((size_t)pair * p.nparts + k) * PER_PAIR + q * NBIN + f];
+                    if (bb == 0)
+                        t += (double)p.lin_partial[((size_t)pair * p.nparts + k) * 4 * LROW + (lane >> 3) * LROW + (lane & 7)];
                 }
 #pragma unroll
                 for (int q = 0; q < 4; ++q) sh[g][q][lane] = s[q];
-                double t = 0.0;
-                if (bb == 0) {                    // lane -> row (re/im of U, V) = lane >> 3, bin = lane & 7
-                    const float* lp = p.lin_partial + (size_t)pair * p.nparts * 4 * LROW + (lane >> 3) * LROW + (lane & 7);
-                    for (int k0 = g; k0 < p.nparts; k0 += 10 * POST_WARPS) {
-                        float r[10];
-#pragma unroll
-                        for (int u = 0; u < 10; ++u) {
-                            const int k = k0 + POST_WARPS * u;
-                            r[u] = k < p.nparts ? lp[(size_t)k * 4 * LROW] : 0.f;
-                        }
-#pragma unroll
-                        for (int u = 0; u < 10; ++u) t += (double)r[u];
-                    }
-                }
                 sh[g][4][lane] = t;
                 __syncthreads();
                 if (g < 5) {
@@ -1067,17 +1069,35 @@ __global__ void __launch_bounds__(POST_THREADS) tc_post_kernel(const TcPostParam
                     __syncthreads();
                     const uint32_t epoch = epoch_prev + 1u;
                     const size_t slot0 = ((size_t)(epoch & 1u) * p.world * items + item) * POST_SLOT;   // + r * items * POST_SLOT
-                    if ((int)threadIdx.x < nval) {
-                        const int i = threadIdx.x;
-                        const double v = i < 128 ? sa[i >> 5][i & 31] : (i < 160 ? sl[(i - 128) >> 3][(i - 128) & 7] : sraw[i - 160]);
-                        for (int r = 0; r < p.world; ++r)
-                            (reinterpret_cast<double*>(p.peer_base[r]) + slot0 + (size_t)p.rank * items * POST_SLOT)[i] = v;
-                    }
-                    __threadfence_system();
-                    __syncthreads();
-                    if ((int)threadIdx.x < p.world) {
-                        uint32_t* theirs = reinterpret_cast<uint32_t*>(reinterpret_cast<double*>(p.peer_base[threadIdx.x]) + stage_doubles);
-                        st_release_sys(theirs + (size_t)p.rank * items + item, epoch);
+                    if (p.ll) {
+                        // every double travels as two 8-byte words (32 data bits | epoch): an 8-byte store arrives whole,
+                        // so a word that carries the epoch is valid by itself -- no fence, no separate flag, and the
+                        // latency of the exchange is one NVLink crossing
+                        if ((int)threadIdx.x < nval) {
+                            const int i = threadIdx.x;
+                            const double v = i < 128 ? sa[i >> 5][i & 31] : (i < 160 ? sl[(i - 128) >> 3][(i - 128) & 7] : sraw[i - 160]);
+                            const unsigned long long bits = (unsigned long long)__double_as_longlong(v);
+                            const unsigned long long w0 = (bits & 0xffffffffull) | ((unsigned long long)epoch << 32);
+                            const unsigned long long w1 = (bits >> 32) | ((unsigned long long)epoch << 32);
+                            for (int r = 0; r < p.world; ++r) {
+                                unsigned long long* d = reinterpret_cast<unsigned long long*>(p.peer_base[r]) +
+                                                        2 * (slot0 + (size_t)p.rank * items * POST_SLOT + i);
+                                asm volatile("st.relaxed.sys.global.v2.u64 [%0], {%1, %2};" ::"l"(d), "l"(w0), "l"(w1) : "memory");
+                            }
+                        }
+                    } else {
+                        if ((int)threadIdx.x < nval) {
+                            const int i = threadIdx.x;
+                            const double v = i < 128 ? sa[i >> 5][i & 31] : (i < 160 ? sl[(i - 128) >> 3][(i - 128) & 7] : sraw[i - 160]);
+                            for (int r = 0; r < p.world; ++r)
+                                (reinterpret_cast<double*>(p.peer_base[r]) + slot0 + (size_t)p.rank * items * POST_SLOT)[i] = v;
+                        }
+                        __threadfence_system();
+                        __syncthreads();
+                        if ((int)threadIdx.x < p.world) {
+                            uint32_t* theirs = reinterpret_cast<uint32_t*>(reinterpret_cast<double*>(p.peer_base[threadIdx.x]) + stage_doubles);
+                            st_release_sys(theirs + (size_t)p.rank * items + item, epoch);
+                        }
                     }
                     if (threadIdx.x == 0) {
                         my_words[(size_t)p.world * items + item] = epoch;
@@ -1093,27 +1113,61 @@ __global__ void __launch_bounds__(POST_THREADS) tc_post_kernel(const TcPostParam
                 // ---- B2: wait for the item's flags of all ranks, sum the local staging copy in rank order ---- //
                 const uint32_t epoch = phase == 0 ? epoch_prev : epoch_prev + 1u;
                 const size_t slot0 = ((size_t)(epoch & 1u) * p.world * items + item) * POST_SLOT;
-                if ((int)threadIdx.x < p.world) {
-                    bool ok = false;
-                    for (uint32_t it = 0; it < (1u << 24); ++it) {
-                        if ((int32_t)(ld_acquire_sys(my_words + (size_t)threadIdx.x * items + item) - epoch) >= 0) { ok = true; break; }
-                        __nanosleep(20);
+                if (p.ll) {
+                    if ((int)threadIdx.x < nval) {
+                        const int i = threadIdx.x;
+                        double s = 0.0;
+                        const unsigned long long* d0 = reinterpret_cast<const unsigned long long*>(p.peer_base[p.rank]) + 2 * (slot0 + i);
+                        const size_t rstride = (size_t)2 * items * POST_SLOT;
+                        for (int r0 = 0; r0 < p.world && s_ok; r0 += 8) {           // eight ranks' words in flight
+                            unsigned long long w0[8], w1[8];
+#pragma unroll
+                            for (int q = 0; q < 8; ++q)
+                                if (r0 + q < p.world)
+                                    asm volatile("ld.relaxed.sys.global.v2.u64 {%0, %1}, [%2];"
+                                                 : "=l"(w0[q]), "=l"(w1[q]) : "l"(d0 + (size_t)(r0 + q) * rstride) : "memory");
+#pragma unroll
+                            for (int q = 0; q < 8; ++q) {
+                                if (r0 + q >= p.world) break;
+                                uint32_t it = 0;
+                                while ((uint32_t)(w0[q] >> 32) != epoch || (uint32_t)(w1[q] >> 32) != epoch) {
+                                    if (++it > (1u << 24)) { s_ok = 0; atomicOr(p.status, 4); break; }
+                                    __nanosleep(20);
+                                    asm volatile("ld.relaxed.sys.global.v2.u64 {%0, %1}, [%2];"
+                                                 : "=l"(w0[q]), "=l"(w1[q]) : "l"(d0 + (size_t)(r0 + q) * rstride) : "memory");
+                                }
+                                // rank order: the same sum on every GPU
+                                s += __longlong_as_double((long long)((w0[q] & 0xffffffffull) | (w1[q] << 32)));
+                            }
+                        }
+                        if (!s_ok) s = __longlong_as_double(0x7ff8000000000000ll);    // a peer never arrived: fail loudly
+                        if (i < 128) sa[i >> 5][i & 31] = s;
+                        else if (i < 160) sl[(i - 128) >> 3][(i - 128) & 7] = s;
+                        else sraw[i - 160] = s;
                     }
-                    if (!ok) { s_ok = 0; atomicOr(p.status, 4); }
-                }
-                __syncthreads();
-                if ((int)threadIdx.x < nval) {
-                    const int i = threadIdx.x;
-                    double s = 0.0;
-                    if (s_ok) {
-                        const double* st = reinterpret_cast<const double*>(p.peer_base[p.rank]) + slot0 + i;
-                        for (int r = 0; r < p.world; ++r) s += ld_relaxed_sys(st + (size_t)r * items * POST_SLOT);
-                    } else {
-                        s = __longlong_as_double(0x7ff8000000000000ll);       // a peer never arrived: fail loudly
+                } else {
+                    if ((int)threadIdx.x < p.world) {
+                        bool ok = false;
+                        for (uint32_t it = 0; it < (1u << 24); ++it) {
+                            if ((int32_t)(ld_acquire_sys(my_words + (size_t)threadIdx.x * items + item) - epoch) >= 0) { ok = true; break; }
+                            __nanosleep(20);
+                        }
+                        if (!ok) { s_ok = 0; atomicOr(p.status, 4); }
                     }
-                    if (i < 128) sa[i >> 5][i & 31] = s;
-                    else if (i < 160) sl[(i - 128) >> 3][(i - 128) & 7] = s;
-                    else sraw[i - 160] = s;
+                    __syncthreads();
+                    if ((int)threadIdx.x < nval) {
+                        const int i = threadIdx.x;
+                        double s = 0.0;
+                        if (s_ok) {
+                            const double* st = reinterpret_cast<const double*>(p.peer_base[p.rank]) + slot0 + i;
+                            for (int r = 0; r < p.world; ++r) s += ld_relaxed_sys(st + (size_t)r * items * POST_SLOT);
+                        } else {
+                            s = __longlong_as_double(0x7ff8000000000000ll);       // a peer never arrived: fail loudly
+                        }
+                        if (i < 128) sa[i >> 5][i & 31] = s;
+                        else if (i < 160) sl[(i - 128) >> 3][(i - 128) & 7] = s;
+                        else sraw[i - 160] = s;
+                    }
                 }
                 if (phase == 0 && threadIdx.x == 0 && !do_push) my_words[(size_t)(p.world + 1) * items + item] = 0u;
                 __syncthreads();
@@ -1322,9 +1376,11 @@ static int tc_setup(const void* x, const void* y, int64_t y_stride, int32_t nch,
     return PYFFT_OK;
 }
 
-static int tc_post_launch(const TcPostParams& q, bool pdl, cudaStream_t st) {
+static int tc_post_launch(const TcPostParams& q_in, bool pdl, cudaStream_t st) {
     int sms = device_sm_count();
     if (sms <= 0) sms = 148;
+    TcPostParams q = q_in;
+    q.ll = getenv("PYFFT_POST_FENCE") == nullptr ? 1 : 0;
     int64_t blocks = (int64_t)q.nch * POST_NBB;
     if (blocks > 3 * (int64_t)sms) blocks = 3 * (int64_t)sms;      // co-resident: a CTA of the sharded step may wait for its peers
     cudaLaunchAttribute attr[1];
@@ -1415,7 +1471,7 @@ int pyfft_welch_accumulate_tc(const void* x, const void* y, int64_t y_stride, in
 int64_t pyfft_welch_tc_step_peer_bytes(int32_t nch, int32_t world) {
     if (nch <= 0 || world <= 0) return fail(PYFFT_EINVAL, "welch_tc_step_peer_bytes: bad arguments");
     const int64_t items = (int64_t)nch * POST_NBB;
-    return 2 * (int64_t)world * items * POST_SLOT * 8 + 4 * ((int64_t)world * items + 2 * items) + 64;
+    return 4 * (int64_t)world * items * POST_SLOT * 8 + 4 * ((int64_t)world * items + 2 * items) + 64;
 }
 
 int pyfft_welch_tc_step(const void* x, const void* y, int64_t y_stride, int32_t nch, const pyfft_record_map* map,

@@ -71,9 +71,10 @@ def test_fused_step_matches_unfused(onesided, reflect, nch):
     assert rep.shape == (2, nch + 1) and bool((rep[0] > 1e-2).all())
 
 
-def test_fused_step_two_ranks_one_process():
-    """world = 2 on one GPU: each 'rank' analyses half of the segments on its own stream, the peer buffers are
-    plain device tensors; both must end with the whole-record result."""
+@pytest.mark.parametrize("world", [2, 3])
+def test_fused_step_ranks_in_one_process(world):
+    """world = 2, 3 on one GPU: each 'rank' analyses its share of the segments on its own stream, the peer buffers
+    are plain device tensors; all must end with the whole-record result, bit-identical."""
     from pyfft_b200 import _lib
     nch, n = 2, 1 << 21
     engine, dev, x, y, win = _setup(n, nch, seed=5)
@@ -82,8 +83,8 @@ def test_fused_step_two_ranks_one_process():
     K = (nana - NFFT) // HOP + 1
     rmap = engine.record_map(nana, 0, reflect, 0, n)
     scale = 2.5e-3
-    kh = K // 2
-    spans = [(0, kh, ((0, 0), (0, 0))), (kh, K, ((0, 0), (K * HOP, nana)))]
+    cuts = [K * r // world for r in range(world + 1)]
+    spans = [(cuts[r], cuts[r + 1], ((0, 0), (K * HOP, nana) if r == world - 1 else (0, 0))) for r in range(world)]
     # the same decomposition through the unfused calls: every shard about its own provisional statistics, moved
     # to the common reference, the states added, one finalize with est = 0
     total = None
@@ -100,28 +101,29 @@ def test_fused_step_two_ranks_one_process():
     wp.state.copy_(total)
     ref = wp.finalize(scale, onesided=True, K=K, correct_nana=nana)
     ref = {k: v.clone() for k, v in ref.items()}
-    nbytes = int(_lib.lib.pyfft_welch_tc_step_peer_bytes(nch, 2))
-    bufs = [torch.zeros((nbytes + 7) // 8, dtype=torch.float64, device=dev) for _ in range(2)]
+    nbytes = int(_lib.lib.pyfft_welch_tc_step_peer_bytes(nch, world))
+    bufs = [torch.zeros((nbytes + 7) // 8, dtype=torch.float64, device=dev) for _ in range(world)]
     base = torch.tensor([b.data_ptr() for b in bufs], dtype=torch.int64, device=dev)
-    plans = [engine.WelchPlan(NFFT, HOP, nch, "fp32", win, dev) for _ in range(2)]
-    streams = [torch.cuda.Stream(device=dev) for _ in range(2)]
-    outs = [None, None]
+    plans = [engine.WelchPlan(NFFT, HOP, nch, "fp32", win, dev) for _ in range(world)]
+    streams = [torch.cuda.Stream(device=dev) for _ in range(world)]
+    outs = [None] * world
     torch.cuda.synchronize()
     for rep in range(3):                              # epochs advance on the device
-        for r in (0, 1):
+        for r in range(world):
             with torch.cuda.stream(streams[r]):
                 k0, k1, tails = spans[r]
                 outs[r] = plans[r].step_tc(x, y, rmap, k0, k1 - k0, tails, K, nana, scale, True,
-                                           peer_override=(base, r, 2))
+                                           peer_override=(base, r, world))
         torch.cuda.synchronize()
-        for r in (0, 1):
+        for r in range(world):
             assert int(plans[r]._tc_status.item()) == 0
             pk = float(ref["Pxx"].abs().max())
             for k in ("Pxx", "Pyy", "Pxy"):
                 assert float((outs[r][k] - ref[k]).abs().max()) <= 1e-9 * max(pk, float(ref[k].abs().max())), (rep, r, k)
             assert float((outs[r]["Cxy"] - ref["Cxy"]).abs().max()) < 1e-8
         for k in ("Pxx", "Pyy", "Pxy", "Cxy", "phi_xy"):
-            assert torch.equal(outs[0][k], outs[1][k]), k       # rank-ordered sums: bit-identical on both ranks
+            for r in range(1, world):
+                assert torch.equal(outs[0][k], outs[r][k]), k   # rank-ordered sums: bit-identical on every rank
 
 
 def test_fused_step_deferred_exchange_two_ranks():
