@@ -304,11 +304,30 @@ def run_ours(args):
             dist.barrier(group=group)
         torch.cuda.synchronize()
 
+    gate = {"red": None, "buf": None}
+
+    def device_gate():
+        """N > 1: after the host barrier the ranks' CPUs reach the timed loop tens of microseconds apart, and coupled
+        steps (one exchange per step) charge that start skew to the timed region of every rank.  A 2 ms device-side
+        sleep lets every rank enqueue its whole timed region, then a rendezvous kernel over NVLink peer memory (else
+        an NCCL all-reduce) releases all GPUs within a few microseconds of each other; the start event follows it."""
+        if group is None:
+            return
+        if gate["buf"] is None:
+            gate["buf"] = torch.zeros(8, dtype=torch.float64, device=dev)
+            gate["red"] = engine.PeerReducer.create(8, dev, group)
+        torch.cuda._sleep(4000000)
+        if gate["red"]:
+            gate["red"].all_reduce(gate["buf"])
+        else:
+            dist.all_reduce(gate["buf"], group=group)
+
     def timed(fn, steps, warmup, last=None):
         for _ in range(warmup):
             fn()
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        device_gate()
         e0.record()
         for _ in range(steps):
             fn()

@@ -237,7 +237,7 @@ int pyfft_welch_accumulate_tc(const void* x, const void* y, int64_t y_stride, in
  *                     what pyfft_detrend_stats_xy adds for the exact global mean, fft_analysis.py:356-357),
  *   welch_tc_kernel = the main kernel of pyfft_welch_accumulate_tc,
  *   tc_post_kernel  = sum of the per-CTA partials -> [sharded: rereference + exchange over NVLink peer memory]
- *                     -> state and the finalised spectra of pyfft_welch_finalize_mean, 32 bins per CTA.
+ *                     -> state and the finalised spectra of pyfft_welch_finalize_mean, 16 bins per CTA.
  * Same results as prepare + accumulate_tc + detrend_stats_xy (+ rereference + peer_allreduce) + finalize_mean;
  * the step is launch-bound around the main kernel, so the boundaries between the small kernels are what it saves.
  *   aux   = double[21 (nch+1)], written: est (2 per channel) | prescale (16 per channel, as pyfft_welch_tc_prepare)
@@ -272,6 +272,27 @@ int pyfft_welch_tc_step_flush(int32_t nch, const double* wlow, int64_t K_total, 
                               int32_t onesided, double* state, double* Pxx, double* Pyy, double* Pxy,
                               double* Cxy, double* Cxy2, double* phi, int32_t* status_flag,
                               const int64_t* peer_base, int32_t rank, int32_t world, void* stream);
+
+/* ------------------------------------------------------------------------- *
+ * per-segment statistics as fused reductions (csrc/segstats.cu)
+ * replaces: the reductions a caller makes over the per-segment spectra the reference materialises
+ *           (Pxx_seg, Pyy_seg, Pxy_seg, phixy_seg: fft_analysis.py:397-460, :1955-1970): np.var over the
+ *           segments -- the "real" variance estimates the reference comments out in favour of the stub
+ *           (P/sqrt(Navr))^2 (:449-458, :503-505) -- and mean_angle(phixy_seg) (:1334-1377).
+ * One pass over the records (the structure of pyfft_welch_accumulate: detrend coefficients, window, two real
+ * channels per complex FFT), nothing per-segment is written.
+ * out = double[nch][12][nfft/2 + 1], sums over the segments of, per bin of the half spectrum,
+ *   0..3  Pxx, Pyy, Re Pxy, Im Pxy   (Pxy = Y conj(X), unscaled products of the windowed detrended segments)
+ *   4..7  Pxx^2, Pyy^2, (Re Pxy)^2, (Im Pxy)^2
+ *   8..11 cos phi, sin phi, cos^2 phi, sin^2 phi,  phi = angle(Pxy) of the segment (angle(0) = 0).
+ * nfft = 64 .. 8192 (power of two); workspace from pyfft_segment_moments_workspace_bytes.
+ * ------------------------------------------------------------------------- */
+int64_t pyfft_segment_moments_workspace_bytes(int dtype, const pyfft_segmentation* seg, int32_t nch);
+
+int pyfft_segment_moments(int dtype, const void* x, const void* y, int64_t y_stride, int32_t nch,
+                          const pyfft_record_map* map, const pyfft_segmentation* seg, const void* window,
+                          const double* coef_x, const double* coef_y, double* out, void* workspace,
+                          int64_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------------- *
  * Welch finalize

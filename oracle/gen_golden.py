@@ -234,8 +234,45 @@ def gen_extras():
     print("wrote extras", d["peaks_4"])
 
 
+def gen_segstats():
+    """Statistics over the segments of the reference's own per-segment spectra (fft_analysis.py:397-460:
+    fftinfo.Pxx_seg / Pyy_seg / Pxy_seg / phixy_seg of the unmodified fft_pwelch): np.var (the estimates the
+    reference comments out at :449-458) and the reference's mean_angle (:1334-1377) of phixy_seg."""
+    import warnings
+    warnings.simplefilter("ignore")
+    m = ref_shim.load_reference()
+    fa = m["fft_analysis"]
+    rng = np.random.default_rng(4417)
+    d = {}
+    cases = (("a", 2 ** 14, 31, 1, True, 1), ("b", 2 ** 14, 63, 2, False, 1), ("c", 3 * 2 ** 12, 23, 1, True, -1),
+             ("d", 2 ** 13, 127, 3, True, 0))
+    for tag, n, navr, nch, onesided, detrend in cases:
+        t = np.arange(n) / 2.0e5
+        x = np.sin(2 * np.pi * 9.0e3 * t) + 0.5 * rng.standard_normal(n) + 0.8 + 3.0 * t
+        ys = [0.6 * np.sin(2 * np.pi * 9.0e3 * t + 0.5 * (c + 1)) + 0.3 * rng.standard_normal(n) + 0.1 * x - 0.4 * c
+              for c in range(nch)]
+        y = ys[0] if nch == 1 else np.stack(ys, axis=1)
+        out = fa.fft_pwelch(t, x, y, None, Navr=navr, windowoverlap=0.5, windowfunction="Hanning", useMLAB=False,
+                            plotit=False, verbose=False, detrend_style=detrend, onesided=onesided)
+        info = out[6]
+        pxx, pyy, pxy, ph = (np.asarray(getattr(info, k)) for k in ("Pxx_seg", "Pyy_seg", "Pxy_seg", "phixy_seg"))
+        d[tag + "_x"], d[tag + "_y"], d[tag + "_fs"] = x, y, np.asarray(2.0e5)
+        d[tag + "_cfg"] = np.asarray([n, navr, nch, int(onesided), detrend])
+        d[tag + "_navr"] = np.asarray(info.Navr)
+        d[tag + "_varPxx"] = np.var(pxx, axis=0)
+        d[tag + "_varPyy"] = np.var(pyy, axis=1).T
+        d[tag + "_varPxy"] = (np.var(pxy.real, axis=1) + 1j * np.var(pxy.imag, axis=1)).T
+        d[tag + "_Pxx"], d[tag + "_Pyy"], d[tag + "_Pxy"] = (np.asarray(out[i]) for i in (2, 3, 1))
+        mp, vp = fa.mean_angle(ph, dim=1)
+        d[tag + "_phi_mean"], d[tag + "_varphi_mean"] = np.asarray(mp).T, np.asarray(vp).T
+    np.savez_compressed(os.path.join(OUT, "segstats.npz"), **d)
+    print("wrote segstats", {k: v.shape for k, v in d.items() if k.startswith("b_")})
+
+
 if __name__ == "__main__":
-    if len(sys.argv) > 1 and sys.argv[1] == "fft_deriv":
+    if len(sys.argv) > 1 and sys.argv[1] == "segstats":
+        gen_segstats()
+    elif len(sys.argv) > 1 and sys.argv[1] == "fft_deriv":
         gen_fft_deriv()
     elif len(sys.argv) > 1 and sys.argv[1] == "extras":
         gen_extras()

@@ -68,6 +68,9 @@ _PROTOS = {
                                        _vp, _vp]),
     "pyfft_welch_finalize_mean": (C.c_int, [_vp, _vp, _i32, _i32, _i64, _vp, _vp, _i64, _vp, _dbl, _i32,
                                             _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "pyfft_segment_moments_workspace_bytes": (_i64, [C.c_int, _pseg, _i32]),
+    "pyfft_segment_moments": (C.c_int, [C.c_int, _vp, _vp, _i64, _i32, _pmap, _pseg, _vp, _vp, _vp, _vp, _vp, _i64,
+                                        _vp]),
     "pyfft_welch_dynamic_range": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _vp]),
     "pyfft_welch_correlation": (C.c_int, [_vp, _i32, _i32, _i32, _i32, _vp, _vp]),
     "pyfft_stft": (C.c_int, [C.c_int, _i32, _vp, _i64, _i32, _pmap, _pseg, _vp, _vp, _i32, _i32, _i32,

@@ -911,8 +911,8 @@ __global__ void __launch_bounds__(256) tc_pre_kernel(const float* __restrict__ x
     }
 }
 
-// One work item = 32 bins of one channel pair:
-//   A. the sums over the main kernel's per-CTA partials (4 rows x 32 bins; the item of bins 0..31 also the linear
+// One work item = 16 bins of one channel pair (129 items per pair: every SM takes one):
+//   A. the sums over the main kernel's per-CTA partials (4 rows x 16 bins; the item of bins 0..15 also the linear
 //      sums of bins < NLIN and the raw sample sums),
 //   B. sharded (world > 1): the shard's sums are moved to the common reference 0 (welch_rereference_kernel),
 //      WRITTEN into slot [rank] of every peer's staging buffer over NVLink, published with one release store per
@@ -925,8 +925,9 @@ __global__ void __launch_bounds__(256) tc_pre_kernel(const float* __restrict__ x
 // | epoch), valid by themselves on arrival (the protocol NCCL calls LL); PYFFT_POST_FENCE=1 selects plain stores +
 // system fence + one flag per item and rank instead.  A rank can be at most one epoch ahead of a peer (it needs
 // the peer's words of epoch e to finish e, which the peer sends after it has read epoch e-1), hence two copies.
-constexpr int POST_SLOT = 168;                    // 128 acc + 32 lin + 2 raw sums, padded
-constexpr int POST_NBB = (tcw::NBIN + 31) / 32;   // items per pair
+constexpr int POST_BINS = 16;                     // bins per work item
+constexpr int POST_SLOT = 4 * POST_BINS + 4 * tcw::NLIN + 8;        // 64 sums + 32 linear sums + 2 raw sums, padded
+constexpr int POST_NBB = (tcw::NBIN + POST_BINS - 1) / POST_BINS;   // items per pair: 129
 constexpr int POST_THREADS = 512, POST_WARPS = POST_THREADS / 32;
 struct TcPostParams {
     const float* partial;
@@ -952,6 +953,7 @@ struct TcPostParams {
     int rank, world;
     int mode;                 // 0 = this step, exchange waited for; 1 = deferred exchange; 2 = flush
     int ll;                   // exchange protocol: 1 = flagged 8-byte words (default), 0 = plain stores + fence + flag
+    long long* trace;         // debug: globaltimer stamps of CTA 0 (pyfft_debug_set_post_trace), or NULL
 };
 
 // mode 0: reduce -> [exchange: push, wait, sum] -> finalize, all for THIS step (what pyfft_welch_tc_step returns
@@ -961,23 +963,31 @@ struct TcPostParams {
 //         a full step ahead), then reduces and pushes this step's; outputs and state are the previous step's;
 // mode 2: flush -- collect and finalise what is pending, push nothing.
 // per item on the device: epochs[item] (last epoch pushed) and pending[item] (pushed, not yet collected).
+#define PYFFT_POST_STAMP(I)                                                              \
+    if (p.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0) {                     \
+        unsigned long long t_;                                                           \
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                           \
+        p.trace[I] = (long long)t_;                                                      \
+    }
 __global__ void __launch_bounds__(POST_THREADS) tc_post_kernel(const TcPostParams p) {
     using namespace tcw;
-    constexpr int PER_PAIR = 4 * NBIN, LROW = L / 16;
+    constexpr int PER_PAIR = 4 * NBIN, LROW = L / 16, NB = POST_BINS;
     const int lane = threadIdx.x & 31, g = threadIdx.x >> 5;
+    const int lb = lane & (NB - 1), half = lane / NB;       // bin of the item and which half of the parts
     const int items = p.nch * POST_NBB;
     __shared__ double sh[POST_WARPS][5][33];
-    __shared__ double sa[4][32], sl[4][NLIN], sraw[2];
+    __shared__ double sa[4][NB], sl[4][NLIN], sraw[2];
     __shared__ uint32_t s_epoch, s_pending;
     __shared__ int s_ok;
     const size_t stage_doubles = (size_t)4 * p.world * items * POST_SLOT;     // 16 bytes per value (two flagged words)
     uint32_t* const my_words = p.world > 1 ? reinterpret_cast<uint32_t*>(reinterpret_cast<double*>(p.peer_base[p.rank]) + stage_doubles)
                                            : nullptr;      // flags[world][items] | epochs[items] | pending[items]
-    pdl_wait();
+    PYFFT_POST_STAMP(0)
+    bool waited = false;                                     // for the main kernel (programmatic dependent launch)
     for (int item = blockIdx.x; item < items; item += gridDim.x) {
         const int pair = item / POST_NBB, bb = item - pair * POST_NBB;
-        const int f = bb * 32 + lane;
-        const int nval = bb == 0 ? 162 : 128;               // 4 x 32 sums (+ 4 x 8 linear sums + 2 raw sums)
+        const int f = bb * NB + lb;
+        const int nval = bb == 0 ? 4 * NB + 4 * NLIN + 2 : 4 * NB;     // the item's sums (+ linear sums + 2 raw sums)
         if (threadIdx.x == 0) {
             s_ok = 1;
             s_epoch = p.world > 1 ? my_words[(size_t)p.world * items + item] : 0u;
@@ -985,58 +995,74 @@ __global__ void __launch_bounds__(POST_THREADS) tc_post_kernel(const TcPostParam
         }
         __syncthreads();
         const uint32_t epoch_prev = s_epoch;
-        const bool pending = s_pending != 0u;
-        // the loads of this step's partials are issued first and stay in registers while a deferred exchange is
-        // collected and finalised: every warp takes every 16th part, up to 10 parts x 4 rows (+ 10 linear sums) per
-        // thread, all independent
-        float rp[10][4], rl[10];
-        {
-            const float* pp = p.partial + (size_t)pair * p.nparts * PER_PAIR + f;
-            const float* lp = p.lin_partial + (size_t)pair * p.nparts * 4 * LROW + (lane >> 3) * LROW + (lane & 7);
-            const bool main_ok = p.mode != 2 && f < NBIN, lin_ok = p.mode != 2 && bb == 0;
-#pragma unroll
-            for (int u = 0; u < 10; ++u) {
-                const int k = g + POST_WARPS * u;
-#pragma unroll
-                for (int q = 0; q < 4; ++q) rp[u][q] = (main_ok && k < p.nparts) ? pp[(size_t)k * PER_PAIR + q * NBIN] : 0.f;
-                rl[u] = (lin_ok && k < p.nparts) ? lp[(size_t)k * 4 * LROW] : 0.f;
-            }
-        }
-        // phases of this item: collect + finalise what was pushed before / reduce this step / push it / collect it
-        const bool do_old = p.world > 1 && p.mode != 0 && pending;
+        // what this launch does with the item: collect + finalise what the previous deferred step pushed / reduce
+        // this step's partials / push them / collect and finalise them
+        const bool do_old = p.world > 1 && p.mode != 0 && s_pending != 0u;
         const bool do_reduce = p.mode != 2;
         const bool do_push = p.world > 1 && p.mode != 2;
-        const bool do_now = p.mode == 0;                    // finalise this step's sums inside this launch
-        for (int phase = do_old ? 0 : 1; phase < 2; ++phase) {
-            double ex = 0.0, ey = 0.0, Kc = p.K_total;      // sums that went through the exchange are about the reference 0
-            if (phase == 1) {
+        const bool do_now = p.mode == 0 || p.world == 1;    // finalise this step's sums inside this launch
+        // this step's partials: the two halves of a warp take the even / odd parts of every 16th pair of parts, 5 parts
+        // x 4 rows (+ 10 linear sums in the item of bins 0..15) per thread, all independent, issued in one go and left
+        // in registers while the previous step is finalised
+        float rp[5][4], rl[10];
+#define PYFFT_POST_LOADS                                                                                         \
+        {                                                                                                            \
+            if (!waited) {                                                                                           \
+                pdl_wait();                                                                                          \
+                waited = true;                                                                                       \
+            }                                                                                                        \
+            PYFFT_POST_STAMP(1)                                                                                      \
+            const float* pp = p.partial + (size_t)pair * p.nparts * PER_PAIR + f;                                    \
+            const float* lp = p.lin_partial + (size_t)pair * p.nparts * 4 * LROW + (lane >> 3) * LROW + (lane & 7);  \
+            const bool main_ok = do_reduce && f < NBIN, lin_ok = do_reduce && bb == 0;                               \
+            _Pragma("unroll") for (int u = 0; u < 5; ++u) {                                                          \
+                const int k = 2 * (g + POST_WARPS * u) + half;                                                       \
+                _Pragma("unroll") for (int q = 0; q < 4; ++q)                                                        \
+                    rp[u][q] = (main_ok && k < p.nparts) ? pp[(size_t)k * PER_PAIR + q * NBIN] : 0.f;                \
+            }                                                                                                        \
+            _Pragma("unroll") for (int u = 0; u < 10; ++u) {                                                         \
+                const int k = g + POST_WARPS * u;                                                                    \
+                rl[u] = (lin_ok && k < p.nparts) ? lp[(size_t)k * 4 * LROW] : 0.f;                                   \
+            }                                                                                                        \
+        }
+#pragma unroll 1
+        for (int round = do_old ? 0 : 1; round < 2; ++round) {
+            // round 0: the previous deferred step (sums about the reference 0); round 1: this step
+            double ex = 0.0, ey = 0.0, Kc = p.K_total;
+            uint32_t epoch = epoch_prev;
+            if (round == 1) {
+                if (!do_old) PYFFT_POST_LOADS
+                PYFFT_POST_STAMP(3)
                 if (!do_reduce) break;
                 // ---- A: reduce the partials of the main kernel ---------------------------------- //
                 double s[4] = {0.0, 0.0, 0.0, 0.0}, t = 0.0;
 #pragma unroll
-                for (int u = 0; u < 10; ++u) {
+                for (int u = 0; u < 5; ++u)
 #pragma unroll
                     for (int q = 0; q < 4; ++q) s[q] += (double)rp[u][q];
-                    t += (double)rl[u];
-                }
-                for (int k = g + 10 * POST_WARPS; k < p.nparts; k += POST_WARPS) {       // more than 160 parts: never on 148 SMs
+#pragma unroll
+                for (int u = 0; u < 10; ++u) t += (double)rl[u];
+                for (int k = 10 * POST_WARPS + 2 * g + half; k < p.nparts; k += 2 * POST_WARPS)      // > 160 parts: never on 148 SMs
                     if (f < NBIN)
 #pragma unroll
                         for (int q = 0; q < 4; ++q)
                             s[q] += (double)p.partial[((size_t)pair * p.nparts + k) * PER_PAIR + q * NBIN + f];
+                for (int k = 10 * POST_WARPS + g; k < p.nparts; k += POST_WARPS)
                     if (bb == 0)
                         t += (double)p.lin_partial[((size_t)pair * p.nparts + k) * 4 * LROW + (lane >> 3) * LROW + (lane & 7)];
-                }
 #pragma unroll
-                for (int q = 0; q < 4; ++q) sh[g][q][lane] = s[q];
+                for (int q = 0; q < 4; ++q) {
+                    s[q] += __shfl_xor_sync(0xffffffffu, s[q], NB);
+                    if (half == 0) sh[g][q][lb] = s[q];
+                }
                 sh[g][4][lane] = t;
                 __syncthreads();
                 if (g < 5) {
                     double v = 0.0;
 #pragma unroll
-                    for (int u = 0; u < POST_WARPS; ++u) v += sh[u][g][lane];
+                    for (int u = 0; u < POST_WARPS; ++u) v += sh[u][g][g < 4 ? lb : lane];
                     if (g < 4) {
-                        sa[g][lane] = v;
+                        if (half == 0) sa[g][lb] = v;
                         // an fp16 operand out of range (a record far louder than the sampled statistics said) shows as Inf / NaN
                         if (f < NBIN && !isfinite(v)) atomicOr(p.status, 2);
                     } else if (bb == 0) {
@@ -1047,6 +1073,7 @@ __global__ void __launch_bounds__(POST_THREADS) tc_post_kernel(const TcPostParam
                     sraw[1] = p.tail[2 * (1 + pair)] + p.dev_sums[1 + pair] + p.count * p.est[2 * (1 + pair)];
                 }
                 __syncthreads();
+                PYFFT_POST_STAMP(4)
                 ex = p.est[0];
                 ey = p.est[2 * (1 + pair)];
                 Kc = p.K_local;
@@ -1067,15 +1094,17 @@ __global__ void __launch_bounds__(POST_THREADS) tc_post_kernel(const TcPostParam
                         sl[3][b] = svi - Kc * dy * wi;
                     }
                     __syncthreads();
-                    const uint32_t epoch = epoch_prev + 1u;
+                    epoch = epoch_prev + 1u;
                     const size_t slot0 = ((size_t)(epoch & 1u) * p.world * items + item) * POST_SLOT;   // + r * items * POST_SLOT
-                    if (p.ll) {
-                        // every double travels as two 8-byte words (32 data bits | epoch): an 8-byte store arrives whole,
-                        // so a word that carries the epoch is valid by itself -- no fence, no separate flag, and the
-                        // latency of the exchange is one NVLink crossing
-                        if ((int)threadIdx.x < nval) {
-                            const int i = threadIdx.x;
-                            const double v = i < 128 ? sa[i >> 5][i & 31] : (i < 160 ? sl[(i - 128) >> 3][(i - 128) & 7] : sraw[i - 160]);
+                    if ((int)threadIdx.x < nval) {
+                        const int i = threadIdx.x;
+                        const double v = i < 4 * NB ? sa[i / NB][i % NB]
+                                                    : (i < 4 * NB + 4 * NLIN ? sl[(i - 4 * NB) >> 3][(i - 4 * NB) & 7]
+                                                                             : sraw[i - 4 * NB - 4 * NLIN]);
+                        if (p.ll) {
+                            // every double travels as two 8-byte words (32 data bits | epoch): an 8-byte store arrives
+                            // whole, so a word that carries the epoch is valid by itself -- no fence, no separate flag,
+                            // and the latency of the exchange is one NVLink crossing
                             const unsigned long long bits = (unsigned long long)__double_as_longlong(v);
                             const unsigned long long w0 = (bits & 0xffffffffull) | ((unsigned long long)epoch << 32);
                             const unsigned long long w1 = (bits >> 32) | ((unsigned long long)epoch << 32);
@@ -1084,14 +1113,12 @@ __global__ void __launch_bounds__(POST_THREADS) tc_post_kernel(const TcPostParam
                                                         2 * (slot0 + (size_t)p.rank * items * POST_SLOT + i);
                                 asm volatile("st.relaxed.sys.global.v2.u64 [%0], {%1, %2};" ::"l"(d), "l"(w0), "l"(w1) : "memory");
                             }
-                        }
-                    } else {
-                        if ((int)threadIdx.x < nval) {
-                            const int i = threadIdx.x;
-                            const double v = i < 128 ? sa[i >> 5][i & 31] : (i < 160 ? sl[(i - 128) >> 3][(i - 128) & 7] : sraw[i - 160]);
+                        } else {
                             for (int r = 0; r < p.world; ++r)
                                 (reinterpret_cast<double*>(p.peer_base[r]) + slot0 + (size_t)p.rank * items * POST_SLOT)[i] = v;
                         }
+                    }
+                    if (!p.ll) {
                         __threadfence_system();
                         __syncthreads();
                         if ((int)threadIdx.x < p.world) {
@@ -1103,20 +1130,32 @@ __global__ void __launch_bounds__(POST_THREADS) tc_post_kernel(const TcPostParam
                         my_words[(size_t)p.world * items + item] = epoch;
                         my_words[(size_t)(p.world + 1) * items + item] = do_now ? 0u : 1u;
                     }
+                    PYFFT_POST_STAMP(5)
                     if (!do_now) break;                       // collected by the next deferred step or the flush
                     ex = 0.0;
                     ey = 0.0;
                     Kc = p.K_total;
+                    __syncthreads();
                 }
             }
             if (p.world > 1) {
-                // ---- B2: wait for the item's flags of all ranks, sum the local staging copy in rank order ---- //
-                const uint32_t epoch = phase == 0 ? epoch_prev : epoch_prev + 1u;
+                // ---- B2: the item's values of all ranks, summed from the local staging copy in rank order ---- //
                 const size_t slot0 = ((size_t)(epoch & 1u) * p.world * items + item) * POST_SLOT;
-                if (p.ll) {
-                    if ((int)threadIdx.x < nval) {
-                        const int i = threadIdx.x;
-                        double s = 0.0;
+                if (!p.ll) {
+                    if ((int)threadIdx.x < p.world) {
+                        bool ok = false;
+                        for (uint32_t it = 0; it < (1u << 24); ++it) {
+                            if ((int32_t)(ld_acquire_sys(my_words + (size_t)threadIdx.x * items + item) - epoch) >= 0) { ok = true; break; }
+                            __nanosleep(20);
+                        }
+                        if (!ok) { s_ok = 0; atomicOr(p.status, 4); }
+                    }
+                    __syncthreads();
+                }
+                if ((int)threadIdx.x < nval) {
+                    const int i = threadIdx.x;
+                    double s = 0.0;
+                    if (p.ll) {
                         const unsigned long long* d0 = reinterpret_cast<const unsigned long long*>(p.peer_base[p.rank]) + 2 * (slot0 + i);
                         const size_t rstride = (size_t)2 * items * POST_SLOT;
                         for (int r0 = 0; r0 < p.world && s_ok; r0 += 8) {           // eight ranks' words in flight
@@ -1140,104 +1179,99 @@ __global__ void __launch_bounds__(POST_THREADS) tc_post_kernel(const TcPostParam
                                 s += __longlong_as_double((long long)((w0[q] & 0xffffffffull) | (w1[q] << 32)));
                             }
                         }
-                        if (!s_ok) s = __longlong_as_double(0x7ff8000000000000ll);    // a peer never arrived: fail loudly
-                        if (i < 128) sa[i >> 5][i & 31] = s;
-                        else if (i < 160) sl[(i - 128) >> 3][(i - 128) & 7] = s;
-                        else sraw[i - 160] = s;
+                    } else if (s_ok) {
+                        const double* st = reinterpret_cast<const double*>(p.peer_base[p.rank]) + slot0 + i;
+                        for (int r = 0; r < p.world; ++r) s += ld_relaxed_sys(st + (size_t)r * items * POST_SLOT);
                     }
-                } else {
-                    if ((int)threadIdx.x < p.world) {
-                        bool ok = false;
-                        for (uint32_t it = 0; it < (1u << 24); ++it) {
-                            if ((int32_t)(ld_acquire_sys(my_words + (size_t)threadIdx.x * items + item) - epoch) >= 0) { ok = true; break; }
-                            __nanosleep(20);
-                        }
-                        if (!ok) { s_ok = 0; atomicOr(p.status, 4); }
-                    }
-                    __syncthreads();
-                    if ((int)threadIdx.x < nval) {
-                        const int i = threadIdx.x;
-                        double s = 0.0;
-                        if (s_ok) {
-                            const double* st = reinterpret_cast<const double*>(p.peer_base[p.rank]) + slot0 + i;
-                            for (int r = 0; r < p.world; ++r) s += ld_relaxed_sys(st + (size_t)r * items * POST_SLOT);
-                        } else {
-                            s = __longlong_as_double(0x7ff8000000000000ll);       // a peer never arrived: fail loudly
-                        }
-                        if (i < 128) sa[i >> 5][i & 31] = s;
-                        else if (i < 160) sl[(i - 128) >> 3][(i - 128) & 7] = s;
-                        else sraw[i - 160] = s;
-                    }
+                    if (!s_ok) s = __longlong_as_double(0x7ff8000000000000ll);    // a peer never arrived: fail loudly
+                    if (i < 4 * NB) sa[i / NB][i % NB] = s;
+                    else if (i < 4 * NB + 4 * NLIN) sl[(i - 4 * NB) >> 3][(i - 4 * NB) & 7] = s;
+                    else sraw[i - 4 * NB - 4 * NLIN] = s;
                 }
-                if (phase == 0 && threadIdx.x == 0 && !do_push) my_words[(size_t)(p.world + 1) * items + item] = 0u;
+                if (round == 0 && threadIdx.x == 0 && !do_push) my_words[(size_t)(p.world + 1) * items + item] = 0u;
                 __syncthreads();
             }
-            // ---- C: state and the finalised spectra ------------------------------------------------- //
-            if (threadIdx.x < 128) {
-                const int q = threadIdx.x >> 5;
-                if (f < NBIN) p.acc[((size_t)pair * 4 + q) * NBIN + f] = sa[q][lane];
+            PYFFT_POST_STAMP(round == 0 ? 2 : 6)
+            // what the previous step pushed does not depend on this step's main kernel: it was collected before
+            // waiting for it, and is finalised while this step's partials are on their way
+            if (round == 0) PYFFT_POST_LOADS
+            // ---- C: state and the finalised spectra (4 x NB threads: one group of outputs each) ---------- //
+            if (threadIdx.x < 4 * NB) {
+                const int q = threadIdx.x / NB, b = threadIdx.x % NB, fb = bb * NB + b;
+                if (fb < NBIN) p.acc[((size_t)pair * 4 + q) * NBIN + fb] = sa[q][b];
             }
-            if (bb == 0) {
-                for (int i = threadIdx.x; i < 4 * LROW; i += POST_THREADS)
+            if (bb == 0 && threadIdx.x >= 128) {
+                for (int i = threadIdx.x - 128; i < 4 * LROW; i += POST_THREADS - 128)
                     p.lin[(size_t)pair * 4 * LROW + i] = (i & (LROW - 1)) < NLIN ? sl[i / LROW][i & (LROW - 1)] : 0.0;
-                if (threadIdx.x == 0) {
+                if (threadIdx.x == 128) {
                     if (pair == 0) { p.stats[0] = sraw[0]; p.stats[1] = 0.0; }
                     p.stats[2 * (1 + pair)] = sraw[1];
                     p.stats[2 * (1 + pair) + 1] = 0.0;
                 }
             }
-            if (threadIdx.x < 32 && f < NBIN) {
-                double a0 = sa[0][lane], a1 = sa[1][lane], a2 = sa[2][lane], a3 = sa[3][lane];
-                if (bb == 0 && lane < NLIN) {
+            if (threadIdx.x < 4 * NB && bb * NB + (int)(threadIdx.x % NB) < NBIN) {
+                const int part = threadIdx.x / NB, b = threadIdx.x % NB;     // part 0: Pxx, Pyy, Pxy   1: Cxy   2: Cxy2   3: phi
+                const int fb = bb * NB + b;
+                double a0 = sa[0][b], a1 = sa[1][b], a2 = sa[2][b], a3 = sa[3][b];
+                if (bb == 0 && b < NLIN) {
                     const double dx = sraw[0] / p.nana - ex, dy = sraw[1] / p.nana - ey;
-                    const double wr = p.W[2 * f], wi = p.W[2 * f + 1], w2 = wr * wr + wi * wi;
-                    const double sur = sl[0][f], sui = sl[1][f], svr = sl[2][f], svi = sl[3][f];
+                    const double wr = p.W[2 * fb], wi = p.W[2 * fb + 1], w2 = wr * wr + wi * wi;
+                    const double sur = sl[0][fb], sui = sl[1][fb], svr = sl[2][fb], svi = sl[3][fb];
                     a0 += -2.0 * dx * (wr * sur + wi * sui) + Kc * dx * dx * w2;
                     a1 += -2.0 * dy * (wr * svr + wi * svi) + Kc * dy * dy * w2;
                     a2 += -dx * (wr * svr + wi * svi) - dy * (wr * sur + wi * sui) + Kc * dx * dy * w2;
                     a3 += -dx * (wr * svi - wi * svr) - dy * (wi * sur - wr * sui);
                 }
                 const int nch = p.nch;
-                // outputs of bin f: one-sided o = f (< F = L/2), x2 on bins 1..F-2 (fft_analysis.py:414-416);
-                // two-sided, fftshift order (:423-427): o = (f + L/2) mod L and, mirrored, o = L/2 - f with Pxy conjugated
+                // outputs of bin fb: one-sided o = fb (< F = L/2), x2 on bins 1..F-2 (fft_analysis.py:414-416);
+                // two-sided, fftshift order (:423-427): o = (fb + L/2) mod L and, mirrored, o = L/2 - fb with Pxy conjugated
                 for (int side = 0; side < 2; ++side) {
                     int o;
                     double wgt = 1.0;
                     bool conj = false;
                     if (p.onesided) {
-                        if (side == 1 || f >= p.F) break;
-                        o = f;
+                        if (side == 1 || fb >= p.F) break;
+                        o = fb;
                         if (o >= 1 && o <= p.F - 2) wgt = 2.0;
                     } else if (side == 0) {
-                        o = (f + L / 2) & (L - 1);
+                        o = (fb + L / 2) & (L - 1);
                     } else {
-                        if (f == 0 || f == L / 2) break;
-                        o = L / 2 - f;
+                        if (fb == 0 || fb == L / 2) break;
+                        o = L / 2 - fb;
                         conj = true;
                     }
                     const double s = p.scale_over_k * wgt;
                     const double pxx = a0 * s, pyy = a1 * s, pr = a2 * s, pi = (conj ? -a3 : a3) * s;
                     const size_t idx = (size_t)o * nch + pair;
-                    if (p.Pxx && pair == 0) { p.Pxx[2 * o] = pxx; p.Pxx[2 * o + 1] = 0.0; }
-                    if (p.Pyy) { p.Pyy[2 * idx] = pyy; p.Pyy[2 * idx + 1] = 0.0; }
-                    if (p.Pxy) { p.Pxy[2 * idx] = pr; p.Pxy[2 * idx + 1] = pi; }
                     const double den = fabs(pxx) * fabs(pyy);                 // fft_analysis.py:1672, 1677
-                    if (p.Cxy) { const double r = 1.0 / sqrt(den); p.Cxy[2 * idx] = pr * r; p.Cxy[2 * idx + 1] = pi * r; }
-                    if (p.Cxy2) { p.Cxy2[2 * idx] = (pr * pr + pi * pi) / den; p.Cxy2[2 * idx + 1] = 0.0 / den; }
-                    if (p.phi) p.phi[idx] = atan2(pi, pr);                    // fft_analysis.py:520
+                    if (part == 0) {
+                        if (p.Pxx && pair == 0) { p.Pxx[2 * o] = pxx; p.Pxx[2 * o + 1] = 0.0; }
+                        if (p.Pyy) { p.Pyy[2 * idx] = pyy; p.Pyy[2 * idx + 1] = 0.0; }
+                        if (p.Pxy) { p.Pxy[2 * idx] = pr; p.Pxy[2 * idx + 1] = pi; }
+                    } else if (part == 1) {
+                        if (p.Cxy) { const double r = 1.0 / sqrt(den); p.Cxy[2 * idx] = pr * r; p.Cxy[2 * idx + 1] = pi * r; }
+                    } else if (part == 2) {
+                        if (p.Cxy2) { p.Cxy2[2 * idx] = (pr * pr + pi * pi) / den; p.Cxy2[2 * idx + 1] = 0.0 / den; }
+                    } else {
+                        if (p.phi) p.phi[idx] = atan2(pi, pr);                // fft_analysis.py:520
+                    }
                 }
             }
             __syncthreads();
         }
+#undef PYFFT_POST_LOADS
         __syncthreads();
     }
+    PYFFT_POST_STAMP(7)
 }
+#undef PYFFT_POST_STAMP
 
 // ------------------------------------------------------------------------- //
 // host side
 // ------------------------------------------------------------------------- //
 static std::mutex g_tc_mutex;
 static long long* g_tc_trace = nullptr;     // debug hook, see pyfft_debug_set_tc_trace
+static long long* g_post_trace = nullptr;   // debug hook, see pyfft_debug_set_post_trace
 static std::map<int, unsigned char*> g_tc_consts;
 
 static void put_half(std::vector<unsigned char>& buf, size_t off, __half h) {
@@ -1381,8 +1415,13 @@ static int tc_post_launch(const TcPostParams& q_in, bool pdl, cudaStream_t st) {
     if (sms <= 0) sms = 148;
     TcPostParams q = q_in;
     q.ll = getenv("PYFFT_POST_FENCE") == nullptr ? 1 : 0;
+    q.trace = g_post_trace;
     int64_t blocks = (int64_t)q.nch * POST_NBB;
-    if (blocks > 3 * (int64_t)sms) blocks = 3 * (int64_t)sms;      // co-resident: a CTA of the sharded step may wait for its peers
+    if (blocks > (int64_t)sms) blocks = (int64_t)sms;             // one CTA per SM, items in the same order on every GPU
+    if (const char* cap = getenv("PYFFT_POST_BLOCKS")) {           // tests: several ranks driven on ONE GPU must all fit
+        const int64_t c = atoll(cap);
+        if (c >= 1 && c < blocks) blocks = c;
+    }      // co-resident: a CTA of the sharded step may wait for its peers
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
@@ -1407,6 +1446,14 @@ extern "C" {
 // clock64() stamps of its pipeline events (NULL switches it off); used by tools/tc_trace.py
 int pyfft_debug_set_tc_trace(void* buf) {
     g_tc_trace = static_cast<long long*>(buf);
+    return PYFFT_OK;
+}
+
+// debug: device buffer of 8 long long that CTA 0 of the next tc_post_kernel launches fills with globaltimer
+// stamps (0 start, 1 predecessor done, 2 deferred sums collected, 3 deferred step finalised, 4 partials reduced,
+// 5 pushed, 6 this step's sums collected, 7 end); NULL switches it off
+int pyfft_debug_set_post_trace(void* buf) {
+    g_post_trace = static_cast<long long*>(buf);
     return PYFFT_OK;
 }
 

@@ -72,10 +72,13 @@ def test_fused_step_matches_unfused(onesided, reflect, nch):
 
 
 @pytest.mark.parametrize("world", [2, 3])
-def test_fused_step_ranks_in_one_process(world):
+def test_fused_step_ranks_in_one_process(world, monkeypatch):
     """world = 2, 3 on one GPU: each 'rank' analyses its share of the segments on its own stream, the peer buffers
     are plain device tensors; all must end with the whole-record result, bit-identical."""
     from pyfft_b200 import _lib
+    # every rank's exchange kernel spins until all ranks have pushed: on ONE GPU they must leave SMs for the other
+    # ranks' main kernels (a real rank has a GPU to itself and runs one CTA per SM)
+    monkeypatch.setenv("PYFFT_POST_BLOCKS", "32")
     nch, n = 2, 1 << 21
     engine, dev, x, y, win = _setup(n, nch, seed=5)
     reflect = NFFT - 1
@@ -126,10 +129,11 @@ def test_fused_step_ranks_in_one_process(world):
                 assert torch.equal(outs[0][k], outs[r][k]), k   # rank-ordered sums: bit-identical on every rank
 
 
-def test_fused_step_deferred_exchange_two_ranks():
+def test_fused_step_deferred_exchange_two_ranks(monkeypatch):
     """Deferred exchange: step i's sums are collected by step i + 1 (or the flush); records that change from step
     to step must come out in order, one step late, and bit-identical on both ranks."""
     from pyfft_b200 import _lib
+    monkeypatch.setenv("PYFFT_POST_BLOCKS", "48")
     nch, n = 1, 1 << 20
     reflect = NFFT - 1
     nana = n + reflect
