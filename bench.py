@@ -41,8 +41,10 @@ def parse():
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="weak: --samples per channel PER GPU; strong: --samples per channel in TOTAL")
     ap.add_argument("--no-graph", action="store_true", help="launch the step's kernels one by one (no CUDA graph)")
-    ap.add_argument("--sync-exchange", action="store_true",
-                    help="N > 1: every step waits for its own exchange (default: collected by the next step)")
+    ap.add_argument("--deferred-exchange", action="store_true",
+                    help="N > 1: a step's exchange is collected by the next step (a stream of records; the timed region "
+                         "ends with the flush of its last step) instead of being waited for inside the step; measured "
+                         "equal on NVSwitch (profiles/r02f_multi_gpu.txt)")
     ap.add_argument("--unfused", action="store_true",
                     help="the step as separate calls (prepare, accumulate, tail sums, [rereference, reduce,] finalize) "
                          "instead of the three launches of pyfft_welch_tc_step")
@@ -261,7 +263,7 @@ def run_ours(args):
 
     tails = ((s_lo, c_lo), (c_hi, s_hi))
     fused_step = use_tc and not args.unfused
-    defer = world > 1 and not args.sync_exchange
+    defer = world > 1 and args.deferred_exchange
 
     def step():
         # ONE pass over HBM: provisional mean (+ scale) from 64 Ki samples, fused Welch
@@ -361,6 +363,16 @@ def run_ours(args):
         def step_sync():
             return wp.step_tc(x, y, rmap, k0, k1 - k0, tails, K, nana, scale, True, group, deferred=False)
         ms_sync = timed(step_sync if args.no_graph else engine.GraphedStep(step_sync), args.steps, 3)
+    ms_deferred = None
+    if step_is_fused and world > 1 and not deferred_on and wp._peer is None:
+        # for the record: the exchange of a step collected by the next one (no rank waits inside a step)
+        def step_def():
+            return wp.step_tc(x, y, rmap, k0, k1 - k0, tails, K, nana, scale, True, group, deferred=True)
+        step_def()
+        if wp._deferred_args is not None:
+            run_def = step_def if args.no_graph else engine.GraphedStep(step_def)
+            ms_deferred = timed(run_def, args.steps, 3, lambda: wp.flush_tc(force=True))
+            wp.flush_tc(force=True)
     # dominant kernel alone (welch_pair_kernel + its partial-sum reductions, ~3 us)
     wp.prepare_tc(x, y, rmap, c_lo, c_hi) if use_tc else wp.estimate_mean(x, y, rmap, c_lo, c_hi)
     ms_k1 = timed(lambda: (wp.accumulate_tc if use_tc else wp.accumulate_mean)(x, y, rmap, k0, k1 - k0),
@@ -471,7 +483,7 @@ def run_ours(args):
            "exchange": (None if world == 1 else
                         ("deferred: collected by the next step's tc_post_kernel, the timed region ends with the flush "
                          "of its last step" if deferred_on else "waited for inside every step")),
-           "sync_exchange_ms_per_step": ms_sync,
+           "sync_exchange_ms_per_step": ms_sync, "deferred_exchange_ms_per_step": ms_deferred,
            "launch_mode": "per-kernel launches" if args.no_graph else "one CUDA graph replay per step"}
     if world > 1:
         out["config"]["collective"] = (

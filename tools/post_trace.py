@@ -81,6 +81,25 @@ if rank == 0:
     print("mode:", "sync" if sync or world == 1 else "deferred", "world", world, "(us relative to 'K1 done')")
     for r, a in enumerate(allr):
         print("rank %d: " % r + "  ".join("%s %.2f" % (nm, v) for nm, v in zip(names, a.cpu().numpy())))
+# step time of the same replay, 200 back to back
+for _ in range(3):
+    if group is not None:
+        dist.barrier(group=group)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(200):
+        run()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1) / 200], device=dev, dtype=torch.float64)
+    each = [torch.zeros_like(ms) for _ in range(world)]
+    if group is not None:
+        dist.all_gather(each, ms, group=group)
+    else:
+        each = [ms]
+    if rank == 0:
+        print("ms per step, per rank:", " ".join("%.4f" % float(v) for v in each))
 if group is not None:
     wp.flush_tc(force=True)
     torch.cuda.synchronize()
