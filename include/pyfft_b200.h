@@ -274,6 +274,23 @@ int pyfft_welch_tc_step_flush(int32_t nch, const double* wlow, int64_t K_total, 
                               const int64_t* peer_base, int32_t rank, int32_t world, void* stream);
 
 /* ------------------------------------------------------------------------- *
+ * the steps either side of the path (csrc/bands.cu)
+ * pyfft_spectral_centroid replaces the reduction of Doppler.cog (Doppler.py:43-61) and of the per-window loop of
+ *   cogspec (:72-81): out[row] = sum_b P[row][b] wnum[b] / sum_b P[row][b] wden[b] (0 when wden is all zero) over
+ *   the window spectra P = |FFT|^2 [rows][nbins] as written by pyfft_stft with power_out (natural bin order); the
+ *   host puts the signed frequencies and the fmin / fmax selection into wnum / wden (double[nbins]).
+ * pyfft_resample_linear replaces filters.upsample (filters.py:20-34) behind fftanal.resample
+ *   (fft_analysis.py:2363-2373): records sampled at fs_in interpolated linearly onto t_i = i / fs_out, i < m
+ *   (evaluated like numpy.interp; pybaseutils.utils.interp, which the reference calls, is not in the image:
+ *   parity unpinned for this entry).
+ * ------------------------------------------------------------------------- */
+int pyfft_spectral_centroid(int dtype, const void* P, int64_t rows, int32_t nbins, const double* wnum,
+                            const double* wden, double* out, void* stream);
+
+int pyfft_resample_linear(int dtype, const void* in, int64_t in_stride, int32_t nch, int64_t n, double fs_in,
+                          double fs_out, int64_t m, void* out, int64_t out_stride, void* stream);
+
+/* ------------------------------------------------------------------------- *
  * per-segment statistics as fused reductions (csrc/segstats.cu)
  * replaces: the reductions a caller makes over the per-segment spectra the reference materialises
  *           (Pxx_seg, Pyy_seg, Pxy_seg, phixy_seg: fft_analysis.py:397-460, :1955-1970): np.var over the

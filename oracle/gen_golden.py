@@ -269,8 +269,54 @@ def gen_segstats():
     print("wrote segstats", {k: v.shape for k, v in d.items() if k.startswith("b_")})
 
 
+def gen_cog():
+    """Doppler.cog of the unmodified reference (Doppler.py:43-61).  Doppler.py itself cannot be imported as it is
+    -- it imports FFT.stft, a module the reference does not have -- so that name is bound to the reference's own
+    spectrogram.stft for the import; cog is called untouched."""
+    import importlib.util
+    import types
+    import warnings
+    warnings.simplefilter("ignore")
+    m = ref_shim.load_reference()
+    st = types.ModuleType("FFT.stft")
+    st.stft = m["spectrogram"].stft
+    sys.modules["FFT.stft"] = st
+    mods = {}
+    for name in ("filters", "Doppler"):
+        spec = importlib.util.spec_from_file_location("FFT." + name, os.path.join(ref_shim.REFERENCE_DIR, name + ".py"))
+        mods[name] = importlib.util.module_from_spec(spec)
+        sys.modules["FFT." + name] = mods[name]
+        spec.loader.exec_module(mods[name])
+    cog = mods["Doppler"].cog
+    rng = np.random.default_rng(77)
+    d = {}
+    fs = 2.0e6
+    for tag, n, cplx in (("a", 512, True), ("b", 1000, True), ("c", 4096, False), ("d", 333, True)):
+        t = np.arange(n) / fs
+        f0 = 1.3e5 + 4.0e4 * np.sin(2 * np.pi * 3.0e3 * t)
+        ph = 2 * np.pi * np.cumsum(f0) / fs
+        x = np.exp(1j * ph) + 0.2 * (rng.standard_normal(n) + 1j * rng.standard_normal(n))
+        if not cplx:
+            x = x.real
+        d[tag + "_x"] = x
+        d[tag + "_cog"] = np.asarray(cog(x, fs))
+        d[tag + "_cog_band"] = np.asarray(cog(x, fs, fmin=5.0e4, fmax=4.0e5))
+        d[tag + "_cog_none"] = np.asarray(cog(x, fs, fmin=3.0e6))           # empty selection -> 0.0
+    # sliding windows of one long record, each through the reference's cog
+    n, win, step = 2 ** 14, 512, 256
+    t = np.arange(n) / fs
+    ph = 2 * np.pi * np.cumsum(2.0e5 + 1.0e5 * np.sin(2 * np.pi * 2.0e3 * t)) / fs
+    x = np.exp(1j * ph) + 0.3 * (rng.standard_normal(n) + 1j * rng.standard_normal(n))
+    d["s_x"], d["s_fs"] = x, np.asarray(fs)
+    d["s_cog"] = np.asarray([cog(x[i:i + win], fs) for i in range(0, n - win + 1, step)])
+    np.savez_compressed(os.path.join(OUT, "cog.npz"), **d)
+    print("wrote cog", d["a_cog"], d["a_cog_band"], d["a_cog_none"], d["s_cog"][:3])
+
+
 if __name__ == "__main__":
-    if len(sys.argv) > 1 and sys.argv[1] == "segstats":
+    if len(sys.argv) > 1 and sys.argv[1] == "cog":
+        gen_cog()
+    elif len(sys.argv) > 1 and sys.argv[1] == "segstats":
         gen_segstats()
     elif len(sys.argv) > 1 and sys.argv[1] == "fft_deriv":
         gen_fft_deriv()

@@ -589,3 +589,34 @@ def fft_deriv(sig, xx=None, lowpass=True, Fs_new=None, modified=True, detrend=No
     d[-1] = ds1
     # unscale (:1439-1451)
     return d * slope / xslope, x * xslope + xoffset
+
+
+# --------------------------------------------------------------------------- #
+# SURVEY 8(f) rank 4
+# --------------------------------------------------------------------------- #
+def cog(x, fs, fmin=None, fmax=None):
+    """Doppler.cog (Doppler.py:43-61), line by line -- including the band selection, which indexes the spectrum
+    with a mask computed from the already filtered frequency vector (so the first len(freq) entries are kept)."""
+    if fmax is None:
+        fmax = fs
+    n = len(x)
+    freq = np.fft.fftshift(np.fft.fftfreq(n, 1 / fs))
+    spec = np.fft.fftshift(np.fft.fft(x)) / np.sqrt(n / 2)
+    if fmin is not None:
+        freq = freq[np.where((np.abs(freq) >= fmin) * (np.abs(freq) <= fmax))]
+        spec = spec[np.where((np.abs(freq) >= fmin) * (np.abs(freq) <= fmax))]
+    if len(freq) > 0:
+        return np.sum(np.abs(np.square(spec)) * freq) / np.sum(np.abs(np.square(spec)))
+    return 0.0
+
+
+def upsample(u_t, Fs, Fs_new):
+    """filters.upsample (filters.py:20-34) with numpy.interp standing in for pybaseutils.utils.interp (absent from
+    the image and from the reference tree: PARITY UNPINNED for this function)."""
+    u_t = np.asarray(u_t)
+    nt = len(u_t)
+    tt = np.arange(0, nt, 1) / Fs
+    ti = np.arange(tt[0], tt[-1], 1 / Fs_new)
+    if u_t.ndim == 1:
+        return np.interp(ti, tt, u_t)
+    return np.stack([np.interp(ti, tt, u_t[:, c]) for c in range(u_t.shape[1])], axis=1)

@@ -13,6 +13,8 @@ from .fft_analysis import (fft_pwelch, fftanal, cross_spectral_matrix, fft_deriv
                            mean_angle, varcoh, varphi)
 from .laplace import laplace_1d         # noqa: F401,E402
 from .segstats import welch_segment_statistics   # noqa: F401,E402
+from .filters import upsample            # noqa: F401,E402
+from .doppler import cog, cog_sliding    # noqa: F401,E402
 
 from .spectrogram import stft, specgram  # noqa: F401,E402
 from .hilbert import hilbert, hilbert_1d  # noqa: F401,E402

@@ -77,6 +77,8 @@ _PROTOS = {
                              _vp, _i32, _vp, _vp, _vp]),
     "pyfft_find_peaks": (C.c_int, [_vp, _i32, _i32, _i32, _i32, _vp, _vp]),
     "pyfft_band_integrate": (C.c_int, [_vp, _i32, _vp, _vp, _i32, _vp, _i32, _vp, _i32, _vp, _vp]),
+    "pyfft_spectral_centroid": (C.c_int, [C.c_int, _vp, _i64, _i32, _vp, _vp, _vp, _vp]),
+    "pyfft_resample_linear": (C.c_int, [C.c_int, _vp, _i64, _i32, _i64, _dbl, _dbl, _i64, _vp, _i64, _vp]),
     "pyfft_mean_angle": (C.c_int, [C.c_int, _vp, _vp, _vp, _i64, _i64, _vp, _vp]),
     "pyfft_anyfft_workspace_bytes": (_i64, [_i64, _i64]),
     "pyfft_laplace_1d": (C.c_int, [C.c_int, _vp, _i64, _vp, _i32, _vp, _vp, _i64, _vp]),

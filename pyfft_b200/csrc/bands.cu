@@ -163,6 +163,67 @@ __global__ void __launch_bounds__(256) mean_angle_kernel(const T* __restrict__ p
     o[3] = (sss / n - ms * ms) + sv / (kk * kk) + (sy / kk) * (sy / kk);
 }
 
+// ------------------------------------------------------------------------- //
+// the two steps either side of the path
+// ------------------------------------------------------------------------- //
+// Doppler.cog (Doppler.py:43-61): power-weighted mean frequency of every window's spectrum,
+// out[row] = sum_b P[row][b] wnum[b] / sum_b P[row][b] wden[b] (0 when no bin is selected), one warp per row.
+// P = |FFT|^2 of the windows as written by pyfft_stft (power_out, natural bin order); the host puts the signed
+// frequencies (and the band selection of fmin / fmax) into wnum / wden.
+template <typename T>
+__global__ void __launch_bounds__(256) spectral_centroid_kernel(const T* __restrict__ P, int64_t rows, int nb,
+                                                                const double* __restrict__ wnum,
+                                                                const double* __restrict__ wden, double* __restrict__ out) {
+    const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (row >= rows) return;
+    const T* p = P + row * nb;
+    double num = 0.0, den = 0.0, any = 0.0;
+    for (int b = lane; b < nb; b += 32) {
+        const double v = (double)p[b];
+        num += v * wnum[b];
+        den += v * wden[b];
+        any += wden[b];
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        num += __shfl_xor_sync(0xffffffffu, num, o);
+        den += __shfl_xor_sync(0xffffffffu, den, o);
+        any += __shfl_xor_sync(0xffffffffu, any, o);
+    }
+    if (lane == 0) out[row] = any > 0.0 ? num / den : 0.0;
+}
+
+// filters.upsample (filters.py:20-34; fftanal.resample, fft_analysis.py:2363-2373): piecewise-linear interpolation
+// of records sampled at fs_in onto the grid t_i = i / fs_out, i < m, written the way numpy.interp evaluates it
+// (slope (y1 - y0) / (x1 - x0) times (x - x0), plus y0, on the abscissae x_j = j / fs_in).
+template <typename T>
+__global__ void __launch_bounds__(256) resample_linear_kernel(const T* __restrict__ in, int64_t in_stride, int64_t n,
+                                                              double fs_in, double fs_out, int64_t m,
+                                                              T* __restrict__ out, int64_t out_stride) {
+    const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    if (i >= m) return;
+    const T* p = in + (int64_t)blockIdx.y * in_stride;
+    const double step = 1.0 / fs_out;
+    const double x = 0.0 + (double)i * step;                 // numpy.arange: start + i * step
+    int64_t j = (int64_t)floor(x * fs_in);
+    if (j > n - 2) j = n - 2;
+    if (j < 0) j = 0;
+    // the abscissae are j / fs_in: settle j so that x_j <= x < x_{j+1} in the arithmetic numpy sees
+    while (j > 0 && (double)j / fs_in > x) --j;
+    while (j < n - 2 && (double)(j + 1) / fs_in <= x) ++j;
+    double r;
+    if (n == 1) {
+        r = (double)p[0];
+    } else {
+        const double x0 = (double)j / fs_in, x1 = (double)(j + 1) / fs_in;
+        const double y0 = (double)p[j], y1 = (double)p[j + 1];
+        if (x >= x1 && j == n - 2) r = y1;                      // at (or past) the last sample: numpy.interp clamps
+        else r = (y1 - y0) / (x1 - x0) * (x - x0) + y0;
+    }
+    out[(int64_t)blockIdx.y * out_stride + i] = (T)r;
+}
+
 }  // namespace pyfft
 
 using namespace pyfft;
@@ -201,6 +262,39 @@ int pyfft_mean_angle(int dtype, const void* phi, const void* vphi, const void* v
                                                      static_cast<const double*>(vsyst), K, ncol, out);
     else return fail(PYFFT_EINVAL, "unknown dtype %d", dtype);
     PYFFT_LAUNCH_OK("mean_angle_kernel");
+    return PYFFT_OK;
+}
+
+int pyfft_spectral_centroid(int dtype, const void* P, int64_t rows, int32_t nbins, const double* wnum, const double* wden,
+                            double* out, void* stream) {
+    if (!P || !wnum || !wden || !out || rows <= 0 || nbins <= 0) return fail(PYFFT_EINVAL, "spectral_centroid: bad arguments");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const unsigned g = (unsigned)((rows + 7) / 8);
+    if (dtype == PYFFT_F32)
+        spectral_centroid_kernel<float><<<g, 256, 0, st>>>(static_cast<const float*>(P), rows, nbins, wnum, wden, out);
+    else if (dtype == PYFFT_F64)
+        spectral_centroid_kernel<double><<<g, 256, 0, st>>>(static_cast<const double*>(P), rows, nbins, wnum, wden, out);
+    else return fail(PYFFT_EINVAL, "unknown dtype %d", dtype);
+    PYFFT_LAUNCH_OK("spectral_centroid_kernel");
+    return PYFFT_OK;
+}
+
+int pyfft_resample_linear(int dtype, const void* in, int64_t in_stride, int32_t nch, int64_t n, double fs_in, double fs_out,
+                          int64_t m, void* out, int64_t out_stride, void* stream) {
+    if (!in || !out || nch <= 0 || n <= 0 || m <= 0 || !(fs_in > 0.0) || !(fs_out > 0.0))
+        return fail(PYFFT_EINVAL, "resample_linear: bad arguments");
+    if ((double)(m - 1) / fs_out > (double)(n - 1) / fs_in * (1.0 + 1e-12))
+        return fail(PYFFT_EINVAL, "resample_linear: the output grid runs past the last input sample");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const dim3 g((unsigned)((m + 255) / 256), (unsigned)nch);
+    if (dtype == PYFFT_F32)
+        resample_linear_kernel<float><<<g, 256, 0, st>>>(static_cast<const float*>(in), in_stride, n, fs_in, fs_out, m,
+                                                         static_cast<float*>(out), out_stride);
+    else if (dtype == PYFFT_F64)
+        resample_linear_kernel<double><<<g, 256, 0, st>>>(static_cast<const double*>(in), in_stride, n, fs_in, fs_out, m,
+                                                          static_cast<double*>(out), out_stride);
+    else return fail(PYFFT_EINVAL, "unknown dtype %d", dtype);
+    PYFFT_LAUNCH_OK("resample_linear_kernel");
     return PYFFT_OK;
 }
 

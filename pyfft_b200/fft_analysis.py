@@ -1056,7 +1056,9 @@ class fftanal(Struct):
         if self.onesided is None:
             self.onesided = not (np.iscomplexobj(sigx) or np.iscomplexobj(sigy))
         if self.tvecy is not None:
-            raise NotImplementedError("tvecy resampling (filters.upsample) is out of scope")
+            # put the signals on the same time base (fft_analysis.py:1750-1752)
+            self.tvec, self.sigx, self.sigy = self.resample(tvec, sigx, self.tvecy, sigy)
+            tvec, sigx, sigy = self.tvec, self.sigx, self.sigy
         self.Fs = self.__Fs__(self.tvec)
         self.ibounds = self.__ibounds__(self.tvec, self.tbounds)
         self.nsig = np.size(self.__trimsig__(tvec, self.ibounds))
@@ -1114,6 +1116,23 @@ class fftanal(Struct):
 
     def getNorms(self):
         self.S1, self.S2, self.NENBW, self.ENBW = fftanal._getNorms(self.win, self.Nnyquist, self.Fs)
+
+    @staticmethod
+    def resample(tvx, sigx, tvy, sigy):
+        """fft_analysis.py:2363-2373: the shorter record is up-sampled (filters.upsample, on the device) to the
+        rate of the longer one.  Like the reference, tvec is the longer record's time vector while the up-sampled
+        record has numpy.arange(t[0], t[-1], 1/Fs) points."""
+        from .filters import upsample
+        Fsx = fftanal.__Fs__(tvx)
+        Fsy = fftanal.__Fs__(tvy)
+        tvec = tvx
+        if len(sigx) > len(sigy):
+            sigy = upsample(sigy, Fsy, Fsx)
+            tvec = tvx
+        elif len(sigy) > len(sigx):
+            sigx = upsample(sigx, Fsx, Fsy)
+            tvec = tvy
+        return tvec, sigx, sigy
 
     @staticmethod
     def __Fs__(tvec):

@@ -155,3 +155,19 @@ def test_fft_deriv_restatement_matches_reference():
             assert relerr(xo, g["xo_%s_%d" % (tag, n)]) <= 1e-14
     d, xo = R.fft_deriv(g["s_256"])
     assert relerr(d, g["d_noxx_256"]) <= 1e-12 and relerr(xo, g["xo_noxx_256"]) <= 1e-14
+
+
+def test_oracle_cog_matches_reference_fixtures():
+    """Doppler.cog restatement against the unmodified reference (tests/golden/cog.npz)."""
+    from oracle.restatement import cog
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "cog.npz"))
+    fs = 2.0e6
+    for tag in "abcd":
+        x = g[tag + "_x"]
+        assert cog(x, fs) == float(g[tag + "_cog"])
+        assert cog(x, fs, fmin=5.0e4, fmax=4.0e5) == float(g[tag + "_cog_band"])
+        assert cog(x, fs, fmin=3.0e6) == 0.0
+    x = g["s_x"]
+    ref = g["s_cog"]
+    got = np.asarray([cog(x[i:i + 512], fs) for i in range(0, len(x) - 511, 256)])
+    assert np.array_equal(got, ref)
