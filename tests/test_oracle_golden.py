@@ -2,6 +2,7 @@
 (tests/golden/*.npz, written by oracle/gen_golden.py from the unmodified
 reference in the build container)."""
 import json
+import os
 
 import numpy as np
 import pytest
