@@ -41,6 +41,8 @@ def parse():
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="weak: --samples per channel PER GPU; strong: --samples per channel in TOTAL")
     ap.add_argument("--no-graph", action="store_true", help="launch the step's kernels one by one (no CUDA graph)")
+    ap.add_argument("--no-affinity", action="store_true",
+                    help="do not bind the process to the CPU cores next to its GPU (engine.bind_host_to_gpu)")
     ap.add_argument("--deferred-exchange", action="store_true",
                     help="N > 1: a step's exchange is collected by the next step (a stream of records; the timed region "
                          "ends with the flush of its last step) instead of being waited for inside the step; measured "
@@ -234,6 +236,8 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=dev)
         group = dist.group.WORLD
 
+    # host side of e2e: this rank's pinned buffers live on the NUMA node of its GPU
+    cores = None if args.no_affinity else engine.bind_host_to_gpu(dev)
     clocks = Clocks(local)                                     # sampled over the whole run (100 ms period)
     if rank == 0:
         clocks.start()
@@ -484,7 +488,8 @@ def run_ours(args):
                         ("deferred: collected by the next step's tc_post_kernel, the timed region ends with the flush "
                          "of its last step" if deferred_on else "waited for inside every step")),
            "sync_exchange_ms_per_step": ms_sync, "deferred_exchange_ms_per_step": ms_deferred,
-           "launch_mode": "per-kernel launches" if args.no_graph else "one CUDA graph replay per step"}
+           "launch_mode": "per-kernel launches" if args.no_graph else "one CUDA graph replay per step",
+           "host_affinity": (None if cores is None else "%d cores next to the GPU (NVML)" % len(cores))}
     if world > 1:
         out["config"]["collective"] = (
             "inside tc_post_kernel: per-item pushes over NVLink peer memory, 131 KB per rank" if step_is_fused else

@@ -19,6 +19,29 @@ _TORCH_CPLX = {"fp32": torch.complex64, "fp64": torch.complex128}
 _CODE = {"fp32": _lib.F32, "fp64": _lib.F64}
 
 
+def bind_host_to_gpu(device=None):
+    """Restricts this process to the CPU cores next to `device` (NVML's CPU affinity of the GPU), so that the pinned
+    staging buffers it allocates afterwards are first-touched on the GPU's own NUMA node: with one process per GPU,
+    eight host->device streams otherwise cross the socket interconnect.  Call it before allocating pinned memory.
+    -> sorted list of the cores, or None when NVML / the affinity call is not available (nothing changed)."""
+    try:
+        import pynvml
+        dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        pynvml.nvmlInit()
+        uuid = str(torch.cuda.get_device_properties(dev).uuid)
+        handle = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid) if not uuid.startswith("GPU-") else uuid)
+        words = (max(os.cpu_count() or 64, 64) + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(handle, words)
+        cores = set(64 * i + b for i, m in enumerate(mask) for b in range(64) if (int(m) >> b) & 1)
+        cores &= set(os.sched_getaffinity(0))
+        if not cores:
+            return None
+        os.sched_setaffinity(0, cores)
+        return sorted(cores)
+    except Exception:
+        return None
+
+
 def require_cuda(device=None):
     if not torch.cuda.is_available():
         raise RuntimeError("pyfft_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
@@ -270,8 +293,8 @@ class WelchPlan(object):
         p = np.abs(W) ** 2
         leak = float(p[self.nlin:self.nfft // 2 + 1].max() / (win ** 2).sum()) if self.nfft >= 1024 else 1.0
         self.can_fuse_mean = self.nfft >= 1024 and leak < (1e-9 if precision == "fp32" else 1e-18)
-        self.wlow = torch.from_numpy(np.ascontiguousarray(
-            np.stack([W.real[:self.nlin], W.imag[:self.nlin]], 1))).to(self.device)
+        self.wlow_host = np.ascontiguousarray(np.stack([W.real[:self.nlin], W.imag[:self.nlin]], 1))
+        self.wlow = torch.from_numpy(self.wlow_host).to(self.device)
         self.est = None
         self.K_local = 0
         # tensor-core route (pyfft_welch_accumulate_tc): nfft 4096, fp32, hop 512 / 1024 / 2048 / 4096, window

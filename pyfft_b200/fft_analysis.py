@@ -58,6 +58,11 @@ class fftinfosc(Struct):
     """Result container of fft_pwelch (fft_analysis.py:794-826): same attribute names."""
 
     _LAZY = ("Pxx_seg", "Pyy_seg", "Pxy_seg", "Xfft_seg", "Yfft_seg", "phixy_seg", "varphi_seg")
+    # O(nfreq) statistics derived from the averaged spectra (fft_analysis.py:496-540, :585-597): computed on the
+    # host at first access (or by dict_from_class) instead of on every call -- twenty numpy passes that most
+    # callers never read cost 0.5 ms of an 11 ms end-to-end call
+    _LAZY_DERIVED = ("varCxy", "varCxy2", "varPxx", "varPyy", "varPxy", "varPhxy", "Lxx", "Lyy", "Lxy", "varLxx",
+                     "varLyy", "varLxy", "Ex", "Ey", "corrcoef", "lags")
 
     def __init__(self):
         f8, c16 = np.float64, np.complex128
@@ -68,16 +73,30 @@ class fftinfosc(Struct):
                          ("varLxy", c16)):
             setattr(self, name, np.array([], dtype=dt))
         self._segment_loader = None
+        self._derived_loader = None
+
+    def _defer_derived(self, loader):
+        """The derived statistics are produced by loader() -> dict at first access."""
+        for nm in fftinfosc._LAZY_DERIVED:
+            self.__dict__.pop(nm, None)
+        self.__dict__["_derived_loader"] = loader
 
     def __getattr__(self, name):
-        # only reached when normal lookup fails: materialise per-segment spectra on demand
+        # only reached when normal lookup fails: materialise per-segment spectra / derived statistics on demand
         if name in fftinfosc._LAZY and self.__dict__.get("_segment_loader") is not None:
             self.__dict__.update(self.__dict__["_segment_loader"]())
             self.__dict__["_segment_loader"] = None
             return self.__dict__[name]
+        if name in fftinfosc._LAZY_DERIVED and self.__dict__.get("_derived_loader") is not None:
+            loader = self.__dict__["_derived_loader"]
+            self.__dict__["_derived_loader"] = None
+            self.__dict__.update(loader())
+            return self.__dict__[name]
         raise AttributeError(name)
 
     def dict_from_class(self):
+        if self.__dict__.get("_derived_loader") is not None:
+            getattr(self, "varCxy")
         if self.__dict__.get("_segment_loader") is not None:
             getattr(self, "Pxx_seg")
         return dict((k, v) for k, v in self.__dict__.items() if not k.startswith("_"))
@@ -413,6 +432,13 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
               (sigy.is_complex() if isinstance(sigy, torch.Tensor) else np.iscomplexobj(sigy))
     if onesided is None:
         onesided = not is_cplx                                     # :123-127
+    # long pinned host records start crossing PCIe NOW, on a side stream, while the host plans the call (window,
+    # norms, segmentation: ~0.2 ms that would otherwise sit in front of a 9.7 ms copy)
+    early = []
+    if group is None and not is_cplx and isinstance(sigx, torch.Tensor) and not sigx.is_cuda:
+        dev0 = _eng.require_cuda(device)
+        with torch.cuda.device(dev0):
+            early.append(_eng.staged_upload(sigx, sigy, _eng.resolve_precision(precision, sigx, sigy), dev0))
     nx = sigx.shape[0]
     ntv = len(tvec)
     if isinstance(sigy, torch.Tensor):
@@ -482,7 +508,10 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
                 y = _eng.channels_first(_eng.to_device(ysl, precision, dev), g_hi - g_lo)
                 src_base = g_lo
             else:
-                staged = _eng.staged_upload(sigx, sigy, precision, dev) if group is None else None
+                if early:
+                    staged = early.pop()                        # started at the top of the call
+                else:
+                    staged = _eng.staged_upload(sigx, sigy, precision, dev) if group is None else None
                 if staged is not None:
                     x, y = staged[0], staged[1]
                 else:
@@ -597,7 +626,7 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
         channels and low bins of leak power / bin power."""
         d = hosted[10]
         nl = min(wp.nlin, hosted[0].shape[0])
-        w2 = (wp.wlow[:nl, 0] ** 2 + wp.wlow[:nl, 1] ** 2).cpu().numpy() * scale
+        w2 = (wp.wlow_host[:nl, 0] ** 2 + wp.wlow_host[:nl, 1] ** 2) * scale
         if onesided:
             w2 = w2 * np.where((np.arange(nl) > 0), 2.0, 1.0)
         lo = 0 if onesided else nfft // 2                      # bin 0 after the fftshift of two-sided spectra
@@ -618,7 +647,12 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
         # window lengths that are not powers of two (the reference's default Navr = 8 gives them) and
         # complex-valued records: per-segment spectra by Bluestein (pyfft_stft_any), products on the device
         wp, res, use_tc, has_offs = None, None, False, False
-        nch, hosted = _pwelch_generic(sigx, sigy, ntv, plan, win, mode, precision, dev, bool(onesided), scale,
+        gx, gy = sigx, sigy
+        if early and early[0] is not None:                       # already on its way to the device
+            st = early.pop()
+            torch.cuda.current_stream(dev).wait_event(st[2][-1])
+            gx, gy = st[0], st[1]
+        nch, hosted = _pwelch_generic(gx, gy, ntv, plan, win, mode, precision, dev, bool(onesided), scale,
                                       lp, group, is_cplx)
     else:
         wp, res, nch, use_tc, hosted, has_offs = run(tensor_cores)
@@ -675,37 +709,46 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
     freq = np.fft.fftfreq(nfft, 1.0 / plan.Fs)                     # :396
     freq = freq[:plan.Nnyquist] if onesided else np.fft.fftshift(freq)
 
-    # ---- O(nfreq) bookkeeping on the averaged spectra, as in the reference (:496-540) ---- #
-    with np.errstate(all="ignore"):
-        fftinfo.varCxy = ((1.0 - Cxy * np.conjugate(Cxy)) / np.sqrt(2 * K)) ** 2.0
-        fftinfo.varCxy2 = 4.0 * Cxy2 * fftinfo.varCxy
-        fftinfo.varPxx = (Pxx / np.sqrt(K)) ** 2.0
-        fftinfo.varPyy = (Pyy / np.sqrt(K)) ** 2.0
-        fftinfo.varPxy = (Pxy / np.sqrt(K)) ** 2.0
-        fftinfo.varPhxy = (np.sqrt(1.0 - np.abs(Cxy2))) / np.sqrt(2 * K * np.sqrt(np.abs(Cxy2))) ** 2.0
-        for nm, P in (("Lxx", Pxx), ("Lyy", Pyy), ("Lxy", Pxy)):
-            amp = np.sqrt(np.abs(fftinfo.ENBW * P))
-            if onesided:
-                amp[1:-1] = np.sqrt(2) * amp[1:-1]
-                if nfft % 2:
-                    amp[-1] = np.sqrt(2) * amp[-1]
-            setattr(fftinfo, nm, amp)
-        fftinfo.Rxx, fftinfo.Ryy = h_rxx, h_ryy
-        fftinfo.Rxy, fftinfo.iCxy = h_rxy, h_icxy
-        # zero-lag values sit at index nfft//2 after the fftshift (:585-596)
-        fftinfo.Ex = fftinfo.Rxx[nfft // 2, ...].copy()
-        fftinfo.Ey = fftinfo.Ryy[nfft // 2, ...].copy()
-        fftinfo.corrcoef = fftinfo.Rxy / np.sqrt(
-            np.ones((nfft, 1), dtype=fftinfo.Rxy.dtype) * (fftinfo.Ex * fftinfo.Ey))
-        fftinfo.lags = (np.asarray(range(1, nfft + 1), dtype=int) - plan.Nnyquist) / plan.Fs
-        fftinfo.varLxx = (fftinfo.Lxx ** 2) * (fftinfo.varPxx / np.abs(Pxx) ** 2)
-        fftinfo.varLyy = (fftinfo.Lyy ** 2) * (fftinfo.varPyy / np.abs(Pyy) ** 2)
-        fftinfo.varLxy = (fftinfo.Lxy ** 2) * (fftinfo.varPxy / np.abs(Pxy) ** 2)
+    # ---- O(nfreq) bookkeeping on the averaged spectra, as in the reference (:496-540): at first access ---- #
+    fftinfo.Rxx, fftinfo.Ryy = h_rxx, h_ryy
+    fftinfo.Rxy, fftinfo.iCxy = h_rxy, h_icxy
+    enbw, nnyq, fs_ = fftinfo.ENBW, plan.Nnyquist, plan.Fs
+
+    def derived(Pxx=Pxx, Pyy=Pyy, Pxy=Pxy, Cxy=Cxy, Cxy2=Cxy2, h_rxx=h_rxx, h_ryy=h_ryy, h_rxy=h_rxy):
+        d = {}
+        with np.errstate(all="ignore"):
+            d["varCxy"] = ((1.0 - Cxy * np.conjugate(Cxy)) / np.sqrt(2 * K)) ** 2.0
+            d["varCxy2"] = 4.0 * Cxy2 * d["varCxy"]
+            d["varPxx"] = (Pxx / np.sqrt(K)) ** 2.0
+            d["varPyy"] = (Pyy / np.sqrt(K)) ** 2.0
+            d["varPxy"] = (Pxy / np.sqrt(K)) ** 2.0
+            d["varPhxy"] = (np.sqrt(1.0 - np.abs(Cxy2))) / np.sqrt(2 * K * np.sqrt(np.abs(Cxy2))) ** 2.0
+            for nm, P in (("Lxx", Pxx), ("Lyy", Pyy), ("Lxy", Pxy)):
+                amp = np.sqrt(np.abs(enbw * P))
+                if onesided:
+                    amp[1:-1] = np.sqrt(2) * amp[1:-1]
+                    if nfft % 2:
+                        amp[-1] = np.sqrt(2) * amp[-1]
+                d[nm] = amp
+            # zero-lag values sit at index nfft//2 after the fftshift (:585-596)
+            d["Ex"] = h_rxx[nfft // 2, ...].copy()
+            d["Ey"] = h_ryy[nfft // 2, ...].copy()
+            d["corrcoef"] = h_rxy / np.sqrt(np.ones((nfft, 1), dtype=h_rxy.dtype) * (d["Ex"] * d["Ey"]))
+            d["lags"] = (np.asarray(range(1, nfft + 1), dtype=int) - nnyq) / fs_
+            d["varLxx"] = (d["Lxx"] ** 2) * (d["varPxx"] / np.abs(Pxx) ** 2)
+            d["varLyy"] = (d["Lyy"] ** 2) * (d["varPyy"] / np.abs(Pyy) ** 2)
+            d["varLxy"] = (d["Lxy"] ** 2) * (d["varPxy"] / np.abs(Pxy) ** 2)
+        if nch == 1:                                               # :605-631
+            for nm in ("lags", "corrcoef", "Lxx", "Lyy", "Lxy", "varLxx", "varLyy", "varLxy", "varCxy", "varCxy2",
+                       "varPxx", "varPyy", "varPxy", "varPhxy"):
+                d[nm] = d[nm].flatten()
+        return d
+
+    fftinfo._defer_derived(derived)
 
     if nch == 1:                                                   # :605-631
         Pyy, Pxy, Cxy, Cxy2, phi_xy = (a.flatten() for a in (Pyy, Pxy, Cxy, Cxy2, phi_xy))
-        for nm in ("lags", "Rxx", "Ryy", "Rxy", "corrcoef", "iCxy", "Lxx", "Lyy", "Lxy", "varLxx",
-                   "varLyy", "varLxy", "varCxy", "varCxy2", "varPxx", "varPyy", "varPxy", "varPhxy"):
+        for nm in ("Rxx", "Ryy", "Rxy", "iCxy"):
             setattr(fftinfo, nm, getattr(fftinfo, nm).flatten())
 
     fftinfo.nch = nch
