@@ -541,7 +541,9 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
                 # (2^-12 relative, zero mean) averages out as 1/sqrt(K) -- used when enough segments
                 # are averaged for the 1e-5-of-peak contract to hold with margin, and checked afterwards
                 # against the dynamic range of the result (TC_DYNAMIC_RANGE)
-                use_tc = wp.can_use_tc and (nseg >= 16384 if tc_choice is None else bool(tc_choice))
+                # (K, not this rank's share of it: the roundings average over all segments of the record, and every
+                # rank of a sharded call must take the same route -- the routes end in different exchanges)
+                use_tc = wp.can_use_tc and (K >= 16384 if tc_choice is None else bool(tc_choice))
                 accumulate = wp.accumulate_tc if use_tc else wp.accumulate_mean
                 estimate = wp.prepare_tc if use_tc else wp.estimate_mean
                 res = None
@@ -685,6 +687,12 @@ def fft_pwelch(tvec, sigx, sigy, tbounds=None, Navr=None, windowoverlap=None,
                    % float(np.min(rng[:, 0] / np.maximum(rng[:, 1], 1e-300))))
         if flag:
             wp._tc_status.zero_()
+        if group is not None and world > 1 and tensor_cores is None:
+            # sharded: the measures are per shard, the rerun is a collective decision
+            vote = torch.tensor([0 if why is None else 1], dtype=torch.int32, device=dev)
+            torch.distributed.all_reduce(vote, op=torch.distributed.ReduceOp.MAX, group=group)
+            if int(vote.item()) and why is None:
+                why = "another rank's shard failed the checks of the tensor-core path"
         if why is not None:
             if tensor_cores is None:
                 # data-aware selection: rerun on the fp32 CUDA-core kernel (no CPU fallback)
