@@ -448,8 +448,19 @@ def run_ours(args):
             h2d = 2 * (g_hi - g_lo) * 4
         es = max(3, min(args.steps, 10))
         ms_e2e = timed(e2e_step, es, 2)
+
+        # the ceiling of e2e on this box: the same host -> device copies alone (all ranks at once)
+        xd_, yd_ = torch.empty_like(xh, device=dev), torch.empty_like(yh, device=dev)
+
+        def copies_only():
+            xd_.copy_(xh, non_blocking=True)
+            yd_.copy_(yh, non_blocking=True)
+        ms_h2d = timed(copies_only, es, 2)
+        del xd_, yd_
         e2e = {"value": NCH * ntot / (ms_e2e / 1e3) / 1e6, "unit": UNIT, "h2d_bytes_per_step": h2d,
                "d2h_bytes_per_step": 6 * (NFFT // 2) * 16 + 4 * NFFT * 8, "ms_per_step": ms_e2e,
+               "h2d_only_ms_per_step": ms_h2d, "h2d_only_gbs_per_gpu": h2d / (ms_h2d / 1e3) / 1e9,
+               "ceiling_from_h2d": NCH * ntot / (ms_h2d / 1e3) / 1e6,
                "steps": es, "api": "pyfft_b200.fft_pwelch" if world == 1 else "pyfft_b200.fft_pwelch(group=, shard_offset=)"}
 
     if rank != 0:

@@ -141,3 +141,14 @@ def test_peer_reducer_needs_an_nccl_group():
     import torch
     from pyfft_b200 import engine
     assert engine.PeerReducer.create(1024, torch.device("cpu"), None) is False
+
+
+def test_bind_host_to_gpu_is_harmless_without_a_gpu():
+    """engine.bind_host_to_gpu: no NVML / no device -> None and the affinity of the process is untouched."""
+    import os
+    from pyfft_b200 import engine
+    before = os.sched_getaffinity(0)
+    got = engine.bind_host_to_gpu("cuda:0")
+    assert got is None or set(got) <= before
+    if got is None:
+        assert os.sched_getaffinity(0) == before
