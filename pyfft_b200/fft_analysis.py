@@ -94,6 +94,20 @@ class fftinfosc(Struct):
             return self.__dict__[name]
         raise AttributeError(name)
 
+    def __getstate__(self):
+        """Pickling: the derived statistics are computed, the per-segment loader (a closure over the caller's
+        records, which it keeps alive and re-reads at first access -- read the `*_seg` fields before mutating or
+        dropping those arrays) is left behind: an unpickled result has no lazy per-segment fields."""
+        if self.__dict__.get("_derived_loader") is not None:
+            getattr(self, "varCxy")
+        d = dict(self.__dict__)
+        d["_segment_loader"] = None
+        d["_derived_loader"] = None
+        return d
+
+    def __setstate__(self, d):
+        self.__dict__.update(d)
+
     def dict_from_class(self):
         if self.__dict__.get("_derived_loader") is not None:
             getattr(self, "varCxy")

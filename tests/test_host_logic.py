@@ -152,3 +152,21 @@ def test_bind_host_to_gpu_is_harmless_without_a_gpu():
     assert got is None or set(got) <= before
     if got is None:
         assert os.sched_getaffinity(0) == before
+
+
+def test_fftinfo_pickles_without_its_loaders():
+    """The lazy loaders are closures: pickling computes the derived statistics and drops them."""
+    import pickle
+    import numpy as np
+    from pyfft_b200.fft_analysis import fftinfosc
+    f = fftinfosc()
+    f._defer_derived(lambda: {"varCxy": np.ones(3), "Lxx": np.zeros(2)})
+    f._segment_loader = lambda: {"Pxx_seg": np.zeros(1)}
+    g = pickle.loads(pickle.dumps(f))
+    assert np.array_equal(g.varCxy, np.ones(3)) and g._segment_loader is None
+    try:
+        g.Pxx_seg
+        raise AssertionError("expected AttributeError")
+    except AttributeError:
+        pass
+    assert np.array_equal(f.Pxx_seg, np.zeros(1))          # the original keeps its loader
