@@ -388,9 +388,11 @@ def run_ours(args):
     dev_fused = float((r1["Pxy"] - r2["Pxy"]).abs().max() / r2["Pxy"].abs().max())
     assert dev_fused < 1e-5 and not wp.tc_failed(), dev_fused
     dev_coh = float((r1["Cxy"] - r2["Cxy"]).abs().max())
-    # keep the same step running for ~0.8 s so that the 100 ms clock sampler sees the load
-    t_end = time.perf_counter() + 0.8
-    while time.perf_counter() < t_end:
+    # keep the same step running for ~0.8 s so that the 100 ms clock sampler sees the load.  The number of steps is
+    # derived from the (max-over-ranks) step time, NOT from each rank's own clock: the steps of a sharded run are
+    # coupled by their exchange, and a rank that ran one batch more than its peers would wait for them until the
+    # bounded wait of the exchange expires
+    for _ in range(max(1, int(np.ceil(800.0 / (50.0 * ms_step))))):
         for _ in range(50):
             step_run()
         torch.cuda.synchronize()
