@@ -43,11 +43,11 @@ def parse():
     ap.add_argument("--no-graph", action="store_true", help="launch the step's kernels one by one (no CUDA graph)")
     ap.add_argument("--no-affinity", action="store_true",
                     help="do not bind the process to the CPU cores next to its GPU (engine.bind_host_to_gpu)")
-    ap.add_argument("--sync-exchange", action="store_true",
-                    help="N > 1: every step waits for its own exchange.  Default: a step's exchange is collected by the "
-                         "next step's last kernel (a stream of records: no rank waits for a slower one inside a step) and "
-                         "the timed region ends with the flush that completes its last step; 1-2 %% faster at 2-8 GPUs "
-                         "(profiles/r02f_multi_gpu.txt); the in-step number is reported beside it")
+    ap.add_argument("--deferred-exchange", action="store_true",
+                    help="N > 1: a step's exchange is collected by the next step's last kernel (a stream of records: no "
+                         "rank waits for a slower one inside a step; the timed region ends with the flush that completes "
+                         "its last step) instead of being waited for inside the step.  Within +-1.5 %% of the default on "
+                         "NVSwitch (profiles/r02f_multi_gpu.txt); the default line reports it beside its own number")
     ap.add_argument("--unfused", action="store_true",
                     help="the step as separate calls (prepare, accumulate, tail sums, [rereference, reduce,] finalize) "
                          "instead of the three launches of pyfft_welch_tc_step")
@@ -268,7 +268,7 @@ def run_ours(args):
 
     tails = ((s_lo, c_lo), (c_hi, s_hi))
     fused_step = use_tc and not args.unfused
-    defer = world > 1 and not args.sync_exchange
+    defer = world > 1 and args.deferred_exchange
 
     def step():
         # ONE pass over HBM: provisional mean (+ scale) from 64 Ki samples, fused Welch
