@@ -170,3 +170,20 @@ def test_fftinfo_pickles_without_its_loaders():
     except AttributeError:
         pass
     assert np.array_equal(f.Pxx_seg, np.zeros(1))          # the original keeps its loader
+
+
+def test_cog_weights_reproduce_the_reference_band_selection():
+    """doppler._weights (host side of pyfft_spectral_centroid) against the oracle's literal cog, including the
+    reference's band selection that pairs the first m shifted bins with the m selected frequencies."""
+    import numpy as np
+    from oracle.restatement import cog
+    from pyfft_b200.doppler import _weights
+    rng = np.random.default_rng(3)
+    for n in (64, 333, 1000):
+        x = rng.standard_normal(n) + 1j * rng.standard_normal(n) + np.exp(2j * np.pi * 0.11 * np.arange(n))
+        P = np.abs(np.fft.fft(x)) ** 2
+        for fmin, fmax in ((None, None), (5.0e4, 4.0e5), (0.0, 1.0e5), (3.0e6, None)):
+            wn, wd = _weights(n, 2.0e6, fmin, fmax)
+            got = (P @ wn) / (P @ wd) if wd.sum() > 0 else 0.0
+            ref = cog(x, 2.0e6, fmin=fmin, fmax=fmax)
+            assert abs(got - ref) <= 1e-9 * 2.0e6, (n, fmin, fmax)
