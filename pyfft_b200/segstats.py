@@ -33,7 +33,7 @@ def welch_segment_statistics(tvec, sigx, sigy, tbounds=None, Navr=None, windowov
       mca, msa, vca, vsa     the component means / variances behind them
 
     Real records, power-of-two window lengths 64 .. 8192 (the fused kernels); mean / linear / no detrend."""
-    from .fft_analysis import Struct, _Plan, fftanal, varphi
+    from .fft_analysis import _Plan, fftanal
 
     precision = kwargs.pop("precision", None)
     device = kwargs.pop("device", None)
@@ -95,27 +95,35 @@ def welch_segment_statistics(tvec, sigx, sigy, tbounds=None, Navr=None, windowov
         if group is not None and world > 1:
             torch.distributed.all_reduce(mom, group=group)
         m = mom.cpu().numpy()
-    # ---- O(nfft) bookkeeping on the host: side selection, scaling, variances (fft_analysis.py:402-446) ---- #
-    scale = 1.0 / S1 ** 2 / ENBW
+    out = stats_from_moments(m, K, 1.0 / S1 ** 2 / ENBW, bool(onesided), nfft, plan.Fs, plan.Nnyquist, angle_range)
+    out.nwins, out.ENBW = nwins, ENBW
+    return out
+
+
+def stats_from_moments(m, K, scale, onesided, nfft, Fs, nnyq, angle_range=0.5 * np.pi):
+    """Host bookkeeping behind welch_segment_statistics: m = (nch, 12, nfft/2 + 1) sums over the K segments as
+    written by pyfft_segment_moments -> Struct of means, variances and the circular mean of the segment phase
+    (side selection, doubling and scaling as fft_analysis.py:402-446)."""
+    from .fft_analysis import Struct, varphi
+    nch = m.shape[0]
     if onesided:
-        F = plan.Nnyquist
+        F = nnyq
         sel = np.arange(F)
         wgt = np.ones(F)
         wgt[1:-1] = 2.0                                            # :414-416 (nfft even: the last bin stays x1)
         sign = np.ones(F)
-        freq = plan.Fs * np.arange(F) / nfft
+        freq = Fs * np.arange(F) / nfft
     else:
         k = (np.arange(nfft) + nfft - nfft // 2) % nfft            # fftshift order (:423-427)
         sel = np.where(k <= nfft // 2, k, nfft - k)
         sign = np.where(k <= nfft // 2, 1.0, -1.0)                 # Hermitian mirror: Pxy conjugated
         wgt = np.ones(nfft)
-        freq = np.fft.fftshift(np.fft.fftfreq(nfft, 1.0 / plan.Fs))
+        freq = np.fft.fftshift(np.fft.fftfreq(nfft, 1.0 / Fs))
     s = (scale * wgt)[None, :]
     mm = m[:, :, sel] / float(K)                                   # (nch, 12, F) means over the segments
     out = Struct()
-    out.Navr, out.freq, out.nwins, out.ENBW = K, freq, nwins, ENBW
-    Pxx = (mm[0, 0] * s[0])
-    out.Pxx = Pxx.astype(np.complex128)
+    out.Navr, out.freq = K, freq
+    out.Pxx = (mm[0, 0] * s[0]).astype(np.complex128)
     out.Pyy = (mm[:, 1] * s).T.astype(np.complex128)
     out.Pxy = ((mm[:, 2] + 1j * sign[None, :] * mm[:, 3]) * s).T
     out.varPxx = (mm[0, 4] - mm[0, 0] ** 2) * s[0] ** 2

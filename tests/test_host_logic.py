@@ -187,3 +187,47 @@ def test_cog_weights_reproduce_the_reference_band_selection():
             got = (P @ wn) / (P @ wd) if wd.sum() > 0 else 0.0
             ref = cog(x, 2.0e6, fmin=fmin, fmax=fmax)
             assert abs(got - ref) <= 1e-9 * 2.0e6, (n, fmin, fmax)
+
+
+def test_segment_statistics_bookkeeping_against_numpy():
+    """segstats.stats_from_moments (host side of pyfft_segment_moments): moments built with numpy from explicit
+    per-segment spectra -> np.var over the segments and the reference-style mean_angle, one- and two-sided."""
+    import numpy as np
+    from pyfft_b200.segstats import stats_from_moments
+    from pyfft_b200.fft_analysis import varphi
+    rng = np.random.default_rng(4)
+    nfft, hop, K, nch, Fs = 64, 32, 37, 2, 1.0e3
+    n = (K - 1) * hop + nfft
+    x = rng.standard_normal(n) + np.sin(0.7 * np.arange(n))
+    y = rng.standard_normal((nch, n)) + 0.5 * x
+    w = np.hanning(nfft + 1)[:-1]
+    X = np.stack([np.fft.fft(w * x[k * hop:k * hop + nfft]) for k in range(K)])
+    Y = np.stack([[np.fft.fft(w * y[c, k * hop:k * hop + nfft]) for k in range(K)] for c in range(nch)])
+    nb = nfft // 2 + 1
+    m = np.zeros((nch, 12, nb))
+    for c in range(nch):
+        pxx, pyy, pxy = np.abs(X[:, :nb]) ** 2, np.abs(Y[c, :, :nb]) ** 2, Y[c, :, :nb] * np.conj(X[:, :nb])
+        ph = np.angle(pxy)
+        for q, v in enumerate((pxx, pyy, pxy.real, pxy.imag, pxx ** 2, pyy ** 2, pxy.real ** 2, pxy.imag ** 2,
+                               np.cos(ph), np.sin(ph), np.cos(ph) ** 2, np.sin(ph) ** 2)):
+            m[c, q] = v.sum(axis=0)
+    scale = 0.37
+    for onesided in (True, False):
+        out = stats_from_moments(m, K, scale, onesided, nfft, Fs, nfft // 2)
+        if onesided:
+            wgt = np.ones(nfft // 2)
+            wgt[1:-1] = 2.0
+            Pxx_seg = (np.abs(X[:, :nfft // 2]) ** 2) * wgt * scale
+            Pxy_seg = np.stack([(Y[c] * np.conj(X))[:, :nfft // 2] * wgt * scale for c in range(nch)])
+        else:
+            Pxx_seg = np.fft.fftshift(np.abs(X) ** 2, axes=-1) * scale
+            Pxy_seg = np.stack([np.fft.fftshift(Y[c] * np.conj(X), axes=-1) * scale for c in range(nch)])
+        assert np.allclose(out.varPxx, np.var(Pxx_seg, axis=0), rtol=1e-10, atol=1e-12 * np.max(Pxx_seg) ** 2)
+        ref = (np.var(Pxy_seg.real, axis=1) + 1j * np.var(Pxy_seg.imag, axis=1)).T
+        assert np.allclose(out.varPxy, ref, rtol=1e-9, atol=1e-12 * np.max(np.abs(Pxy_seg)) ** 2)
+        assert np.allclose(out.Pxy, Pxy_seg.mean(axis=1).T, rtol=1e-10, atol=1e-12 * np.max(np.abs(Pxy_seg)))
+        ph = np.angle(Pxy_seg)
+        ca, sa = np.cos(ph), np.sin(ph)
+        mp, vp = varphi(Pxy_real=ca.mean(axis=1), Pxy_imag=sa.mean(axis=1), varPxy_real=ca.var(axis=1),
+                        varPxy_imag=sa.var(axis=1), angle_range=0.5 * np.pi)
+        assert np.allclose(out.phi_mean, mp.T, rtol=0, atol=1e-9)
